@@ -1,0 +1,135 @@
+"""Additions of the B200 build that the reference does not have (the reference surface stays untouched).
+
+* :func:`render_heatmap_batched` — FRESH mode: allocates (or overwrites) the heatmap, zero-init fused into the render
+  kernel, so the caller-side ``torch.zeros`` of the reference (e.g.
+  /root/reference/packages/draw_heatmap/tests/test_draw_heatmap_batched_classwise.py:114-116) disappears.
+* :func:`radius_center` — K1, bit-exact to tests/_test_helpers.py:20-28 of the reference.
+* :func:`render_heatmap_from_boxes` — K1 fused into the renderer: float boxes in, heatmap out, one launch.
+* :class:`RaggedBatch` — minimal stand-in for accvlab.batching_helpers.RaggedBatch (fields ``tensor``,
+  ``sample_sizes``; /root/reference/packages/batching_helpers/accvlab/batching_helpers/data_format/ragged_batch.py:109-171).
+* :func:`shard_range` — contiguous batch slice of a rank (multi-GPU: no collective on the data path).
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from accvlab.draw_heatmap import draw_heatmap_ext as _ext
+
+__all__ = [
+    "RaggedBatch",
+    "radius_center",
+    "render_heatmap_batched",
+    "render_heatmap_from_boxes",
+    "render_heatmap_flat",
+    "shard_range",
+    "launch_count",
+    "fill_probe",
+]
+
+
+class RaggedBatch:
+    """Right-padded batch: ``tensor [B, max_sample_size, *data]`` + ``sample_sizes [B]``; padding content undefined."""
+
+    def __init__(self, tensor: torch.Tensor, mask: Optional[torch.Tensor] = None,
+                 sample_sizes: Optional[torch.Tensor] = None, non_uniform_dim: Optional[int] = None):
+        if sample_sizes is None:
+            if mask is None:
+                raise ValueError("Either `mask` or `sample_sizes` must be given")
+            sample_sizes = mask.sum(dim=1)
+        if non_uniform_dim not in (None, 1):
+            raise NotImplementedError("only one batch dimension (non_uniform_dim=1) is supported by draw_heatmap")
+        self._tensor = tensor
+        self._sample_sizes = sample_sizes
+        self._mask = mask
+
+    @property
+    def tensor(self) -> torch.Tensor:
+        return self._tensor
+
+    @property
+    def sample_sizes(self) -> torch.Tensor:
+        return self._sample_sizes
+
+    @property
+    def mask(self) -> torch.Tensor:
+        if self._mask is None:
+            t = torch.arange(self._tensor.shape[1], device=self._tensor.device)
+            self._mask = t[None, :] < self._sample_sizes[:, None]
+        return self._mask
+
+    @property
+    def max_sample_size(self) -> int:
+        return self._tensor.shape[1]
+
+    @property
+    def non_uniform_dim(self) -> int:
+        return 1
+
+
+def radius_center(centers: torch.Tensor, bboxes: torch.Tensor, out_size_factor: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``(int32 centres [...,2], int32 radii [...])`` from float centres ``[...,2]`` and boxes ``[...,4]`` (x1,y1,x2,y2)."""
+    return _ext.radius_center(centers, bboxes, float(out_size_factor))
+
+
+def _tensor_and_sizes(x):
+    return (x.tensor, x.sample_sizes) if hasattr(x, "sample_sizes") else (x, None)
+
+
+def render_heatmap_batched(centers, radii, height: Optional[int] = None, width: Optional[int] = None,
+                           num_classes: Optional[int] = None, labels=None, diameter_to_sigma_factor: float = 6.0,
+                           k_scale: float = 1.0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Render a fresh heatmap (every pixel written once; zeros where nothing is drawn). Returns the heatmap.
+
+    ``centers``/``radii``/``labels`` are RaggedBatches (or anything with ``.tensor`` and ``.sample_sizes``).
+    Either pass ``out`` (any contents, fully overwritten) or ``height``/``width`` (+ ``num_classes`` with labels).
+    """
+    ct, sizes = _tensor_and_sizes(centers)
+    rt, _ = _tensor_and_sizes(radii)
+    lt = None if labels is None else _tensor_and_sizes(labels)[0]
+    if out is None:
+        shape = (ct.shape[0], height, width) if lt is None else (ct.shape[0], num_classes, height, width)
+        out = torch.empty(shape, dtype=torch.float32, device=ct.device)
+    _ext.render_heatmap_batched(out, ct, rt, sizes, lt, diameter_to_sigma_factor, k_scale, True)
+    return out
+
+
+def render_heatmap_from_boxes(centers: torch.Tensor, bboxes: torch.Tensor, out_size_factor: float,
+                              sample_sizes: torch.Tensor, height: Optional[int] = None, width: Optional[int] = None,
+                              num_classes: Optional[int] = None, labels: Optional[torch.Tensor] = None,
+                              diameter_to_sigma_factor: float = 6.0, k_scale: float = 1.0,
+                              out: Optional[torch.Tensor] = None, fresh: bool = True) -> torch.Tensor:
+    """Float centres ``[B,T,2]`` + boxes ``[B,T,4]`` -> heatmap, radius/centre computation fused (one launch)."""
+    if out is None:
+        shape = (centers.shape[0], height, width) if labels is None else (centers.shape[0], num_classes, height, width)
+        out = torch.empty(shape, dtype=torch.float32, device=centers.device)
+        fresh = True
+    _ext.render_heatmap_from_boxes(out, centers, bboxes, float(out_size_factor), sample_sizes, labels,
+                                   diameter_to_sigma_factor, k_scale, fresh)
+    return out
+
+
+def render_heatmap_flat(centers: torch.Tensor, radii: torch.Tensor, heatmap_idxes: torch.Tensor, num_heatmaps: int,
+                        height: int, width: int, diameter_to_sigma_factor: float = 6.0, k_scale: float = 1.0,
+                        out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fresh-mode variant of ``draw_heatmap`` (concatenated objects + plane index)."""
+    if out is None:
+        out = torch.empty((num_heatmaps, height, width), dtype=torch.float32, device=centers.device)
+    _ext.render_heatmap_flat(out, centers, radii, heatmap_idxes, diameter_to_sigma_factor, k_scale, True)
+    return out
+
+
+def shard_range(batch_size: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """Contiguous slice ``[lo, hi)`` of the (flattened batch x camera) dimension owned by ``rank``."""
+    if not (0 <= rank < world_size):
+        raise ValueError("rank must be in [0, world_size)")
+    return batch_size * rank // world_size, batch_size * (rank + 1) // world_size
+
+
+def launch_count() -> int:
+    return int(_ext.launch_count())
+
+
+def fill_probe(t: torch.Tensor) -> None:
+    _ext.fill_probe(t)

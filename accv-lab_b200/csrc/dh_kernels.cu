@@ -1,0 +1,809 @@
+// dh_kernels.cu — sm_100a kernels + C ABI of the B200-native Gaussian heatmap renderer.
+//
+// Replaces the reference hot path (citations relative to /root/reference/packages/draw_heatmap):
+//   accvlab/draw_heatmap/include/draw_heatmap_cuda_kernel.cuh:26-109  (one thread per object, global CAS atomics)
+//   accvlab/draw_heatmap/csrc/draw_heatmap_cuda.cu:29-60              (launchers)
+//   tests/_test_helpers.py:20-28                                      (bbox -> integer centre / radius)
+//
+// Design (not a port): the OUTPUT is partitioned, not the objects.
+//   K1  radius_center   : one thread per box, fp32 IEEE, bit-exact vs the reference helper.
+//   K2  binning         : every render unit (a group of row bands of one plane) scans the objects of its
+//                         sample / plane and compacts the overlapping ones into a shared-memory list with
+//                         warp ballot + popc prefix; band lists are compacted again from the unit list.
+//                         The flat API additionally counting-sorts objects by plane (match_any aggregated).
+//   K3  max-blend       : pixel-owner threads keep max_o(-(i^2+j^2)*vinv_o) in registers (no atomics on
+//                         the heatmap, shared or global) and evaluate ONE expf per touched pixel:
+//                         max_o k*exp(a_o) == k*exp(max_o a_o) bit-for-bit because expf is monotone
+//                         (verified exhaustively on the GPU by tests/test_gpu_expf_monotone.py).
+//   K4  write           : every pixel is stored exactly once with 128-bit coalesced stores; zero-init is
+//                         fused (FRESH mode writes zeros where nothing was drawn and never reads).
+// No tensor cores: this is HBM-write-bound byte work, not a contraction.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+
+#include "dh_b200.h"
+
+#define DH_STR2(x) #x
+#define DH_STR(x) DH_STR2(x)
+
+namespace dh {
+
+constexpr int kThreads = 256;
+constexpr int kItemsPerThread = 8;
+constexpr int kBandCap = kThreads * kItemsPerThread;  // items (float4 or float) per band
+constexpr int kListCap = 1024;                        // objects per shared-memory list
+
+enum Source : int { SRC_BATCHED = 0, SRC_BOXES = 1, SRC_CSR = 2, SRC_FLATSCAN = 3 };
+
+struct __align__(16) Obj {
+    float fx, fy, fr, wv;  // centre, radius (exact small ints as floats), signed 1/var
+};
+
+struct RenderParams {
+    float* heat;
+    const int32_t* centers;  // [.,2]   SRC_BATCHED / SRC_CSR / SRC_FLATSCAN
+    const int32_t* radii;
+    const float* centers_f;  // [.,2]   SRC_BOXES
+    const float* bboxes_f;   // [.,4]
+    float osf;
+    const int32_t* labels;   // may be null (batched sources)
+    const void* sizes;       // [B] int32 / int64
+    int sizes_i64;
+    const int32_t* plane_idx;  // [N] SRC_FLATSCAN
+    const int32_t* csr_off;    // [M+1] SRC_CSR
+    const int32_t* csr_items;  // [N]
+    long long num_objects;     // N (flat sources)
+    long long num_planes;
+    int C, T, H, W;
+    int wunits;  // W / PX
+    int band_rows, band_cols, bands_x, bands_y, bands_per_plane, bands_per_unit, units_per_plane;
+    long long total_units;
+    float factor, k;
+    dh_status* status;
+};
+
+// ------------------------------------------------------------------------------------------------
+// K1 arithmetic (tests/_test_helpers.py:20-28), shared by the stand-alone kernel and SRC_BOXES.
+__device__ __forceinline__ void radius_center_one(float cx, float cy, float x1, float y1, float x2, float y2,
+                                                  float osf, int& xi, int& yi, int& r) {
+    const float m = fminf(fminf(__fsub_rn(cx, x1), __fsub_rn(cy, y1)), fminf(__fsub_rn(x2, cx), __fsub_rn(y2, cy)));
+    r = (int)ceilf(__fdiv_rn(m, osf));
+    if (r < 1) r = 1;
+    xi = (int)__fdiv_rn(cx, osf);
+    yi = (int)__fdiv_rn(cy, osf);
+}
+
+__global__ void __launch_bounds__(256) radius_center_kernel(const float* __restrict__ centers,
+                                                            const float* __restrict__ bboxes, float osf, long long n,
+                                                            int32_t* __restrict__ centers_out,
+                                                            int32_t* __restrict__ radii_out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        int xi, yi, r;
+        radius_center_one(centers[2 * i], centers[2 * i + 1], bboxes[4 * i], bboxes[4 * i + 1], bboxes[4 * i + 2],
+                          bboxes[4 * i + 3], osf, xi, yi, r);
+        centers_out[2 * i] = xi;
+        centers_out[2 * i + 1] = yi;
+        radii_out[i] = r;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Object -> list entry, culled against a pixel rectangle rows [ry0,ry1) x cols [rx0,rx1).
+// sigma/var arithmetic restates cuh:61-63 / 90-92 with explicit IEEE intrinsics.
+__device__ __forceinline__ bool make_obj(int x, int y, int r, float factor, bool kneg, int ry0, int ry1, int rx0, int rx1,
+                                         Obj& o, dh_status* st, bool count) {
+    if (r < 0) return false;  // reference: empty loops
+    if (r > DH_MAX_RADIUS) {
+        if (count && st) atomicAdd(&st->skipped_radius, 1u);
+        return false;
+    }
+    const long long X = x, Y = y, R = r;
+    if (Y + R < ry0 || Y - R >= ry1 || X + R < rx0 || X - R >= rx1) return false;
+    const int d = 2 * r + 1;
+    const float sigma = __fdiv_rn((float)d, factor);
+    const float var = __fmul_rn(__fmul_rn(2.0f, sigma), sigma);
+    const float vinv = __fdiv_rn(1.0f, var);
+    o.fx = (float)x;
+    o.fy = (float)y;
+    o.fr = (float)r;
+    o.wv = kneg ? vinv : -vinv;
+    return true;
+}
+
+// Warp-ballot + popc-prefix compaction of `pred` lanes into list[] (capacity kListCap); *cnt in shared memory.
+__device__ __forceinline__ void compact_push(bool pred, const Obj& o, Obj* list, int* cnt) {
+    const unsigned bal = __ballot_sync(0xffffffffu, pred);
+    if (bal) {
+        const int lane = threadIdx.x & 31;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(cnt, __popc(bal));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        const int pos = base + __popc(bal & ((1u << lane) - 1u));
+        if (pred && pos < kListCap) list[pos] = o;
+    }
+}
+
+template <int PX>
+struct Vec;
+template <>
+struct Vec<4> {
+    using type = float4;
+};
+template <>
+struct Vec<1> {
+    using type = float;
+};
+
+template <int PX>
+__device__ __forceinline__ void store_px(float* p, const float (&v)[PX]) {
+    if constexpr (PX == 4) {
+        *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+        *p = v[0];
+    }
+}
+
+// Zero a rectangle rows [y0,y1) x units [cu0,cu1) of one plane (FRESH mode, nothing to draw there).
+template <int PX>
+__device__ __forceinline__ void zero_rect(float* plane, int W, int wunits, int y0, int y1, int cu0, int cu1) {
+    using V = typename Vec<PX>::type;
+    V z;
+    if constexpr (PX == 4) z = make_float4(0.f, 0.f, 0.f, 0.f); else z = 0.f;
+    if (cu0 == 0 && cu1 == wunits) {
+        V* p = reinterpret_cast<V*>(plane + (long long)y0 * W);
+        const int n = (y1 - y0) * wunits;
+#pragma unroll 4
+        for (int i = threadIdx.x; i < n; i += kThreads) p[i] = z;
+    } else {
+        const int cw = cu1 - cu0;
+        for (int y = y0; y < y1; ++y) {
+            V* p = reinterpret_cast<V*>(plane + (long long)y * W) + cu0;
+            for (int i = threadIdx.x; i < cw; i += kThreads) p[i] = z;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2+K3+K4: persistent tile-owner renderer.
+template <int PX, bool ACCUM, int SRC>
+__global__ void __launch_bounds__(kThreads) render_kernel(const RenderParams p) {
+    __shared__ Obj s_unit[kListCap];
+    __shared__ Obj s_band[kListCap];
+    __shared__ int s_cnt[2];
+
+    const int tid = threadIdx.x;
+    const float NEG_INF = __int_as_float(0xff800000);
+    const bool kneg = p.k < 0.0f;
+    const long long plane_elems = (long long)p.H * p.W;
+
+    for (long long u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+        const long long plane = u / p.units_per_plane;
+        const int ug = (int)(u - plane * p.units_per_plane);
+        float* const plane_ptr = p.heat + plane * plane_elems;
+
+        // unit rectangle
+        int uy0, uy1, ucu0, ucu1, b0, b1;
+        if (p.bands_x == 1) {
+            b0 = ug * p.bands_per_unit;
+            b1 = min(b0 + p.bands_per_unit, p.bands_y);
+            uy0 = b0 * p.band_rows;
+            uy1 = min(b1 * p.band_rows, p.H);
+            ucu0 = 0;
+            ucu1 = p.wunits;
+        } else {  // one band per unit, a column segment of one row group
+            b0 = ug;
+            b1 = ug + 1;
+            const int by = ug / p.bands_x, bx = ug - by * p.bands_x;
+            uy0 = by * p.band_rows;
+            uy1 = min(uy0 + p.band_rows, p.H);
+            ucu0 = bx * p.band_cols;
+            ucu1 = min(ucu0 + p.band_cols, p.wunits);
+        }
+
+        // ---- source range of this unit --------------------------------------------------------
+        long long src_base = 0;  // first object slot
+        int n = 0;               // slots to scan
+        int cls = 0;
+        bool count_skips = false;
+        if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+            const long long sample = plane / p.C;
+            cls = (int)(plane - sample * p.C);
+            long long ns = p.sizes_i64 ? reinterpret_cast<const long long*>(p.sizes)[sample]
+                                       : (long long)reinterpret_cast<const int*>(p.sizes)[sample];
+            ns = ns < 0 ? 0 : (ns > p.T ? p.T : ns);
+            n = (int)ns;
+            src_base = sample * p.T;
+            count_skips = (ug == 0 && cls == 0);
+        } else if constexpr (SRC == SRC_CSR) {
+            const int o0 = p.csr_off[plane], o1 = p.csr_off[plane + 1];
+            src_base = o0;
+            n = o1 - o0;
+            count_skips = (ug == 0);
+        } else {  // SRC_FLATSCAN: every unit looks at all N objects
+            n = (int)p.num_objects;
+            count_skips = (u == 0);
+        }
+
+        // Load slot t (t < n) and cull it against a pixel rectangle.
+        auto load_obj = [&](int t, int ry0, int ry1, int rx0, int rx1, bool cnt, Obj& o) -> bool {
+            int x, y, r;
+            if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+                const long long i = src_base + t;
+                if (p.labels != nullptr) {
+                    const int lab = p.labels[i];
+                    if (lab != cls) {
+                        if (cnt && p.status && (lab < 0 || lab >= p.C)) atomicAdd(&p.status->skipped_label, 1u);
+                        return false;
+                    }
+                }
+                if constexpr (SRC == SRC_BOXES) {
+                    radius_center_one(p.centers_f[2 * i], p.centers_f[2 * i + 1], p.bboxes_f[4 * i], p.bboxes_f[4 * i + 1],
+                                      p.bboxes_f[4 * i + 2], p.bboxes_f[4 * i + 3], p.osf, x, y, r);
+                } else {
+                    x = p.centers[2 * i];
+                    y = p.centers[2 * i + 1];
+                    r = p.radii[i];
+                }
+            } else if constexpr (SRC == SRC_CSR) {
+                const long long i = p.csr_items[src_base + t];
+                x = p.centers[2 * i];
+                y = p.centers[2 * i + 1];
+                r = p.radii[i];
+            } else {
+                const int pi = p.plane_idx[t];
+                if ((long long)pi != plane) {
+                    if (cnt && p.status && (pi < 0 || (long long)pi >= p.num_planes))
+                        atomicAdd(&p.status->skipped_plane, 1u);
+                    return false;
+                }
+                x = p.centers[2 * (long long)t];
+                y = p.centers[2 * (long long)t + 1];
+                r = p.radii[t];
+            }
+            return make_obj(x, y, r, p.factor, kneg, ry0, ry1, rx0, rx1, o, p.status, cnt);
+        };
+
+        // ---- K2a: unit list (ballot + prefix compaction) --------------------------------------
+        __syncthreads();  // previous unit is completely done with the shared lists
+        if (tid == 0) s_cnt[0] = 0;
+        __syncthreads();
+        for (int base = 0; base < n; base += kThreads) {
+            const int t = base + tid;
+            Obj o;
+            bool pred = false;
+            if (t < n) pred = load_obj(t, uy0, uy1, ucu0 * PX, ucu1 * PX, count_skips, o);
+            compact_push(pred, o, s_unit, &s_cnt[0]);
+        }
+        __syncthreads();
+        const int ucnt = s_cnt[0];
+
+        if (ucnt == 0) {
+            if constexpr (!ACCUM) zero_rect<PX>(plane_ptr, p.W, p.wunits, uy0, uy1, ucu0, ucu1);
+            continue;
+        }
+        const bool unit_list_ok = ucnt <= kListCap;
+
+        // ---- bands of the unit ----------------------------------------------------------------
+        for (int b = b0; b < b1; ++b) {
+            int by0, by1, cu0, cu1;
+            if (p.bands_x == 1) {
+                by0 = b * p.band_rows;
+                by1 = min(by0 + p.band_rows, p.H);
+                cu0 = 0;
+                cu1 = p.wunits;
+            } else {
+                by0 = uy0; by1 = uy1; cu0 = ucu0; cu1 = ucu1;
+            }
+            const int cw = cu1 - cu0;
+            const int nitems = (by1 - by0) * cw;
+
+            float acc[kItemsPerThread][PX];
+            float frow[kItemsPerThread], fcol[kItemsPerThread];
+            bool coords_ready = false;
+
+            // Passes: one pass over the unit list, or (overflow) chunks of the global source.
+            const int npass = unit_list_ok ? 1 : (n + kListCap - 1) / kListCap;
+            bool any = false;
+            for (int pass = 0; pass < npass; ++pass) {
+                // ---- K2b: band list ------------------------------------------------------------
+                __syncthreads();  // previous pass / band finished reading s_band
+                if (tid == 0) s_cnt[1] = 0;
+                __syncthreads();
+                if (unit_list_ok) {
+                    const float fy0 = (float)by0, fy1 = (float)by1, fx0 = (float)(cu0 * PX), fx1 = (float)(cu1 * PX);
+                    for (int base = 0; base < ucnt; base += kThreads) {
+                        const int e = base + tid;
+                        Obj o;
+                        bool pred = false;
+                        if (e < ucnt) {
+                            o = s_unit[e];
+                            pred = (o.fy + o.fr >= fy0) && (o.fy - o.fr < fy1) && (o.fx + o.fr >= fx0) && (o.fx - o.fr < fx1);
+                        }
+                        compact_push(pred, o, s_band, &s_cnt[1]);
+                    }
+                } else {
+                    const int c0 = pass * kListCap, c1 = min(n, c0 + kListCap);
+                    for (int base = c0; base < c1; base += kThreads) {
+                        const int t = base + tid;
+                        Obj o;
+                        bool pred = false;
+                        if (t < c1) pred = load_obj(t, by0, by1, cu0 * PX, cu1 * PX, false, o);
+                        compact_push(pred, o, s_band, &s_cnt[1]);
+                    }
+                }
+                __syncthreads();
+                const int bcnt = s_cnt[1];
+                if (bcnt == 0) continue;
+                any = true;
+
+                if (!coords_ready) {
+                    coords_ready = true;
+                    int q = tid / cw, r = tid - q * cw;
+                    const int dq = kThreads / cw, dr = kThreads - dq * cw;
+#pragma unroll
+                    for (int k = 0; k < kItemsPerThread; ++k) {
+                        const bool valid = (k * kThreads + tid) < nitems;
+                        frow[k] = valid ? (float)(by0 + q) : 3.0e38f;  // invalid items never pass the row test
+                        fcol[k] = (float)((cu0 + r) * PX);
+#pragma unroll
+                        for (int j = 0; j < PX; ++j) acc[k][j] = NEG_INF;
+                        q += dq;
+                        r += dr;
+                        if (r >= cw) { r -= cw; q += 1; }
+                    }
+                }
+
+                // ---- K3: max-blend in registers ------------------------------------------------
+                for (int e = 0; e < bcnt; ++e) {
+                    const Obj o = s_band[e];  // broadcast LDS.128
+#pragma unroll
+                    for (int k = 0; k < kItemsPerThread; ++k) {
+                        const float dy = frow[k] - o.fy;
+                        if (fabsf(dy) <= o.fr) {
+                            const float dx0 = fcol[k] - o.fx;
+                            if (dx0 <= o.fr && dx0 + (float)(PX - 1) >= -o.fr) {
+                                const float fi = __fmul_rn(dy, dy);
+#pragma unroll
+                                for (int j = 0; j < PX; ++j) {
+                                    const float dx = dx0 + (float)j;
+                                    const float t = __fmul_rn(__fadd_rn(fi, __fmul_rn(dx, dx)), o.wv);
+                                    acc[k][j] = (fabsf(dx) <= o.fr) ? fmaxf(acc[k][j], t) : acc[k][j];
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+
+            // ---- K4: write --------------------------------------------------------------------
+            if (!any) {
+                if constexpr (!ACCUM) zero_rect<PX>(plane_ptr, p.W, p.wunits, by0, by1, cu0, cu1);
+                continue;
+            }
+#pragma unroll
+            for (int k = 0; k < kItemsPerThread; ++k) {
+                if ((k * kThreads + tid) < nitems) {
+                    float* dst = plane_ptr + (long long)((int)frow[k]) * p.W + (int)fcol[k];
+                    float v[PX];
+                    bool touched[PX];
+                    bool any_t = false;
+#pragma unroll
+                    for (int j = 0; j < PX; ++j) {
+                        const float m = acc[k][j];
+                        touched[j] = m > NEG_INF;
+                        any_t |= touched[j];
+                        v[j] = 0.0f;
+                        if (touched[j]) v[j] = __fmul_rn(expf(kneg ? -m : m), p.k);
+                    }
+                    if constexpr (ACCUM) {
+                        if (any_t) {
+                            float old[PX];
+                            if constexpr (PX == 4) {
+                                const float4 o4 = *reinterpret_cast<const float4*>(dst);
+                                old[0] = o4.x; old[1] = o4.y; old[2] = o4.z; old[3] = o4.w;
+                            } else {
+                                old[0] = *dst;
+                            }
+#pragma unroll
+                            for (int j = 0; j < PX; ++j)  // cuh:30: keep old iff old >= v
+                                v[j] = touched[j] ? ((old[j] >= v[j]) ? old[j] : v[j]) : old[j];
+                            store_px<PX>(dst, v);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < PX; ++j) v[j] = touched[j] ? ((0.0f >= v[j]) ? 0.0f : v[j]) : 0.0f;
+                        store_px<PX>(dst, v);
+                    }
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Flat API binning: counting sort of objects by plane (match_any-aggregated counters).
+__global__ void __launch_bounds__(256) csr_count_kernel(const int32_t* __restrict__ plane_idx, long long n, long long m,
+                                                        int32_t* __restrict__ counts, dh_status* status) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const int idx = (i < n) ? plane_idx[i] : -1;
+    const bool valid = (i < n) && idx >= 0 && (long long)idx < m;
+    if ((i < n) && !valid && status) atomicAdd(&status->skipped_plane, 1u);
+    const unsigned active = __ballot_sync(0xffffffffu, valid);
+    if (valid) {
+        const unsigned peers = __match_any_sync(active, idx);
+        if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&counts[idx], __popc(peers));
+    }
+}
+
+__global__ void __launch_bounds__(1024) csr_scan_kernel(const int32_t* __restrict__ counts, long long m,
+                                                        int32_t* __restrict__ off) {
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (long long base = 0; base < m; base += 1024) {
+        const long long i = base + tid;
+        const int c = (i < m) ? counts[i] : 0;
+        int incl = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, w, d);
+                if (lane >= d) w += t;
+            }
+            s_warp[lane] = w;  // inclusive warp sums
+        }
+        __syncthreads();
+        const int carry = s_carry;
+        const int wprefix = (warp == 0) ? 0 : s_warp[warp - 1];
+        if (i < m) off[i] = carry + wprefix + incl - c;
+        __syncthreads();
+        if (tid == 1023) s_carry = carry + wprefix + incl;
+        __syncthreads();
+    }
+    if (tid == 0) off[m] = s_carry;
+}
+
+__global__ void __launch_bounds__(256) csr_fill_kernel(const int32_t* __restrict__ plane_idx, long long n, long long m,
+                                                       const int32_t* __restrict__ off, int32_t* __restrict__ cursor,
+                                                       int32_t* __restrict__ items) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const int idx = (i < n) ? plane_idx[i] : -1;
+    const bool valid = (i < n) && idx >= 0 && (long long)idx < m;
+    const unsigned active = __ballot_sync(0xffffffffu, valid);
+    if (valid) {
+        const int lane = threadIdx.x & 31;
+        const unsigned peers = __match_any_sync(active, idx);
+        const int leader = __ffs(peers) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(&cursor[idx], __popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        items[off[idx] + base + __popc(peers & ((1u << lane) - 1u))] = (int32_t)i;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Write-only ceiling probe: same store instruction and grid shape as the FRESH renderer.
+__global__ void __launch_bounds__(kThreads) fill_probe_kernel(float4* __restrict__ dst, long long n4, long long chunk4) {
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    const long long nchunks = (n4 + chunk4 - 1) / chunk4;
+    for (long long c = blockIdx.x; c < nchunks; c += gridDim.x) {
+        float4* p = dst + c * chunk4;
+        const int n = (int)min(chunk4, n4 - c * chunk4);
+#pragma unroll 4
+        for (int i = threadIdx.x; i < n; i += kThreads) p[i] = z;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host side
+std::atomic<uint64_t> g_launches{0};
+
+struct DeviceInfo {
+    int sms = 0;
+};
+
+static int device_info(DeviceInfo& di) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    static int cached_sms[64] = {0};
+    if (dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
+    if (cached_sms[dev] == 0) {
+        int sms = 0;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return (int)e;
+        cached_sms[dev] = sms;
+    }
+    di.sms = cached_sms[dev];
+    return DH_OK;
+}
+
+template <typename K>
+static int blocks_per_sm(K kernel, int& cached) {
+    if (cached == 0) {
+        int nb = 0;
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kThreads, 0);
+        if (e != cudaSuccess) return (int)e;
+        cached = nb > 0 ? nb : 1;
+    }
+    return DH_OK;
+}
+
+static int check_shape(int64_t H, int64_t W) {
+    if (H < 1 || W < 1) return DH_ERR_INVALID_ARGUMENT;
+    if (W > (1ll << 23) || H > (1ll << 23) || H * W >= (1ll << 31)) return DH_ERR_UNSUPPORTED_SHAPE;
+    return DH_OK;
+}
+
+// Partition planes into bands (<= kBandCap items) and units (groups of bands of one plane).
+static void make_plan(RenderParams& p, int px, long long max_ctas) {
+    p.wunits = p.W / px;
+    if (p.wunits <= kBandCap) {
+        const int max_rows = kBandCap / p.wunits;
+        const long long total_items = p.num_planes * (long long)p.H * p.wunits;
+        long long want = total_items / (2 * max_ctas);  // >= 2 bands per resident CTA on small problems
+        if (want < kThreads) want = kThreads;
+        if (want > kBandCap) want = kBandCap;
+        long long rows = want / p.wunits;
+        if (rows < 1) rows = 1;
+        if (rows > max_rows) rows = max_rows;
+        if (rows > p.H) rows = p.H;
+        p.bands_x = 1;
+        p.bands_y = (int)((p.H + rows - 1) / rows);
+        p.band_rows = (int)((p.H + p.bands_y - 1) / p.bands_y);  // balance the last band
+        p.bands_y = (p.H + p.band_rows - 1) / p.band_rows;
+        p.band_cols = p.wunits;
+        p.bands_per_plane = p.bands_y;
+        const long long total_bands = p.num_planes * p.bands_y;
+        long long bpu = total_bands / (8 * max_ctas);
+        if (bpu < 1) bpu = 1;
+        if (bpu > p.bands_y) bpu = p.bands_y;
+        p.bands_per_unit = (int)bpu;
+        p.units_per_plane = (p.bands_y + p.bands_per_unit - 1) / p.bands_per_unit;
+    } else {  // a single row does not fit a band: split rows into column segments
+        p.band_rows = 1;
+        p.band_cols = kBandCap;
+        p.bands_x = (p.wunits + kBandCap - 1) / kBandCap;
+        p.bands_y = p.H;
+        p.bands_per_plane = p.bands_x * p.bands_y;
+        p.bands_per_unit = 1;
+        p.units_per_plane = p.bands_per_plane;
+    }
+    p.total_units = p.num_planes * p.units_per_plane;
+}
+
+template <int SRC>
+static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
+    DeviceInfo di;
+    int st = device_info(di);
+    if (st != DH_OK) return st;
+    const bool vec = (p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0);
+    const bool accum = (mode == DH_MODE_ACCUMULATE);
+    static int occ[2][2] = {{0, 0}, {0, 0}};
+    int& o = occ[vec][accum];
+    if (vec && accum) st = blocks_per_sm(render_kernel<4, true, SRC>, o);
+    else if (vec) st = blocks_per_sm(render_kernel<4, false, SRC>, o);
+    else if (accum) st = blocks_per_sm(render_kernel<1, true, SRC>, o);
+    else st = blocks_per_sm(render_kernel<1, false, SRC>, o);
+    if (st != DH_OK) return st;
+    const long long max_ctas = (long long)di.sms * o;
+    make_plan(p, vec ? 4 : 1, max_ctas);
+    if (p.total_units == 0) return DH_OK;
+    const int grid = (int)(p.total_units < max_ctas ? p.total_units : max_ctas);
+    if (vec && accum) render_kernel<4, true, SRC><<<grid, kThreads, 0, stream>>>(p);
+    else if (vec) render_kernel<4, false, SRC><<<grid, kThreads, 0, stream>>>(p);
+    else if (accum) render_kernel<1, true, SRC><<<grid, kThreads, 0, stream>>>(p);
+    else render_kernel<1, false, SRC><<<grid, kThreads, 0, stream>>>(p);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace dh
+
+// ================================================================================================
+extern "C" {
+
+int dh_version(void) { return DH_B200_VERSION; }
+
+const char* dh_build_info(void) {
+    return "dh_b200 0.1.0 | nvcc " DH_STR(__CUDACC_VER_MAJOR__) "." DH_STR(__CUDACC_VER_MINOR__)
+           " | -gencode arch=compute_100a,code=sm_100a | fp32 IEEE (no fast-math) | no CPU fallback";
+}
+
+const char* dh_status_string(int status) {
+    switch (status) {
+        case DH_OK: return "ok";
+        case DH_ERR_INVALID_ARGUMENT: return "invalid argument";
+        case DH_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
+        case DH_ERR_UNSUPPORTED_SHAPE: return "unsupported shape (need 1 <= H,W <= 2^23 and H*W < 2^31)";
+        case DH_ERR_NO_DEVICE: return "no usable CUDA device";
+        default: break;
+    }
+    if (status > 0) return cudaGetErrorString((cudaError_t)status);
+    return "unknown status";
+}
+
+uint64_t dh_launch_count(void) { return dh::g_launches.load(std::memory_order_relaxed); }
+
+int dh_radius_center(void* stream, const float* centers_xy, const float* bboxes_xyxy, float out_size_factor, int64_t n,
+                     int32_t* centers_out, int32_t* radii_out) {
+    if (n < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (n == 0) return DH_OK;
+    if (!centers_xy || !bboxes_xyxy || !centers_out || !radii_out) return DH_ERR_INVALID_ARGUMENT;
+    dh::DeviceInfo di;
+    int st = dh::device_info(di);
+    if (st != DH_OK) return st;
+    long long blocks = (n + 255) / 256;
+    const long long cap = (long long)di.sms * 8;
+    if (blocks > cap) blocks = cap;
+    dh::radius_center_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(centers_xy, bboxes_xyxy, out_size_factor, n,
+                                                                           centers_out, radii_out);
+    dh::g_launches.fetch_add(1, std::memory_order_relaxed);
+    return (int)cudaGetLastError();
+}
+
+static int batched_common(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
+                          const float* centers_f, const float* bboxes_f, float osf, const void* nums_targets,
+                          int nums_dtype, const int32_t* labels, int64_t B, int64_t T, int64_t C, int64_t H, int64_t W,
+                          float factor, float k, int mode, dh_status* status) {
+    if (B < 0 || T < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (mode != DH_MODE_ACCUMULATE && mode != DH_MODE_FRESH) return DH_ERR_INVALID_ARGUMENT;
+    if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
+    if (labels == nullptr) C = 1;
+    if (C < 0 || C > INT32_MAX) return DH_ERR_INVALID_ARGUMENT;
+    if (C == 0) return DH_OK;  // [B,0,H,W]: nothing to draw into
+    int st = dh::check_shape(H, W);
+    if (st != DH_OK) return st;
+    if (B == 0) return DH_OK;
+    if (T > INT32_MAX) return DH_ERR_UNSUPPORTED_SHAPE;
+    if (!heatmap || !nums_targets) return DH_ERR_INVALID_ARGUMENT;
+    if (T > 0 && ((centers_f == nullptr) ? (!centers || !radii) : (!bboxes_f))) return DH_ERR_INVALID_ARGUMENT;
+    dh::RenderParams p{};
+    p.heat = heatmap;
+    p.centers = centers;
+    p.radii = radii;
+    p.centers_f = centers_f;
+    p.bboxes_f = bboxes_f;
+    p.osf = osf;
+    p.labels = labels;
+    p.sizes = nums_targets;
+    p.sizes_i64 = (nums_dtype == DH_SIZES_I64);
+    p.num_planes = B * C;
+    p.C = (int)C;
+    p.T = (int)T;
+    p.H = (int)H;
+    p.W = (int)W;
+    p.factor = factor;
+    p.k = k;
+    p.status = status;
+    if (centers_f) return dh::launch_render<dh::SRC_BOXES>((cudaStream_t)stream, p, mode);
+    return dh::launch_render<dh::SRC_BATCHED>((cudaStream_t)stream, p, mode);
+}
+
+int dh_draw_heatmap_batched(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
+                            const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t batch_size,
+                            int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
+                            float diameter_to_sigma_factor, float k_scale, int mode, dh_status* status) {
+    return batched_common(stream, heatmap, centers, radii, nullptr, nullptr, 1.0f, nums_targets, nums_dtype, labels,
+                          batch_size, max_num_targets, num_classes, height, width, diameter_to_sigma_factor, k_scale,
+                          mode, status);
+}
+
+int dh_draw_heatmap_batched_from_boxes(void* stream, float* heatmap, const float* centers_xy, const float* bboxes_xyxy,
+                                       float out_size_factor, const void* nums_targets, int nums_dtype,
+                                       const int32_t* labels, int64_t batch_size, int64_t max_num_targets,
+                                       int64_t num_classes, int64_t height, int64_t width,
+                                       float diameter_to_sigma_factor, float k_scale, int mode, int32_t* centers_out,
+                                       int32_t* radii_out, dh_status* status) {
+    if ((centers_out == nullptr) != (radii_out == nullptr)) return DH_ERR_INVALID_ARGUMENT;
+    if (batch_size > 0 && max_num_targets > 0 && (!centers_xy || !bboxes_xyxy)) return DH_ERR_INVALID_ARGUMENT;
+    if (centers_out != nullptr) {  // integer outputs requested: K1 then the integer-input renderer
+        int st = dh_radius_center(stream, centers_xy, bboxes_xyxy, out_size_factor, batch_size * max_num_targets,
+                                  centers_out, radii_out);
+        if (st != DH_OK) return st;
+        return batched_common(stream, heatmap, centers_out, radii_out, nullptr, nullptr, 1.0f, nums_targets, nums_dtype,
+                              labels, batch_size, max_num_targets, num_classes, height, width,
+                              diameter_to_sigma_factor, k_scale, mode, status);
+    }
+    return batched_common(stream, heatmap, nullptr, nullptr, centers_xy, bboxes_xyxy, out_size_factor, nums_targets,
+                          nums_dtype, labels, batch_size, max_num_targets, num_classes, height, width,
+                          diameter_to_sigma_factor, k_scale, mode, status);
+}
+
+// Flat path: direct scan when (units x objects) is small, else counting sort by plane.
+static const long long kFlatScanBudget = 1ll << 22;
+
+static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+
+size_t dh_draw_heatmap_workspace_bytes(int64_t num_targets, int64_t num_heatmaps) {
+    if (num_targets < 0 || num_heatmaps < 0) return 0;
+    // counts[M] | cursor[M] | off[M+1] | items[N]
+    return align16((size_t)num_heatmaps * 4 * 2) + align16(((size_t)num_heatmaps + 1) * 4) +
+           align16((size_t)num_targets * 4) + 16;
+}
+
+int dh_draw_heatmap(void* stream_, float* heatmaps, const int32_t* centers, const int32_t* radii,
+                    const int32_t* heatmap_idxes, int64_t N, int64_t M, int64_t H, int64_t W, float factor, float k,
+                    int mode, void* workspace, size_t workspace_bytes, dh_status* status) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (N < 0 || M < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (mode != DH_MODE_ACCUMULATE && mode != DH_MODE_FRESH) return DH_ERR_INVALID_ARGUMENT;
+    int st = dh::check_shape(H, W);
+    if (st != DH_OK) return st;
+    if (M == 0) return DH_OK;
+    if (N > INT32_MAX || M > INT32_MAX) return DH_ERR_UNSUPPORTED_SHAPE;
+    if (!heatmaps) return DH_ERR_INVALID_ARGUMENT;
+    if (N > 0 && (!centers || !radii || !heatmap_idxes)) return DH_ERR_INVALID_ARGUMENT;
+    if (N == 0 && mode == DH_MODE_ACCUMULATE) return DH_OK;
+
+    dh::RenderParams p{};
+    p.heat = heatmaps;
+    p.centers = centers;
+    p.radii = radii;
+    p.plane_idx = heatmap_idxes;
+    p.num_objects = N;
+    p.num_planes = M;
+    p.C = 1;
+    p.T = 0;
+    p.H = (int)H;
+    p.W = (int)W;
+    p.factor = factor;
+    p.k = k;
+    p.status = status;
+
+    // Rough unit count (upper bound: one band per unit) to choose the binning strategy.
+    const long long approx_units = M * (((long long)H * W / 4 + dh::kBandCap - 1) / dh::kBandCap);
+    if (approx_units * N <= kFlatScanBudget) return dh::launch_render<dh::SRC_FLATSCAN>(stream, p, mode);
+
+    if (workspace == nullptr || workspace_bytes < dh_draw_heatmap_workspace_bytes(N, M)) return DH_ERR_WORKSPACE_TOO_SMALL;
+    if (reinterpret_cast<uintptr_t>(workspace) & 15u) return DH_ERR_INVALID_ARGUMENT;
+    char* ws = (char*)workspace;
+    int32_t* counts = (int32_t*)ws;
+    int32_t* cursor = counts + M;
+    ws += align16((size_t)M * 8);
+    int32_t* off = (int32_t*)ws;
+    ws += align16(((size_t)M + 1) * 4);
+    int32_t* items = (int32_t*)ws;
+    cudaError_t e = cudaMemsetAsync(counts, 0, (size_t)M * 8, stream);
+    if (e != cudaSuccess) return (int)e;
+    const int nb = (int)((N + 255) / 256);
+    dh::csr_count_kernel<<<nb, 256, 0, stream>>>(heatmap_idxes, N, M, counts, status);
+    dh::csr_scan_kernel<<<1, 1024, 0, stream>>>(counts, M, off);
+    dh::csr_fill_kernel<<<nb, 256, 0, stream>>>(heatmap_idxes, N, M, off, cursor, items);
+    dh::g_launches.fetch_add(3, std::memory_order_relaxed);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    p.csr_off = off;
+    p.csr_items = items;
+    return dh::launch_render<dh::SRC_CSR>(stream, p, mode);
+}
+
+int dh_fill_probe(void* stream, void* dst, size_t bytes) {
+    if (bytes == 0) return DH_OK;
+    if (!dst || (bytes & 15u) || (reinterpret_cast<uintptr_t>(dst) & 15u)) return DH_ERR_INVALID_ARGUMENT;
+    dh::DeviceInfo di;
+    int st = dh::device_info(di);
+    if (st != DH_OK) return st;
+    const long long n4 = (long long)(bytes / 16);
+    const long long chunk4 = dh::kBandCap;
+    const long long nchunks = (n4 + chunk4 - 1) / chunk4;
+    const long long cap = (long long)di.sms * 8;
+    dh::fill_probe_kernel<<<(int)(nchunks < cap ? nchunks : cap), dh::kThreads, 0, (cudaStream_t)stream>>>(
+        (float4*)dst, n4, chunk4);
+    dh::g_launches.fetch_add(1, std::memory_order_relaxed);
+    return (int)cudaGetLastError();
+}
+
+}  // extern "C"

@@ -1,0 +1,259 @@
+// dh_torch_binding.cpp — thin ATen/pybind layer over the C ABI (include/dh_b200.h).
+//
+// Mirrors the reference extension module `accvlab.draw_heatmap.draw_heatmap_ext`
+// (/root/reference/packages/draw_heatmap/accvlab/draw_heatmap/csrc/draw_heatmap.cpp:131-145): same function names,
+// argument names, order and defaults; same host-side validation as draw_heatmap_cuda.cu:62-165 (is_cuda /
+// is_contiguous / shape checks -> RuntimeError), plus explicit dtype checks. Differences, all documented in
+// nums_targets may be int32 OR int64 (no per-call cast); launch failures raise instead of printf.
+// Everything named *_b200 / radius_center / render_* is an addition (FRESH mode, fused K1), not in the reference.
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <torch/extension.h>
+
+#include <tuple>
+
+#include "dh_b200.h"
+
+namespace {
+
+#define CHECK_CUDA(x) TORCH_CHECK(x.is_cuda(), #x " must be a CUDA tensor")
+#define CHECK_CONTIGUOUS(x) TORCH_CHECK(x.is_contiguous(), #x " must be contiguous")
+#define CHECK_INPUT(x) \
+    CHECK_CUDA(x);     \
+    CHECK_CONTIGUOUS(x)
+#define CHECK_DTYPE(x, dt) TORCH_CHECK(x.scalar_type() == dt, #x " must have dtype " #dt ", got ", x.scalar_type())
+#define CHECK_SAME_DEVICE(x, ref) TORCH_CHECK(x.device() == ref.device(), #x " must be on the same device as " #ref)
+
+void check_status(int st, const char* what) {
+    TORCH_CHECK(st == DH_OK, what, " failed: ", dh_status_string(st), " (status ", st, ")");
+}
+
+const void* sizes_ptr(const at::Tensor& nums_targets, int& tag) {
+    TORCH_CHECK(nums_targets.scalar_type() == at::kInt || nums_targets.scalar_type() == at::kLong,
+                "nums_targets must have dtype int32 or int64, got ", nums_targets.scalar_type());
+    tag = nums_targets.scalar_type() == at::kLong ? DH_SIZES_I64 : DH_SIZES_I32;
+    return nums_targets.data_ptr();
+}
+
+// ---- flat entry (draw_heatmap_cuda.cu:62-89) ---------------------------------------------------------------
+void draw_heatmap_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tensor& radii,
+                       const at::Tensor& heatmap_idxes, float diameter_to_sigma_factor, float k_scale, int mode) {
+    CHECK_INPUT(heatmap);
+    CHECK_INPUT(centers);
+    CHECK_INPUT(radii);
+    CHECK_INPUT(heatmap_idxes);
+    c10::cuda::CUDAGuard guard(heatmap.device());
+    auto stream = at::cuda::getCurrentCUDAStream();
+    TORCH_CHECK(centers.size(0) == radii.size(0), "centers and radii must have the same size at dim0");
+    TORCH_CHECK(centers.size(0) == heatmap_idxes.size(0), "centers and heatmap_idxes must have the same size at dim0");
+    TORCH_CHECK(heatmap.dim() == 3, "heatmap must be of shape [num_heatmaps, height, width]");
+    TORCH_CHECK(centers.dim() == 2 && centers.size(1) == 2, "centers must be of shape [num_targets, 2]");
+    TORCH_CHECK(radii.dim() == 1 && heatmap_idxes.dim() == 1, "radii and heatmap_idxes must be of shape [num_targets]");
+    CHECK_DTYPE(heatmap, at::kFloat);
+    CHECK_DTYPE(centers, at::kInt);
+    CHECK_DTYPE(radii, at::kInt);
+    CHECK_DTYPE(heatmap_idxes, at::kInt);
+    CHECK_SAME_DEVICE(centers, heatmap);
+    CHECK_SAME_DEVICE(radii, heatmap);
+    CHECK_SAME_DEVICE(heatmap_idxes, heatmap);
+    const int64_t n = centers.size(0), m = heatmap.size(0);
+    const size_t ws_bytes = dh_draw_heatmap_workspace_bytes(n, m);
+    at::Tensor ws = at::empty({(int64_t)ws_bytes}, heatmap.options().dtype(at::kByte));
+    check_status(dh_draw_heatmap(stream.stream(), heatmap.data_ptr<float>(), centers.data_ptr<int>(), radii.data_ptr<int>(),
+                                 heatmap_idxes.data_ptr<int>(), n, m, heatmap.size(1), heatmap.size(2),
+                                 diameter_to_sigma_factor, k_scale, mode, ws.data_ptr(), ws_bytes, nullptr),
+                 "draw_heatmap");
+}
+
+void draw_heatmap(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
+                  const at::Tensor& heatmap_idxes, float diameter_to_sigma_factor, float k_scale) {
+    draw_heatmap_mode(heatmaps, centers, radii, heatmap_idxes, diameter_to_sigma_factor, k_scale, DH_MODE_ACCUMULATE);
+}
+
+// ---- batched entries (draw_heatmap_cuda.cu:91-165) ---------------------------------------------------------
+void batched_checks(const at::Tensor& heatmap, const at::Tensor& centers, const at::Tensor& radii,
+                    const at::Tensor& nums_targets, const at::Tensor* labels) {
+    CHECK_INPUT(heatmap);
+    CHECK_INPUT(centers);
+    CHECK_INPUT(radii);
+    CHECK_INPUT(nums_targets);
+    TORCH_CHECK(radii.dim() == 2, "radii must be of shape [batch_size, num_targets]");
+    TORCH_CHECK(centers.dim() == 3 && centers.size(2) == 2, "centers must be of shape [batch_size, num_targets, 2]");
+    const int64_t batch_size = heatmap.size(0);
+    const int64_t num_targets = radii.size(1);
+    TORCH_CHECK(nums_targets.dim() == 1, "nums_targets must be of shape [batch_size]");
+    TORCH_CHECK(batch_size == radii.size(0) && batch_size == centers.size(0) && batch_size == nums_targets.size(0),
+                "batch_size (dim 0) need to be the same for all inputs");
+    TORCH_CHECK(num_targets == centers.size(1), "maximum number of targets (dim 1) need to be the same centers and radii");
+    if (labels == nullptr) {
+        TORCH_CHECK(heatmap.dim() == 3, "heatmap must be of shape [batch_size, height, width]");
+    } else {
+        const at::Tensor& labels_ = *labels;
+        CHECK_INPUT(labels_);
+        TORCH_CHECK(heatmap.dim() == 4, "heatmap must be of shape [batch_size, max_num_classes, height, width]");
+        TORCH_CHECK(labels_.dim() == 2, "labels must be of shape [batch_size, radii.size(1)]");
+        TORCH_CHECK(labels_.size(0) == batch_size && labels_.size(1) == num_targets,
+                    "labels shape must be [batch_size, radii.size(1)]");
+        CHECK_DTYPE(labels_, at::kInt);
+        CHECK_SAME_DEVICE(labels_, heatmap);
+    }
+    CHECK_DTYPE(heatmap, at::kFloat);
+    CHECK_SAME_DEVICE(centers, heatmap);
+    CHECK_SAME_DEVICE(radii, heatmap);
+    CHECK_SAME_DEVICE(nums_targets, heatmap);
+}
+
+void batched_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tensor& radii, const at::Tensor& nums_targets,
+                  const at::Tensor* labels, float factor, float k, int mode) {
+    batched_checks(heatmap, centers, radii, nums_targets, labels);
+    CHECK_DTYPE(centers, at::kInt);
+    CHECK_DTYPE(radii, at::kInt);
+    c10::cuda::CUDAGuard guard(heatmap.device());
+    auto stream = at::cuda::getCurrentCUDAStream();
+    int tag = 0;
+    const void* sizes = sizes_ptr(nums_targets, tag);
+    const bool cw = labels != nullptr;
+    check_status(dh_draw_heatmap_batched(stream.stream(), heatmap.data_ptr<float>(), centers.data_ptr<int>(),
+                                         radii.data_ptr<int>(), sizes, tag, cw ? labels->data_ptr<int>() : nullptr,
+                                         heatmap.size(0), radii.size(1), cw ? heatmap.size(1) : 1,
+                                         heatmap.size(cw ? 2 : 1), heatmap.size(cw ? 3 : 2), factor, k, mode, nullptr),
+                 "draw_heatmap_batched");
+}
+
+void draw_heatmap_batched(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
+                          const at::Tensor& nums_targets, float diameter_to_sigma_factor, float k_scale) {
+    batched_mode(heatmaps, centers, radii, nums_targets, nullptr, diameter_to_sigma_factor, k_scale, DH_MODE_ACCUMULATE);
+}
+
+void draw_heatmap_batched_classwise(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
+                                    const at::Tensor& nums_targets, const at::Tensor& labels,
+                                    float diameter_to_sigma_factor, float k_scale) {
+    batched_mode(heatmaps, centers, radii, nums_targets, &labels, diameter_to_sigma_factor, k_scale, DH_MODE_ACCUMULATE);
+}
+
+// ---- additions -----------------------------------------------------------------------------------------------
+void render_heatmap_batched(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
+                            const at::Tensor& nums_targets, const c10::optional<at::Tensor>& labels,
+                            float diameter_to_sigma_factor, float k_scale, bool fresh) {
+    batched_mode(heatmaps, centers, radii, nums_targets, labels.has_value() ? &labels.value() : nullptr,
+                 diameter_to_sigma_factor, k_scale, fresh ? DH_MODE_FRESH : DH_MODE_ACCUMULATE);
+}
+
+void render_heatmap_flat(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
+                         const at::Tensor& heatmap_idxes, float diameter_to_sigma_factor, float k_scale, bool fresh) {
+    draw_heatmap_mode(heatmaps, centers, radii, heatmap_idxes, diameter_to_sigma_factor, k_scale,
+                      fresh ? DH_MODE_FRESH : DH_MODE_ACCUMULATE);
+}
+
+std::tuple<at::Tensor, at::Tensor> radius_center(const at::Tensor& centers, const at::Tensor& bboxes,
+                                                 double out_size_factor) {
+    CHECK_INPUT(centers);
+    CHECK_INPUT(bboxes);
+    CHECK_DTYPE(centers, at::kFloat);
+    CHECK_DTYPE(bboxes, at::kFloat);
+    CHECK_SAME_DEVICE(bboxes, centers);
+    TORCH_CHECK(centers.dim() >= 1 && centers.size(-1) == 2, "centers must be of shape [..., 2]");
+    TORCH_CHECK(bboxes.dim() == centers.dim() && bboxes.size(-1) == 4, "bboxes must be of shape [..., 4]");
+    for (int64_t d = 0; d + 1 < centers.dim(); ++d)
+        TORCH_CHECK(centers.size(d) == bboxes.size(d), "centers and bboxes must agree in all leading dimensions");
+    c10::cuda::CUDAGuard guard(centers.device());
+    auto stream = at::cuda::getCurrentCUDAStream();
+    at::Tensor centers_out = at::empty(centers.sizes(), centers.options().dtype(at::kInt));
+    auto lead = centers.sizes().vec();
+    lead.pop_back();
+    at::Tensor radii_out = at::empty(lead, centers.options().dtype(at::kInt));
+    check_status(dh_radius_center(stream.stream(), centers.data_ptr<float>(), bboxes.data_ptr<float>(),
+                                  (float)out_size_factor, radii_out.numel(), centers_out.data_ptr<int>(),
+                                  radii_out.data_ptr<int>()),
+                 "radius_center");
+    return {centers_out, radii_out};
+}
+
+void render_heatmap_from_boxes(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& bboxes,
+                               double out_size_factor, const at::Tensor& nums_targets,
+                               const c10::optional<at::Tensor>& labels, float diameter_to_sigma_factor, float k_scale,
+                               bool fresh) {
+    CHECK_INPUT(bboxes);
+    CHECK_DTYPE(centers, at::kFloat);
+    CHECK_DTYPE(bboxes, at::kFloat);
+    TORCH_CHECK(bboxes.dim() == 3 && bboxes.size(2) == 4, "bboxes must be of shape [batch_size, num_targets, 4]");
+    CHECK_SAME_DEVICE(bboxes, heatmaps);
+    TORCH_CHECK(centers.dim() == 3 && centers.size(2) == 2, "centers must be of shape [batch_size, num_targets, 2]");
+    TORCH_CHECK(centers.size(0) == bboxes.size(0) && centers.size(1) == bboxes.size(1),
+                "centers and bboxes must agree in batch_size and num_targets");
+    const at::Tensor* lab = labels.has_value() ? &labels.value() : nullptr;
+    CHECK_INPUT(heatmaps);
+    CHECK_INPUT(centers);
+    CHECK_INPUT(nums_targets);
+    CHECK_DTYPE(heatmaps, at::kFloat);
+    TORCH_CHECK(nums_targets.dim() == 1 && nums_targets.size(0) == heatmaps.size(0) && centers.size(0) == heatmaps.size(0),
+                "batch_size (dim 0) need to be the same for all inputs");
+    CHECK_SAME_DEVICE(centers, heatmaps);
+    CHECK_SAME_DEVICE(nums_targets, heatmaps);
+    const bool cw = lab != nullptr;
+    if (cw) {
+        const at::Tensor& labels_ = *lab;
+        CHECK_INPUT(labels_);
+        CHECK_DTYPE(labels_, at::kInt);
+        CHECK_SAME_DEVICE(labels_, heatmaps);
+        TORCH_CHECK(heatmaps.dim() == 4, "heatmap must be of shape [batch_size, max_num_classes, height, width]");
+        TORCH_CHECK(labels_.dim() == 2 && labels_.size(0) == centers.size(0) && labels_.size(1) == centers.size(1),
+                    "labels shape must be [batch_size, num_targets]");
+    } else {
+        TORCH_CHECK(heatmaps.dim() == 3, "heatmap must be of shape [batch_size, height, width]");
+    }
+    c10::cuda::CUDAGuard guard(heatmaps.device());
+    auto stream = at::cuda::getCurrentCUDAStream();
+    int tag = 0;
+    const void* sizes = sizes_ptr(nums_targets, tag);
+    check_status(dh_draw_heatmap_batched_from_boxes(
+                     stream.stream(), heatmaps.data_ptr<float>(), centers.data_ptr<float>(), bboxes.data_ptr<float>(),
+                     (float)out_size_factor, sizes, tag, cw ? lab->data_ptr<int>() : nullptr, heatmaps.size(0),
+                     centers.size(1), cw ? heatmaps.size(1) : 1, heatmaps.size(cw ? 2 : 1), heatmaps.size(cw ? 3 : 2),
+                     diameter_to_sigma_factor, k_scale, fresh ? DH_MODE_FRESH : DH_MODE_ACCUMULATE, nullptr, nullptr,
+                     nullptr),
+                 "render_heatmap_from_boxes");
+}
+
+void fill_probe(at::Tensor& t) {
+    CHECK_INPUT(t);
+    c10::cuda::CUDAGuard guard(t.device());
+    check_status(dh_fill_probe(at::cuda::getCurrentCUDAStream().stream(), t.data_ptr(), (size_t)t.nbytes()), "fill_probe");
+}
+
+}  // namespace
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+    m.doc() = "B200-native (sm_100a) Gaussian heatmap drawing; drop-in for accvlab.draw_heatmap.draw_heatmap_ext";
+    // --- the reference's surface (draw_heatmap.cpp:131-145) ---
+    m.def("draw_heatmap", &draw_heatmap, "Draw Gaussians (max-blend, in place) from concatenated objects.",
+          pybind11::arg("heatmaps"), pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("heatmap_idxes"),
+          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f);
+    m.def("draw_heatmap_batched_impl", &draw_heatmap_batched, "Draw Gaussians (max-blend, in place), one plane per sample.",
+          pybind11::arg("heatmaps"), pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"),
+          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f);
+    m.def("draw_heatmap_batched_classwise_impl", &draw_heatmap_batched_classwise,
+          "Draw Gaussians (max-blend, in place), one plane per (sample, class).", pybind11::arg("heatmaps"),
+          pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"), pybind11::arg("labels"),
+          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f);
+    // --- additions ---
+    m.def("render_heatmap_batched", &render_heatmap_batched,
+          "Batched drawing with explicit mode: fresh=True overwrites every pixel (zero-init fused, nothing read).",
+          pybind11::arg("heatmaps"), pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"),
+          pybind11::arg("labels") = pybind11::none(), pybind11::arg("diameter_to_sigma_factor") = 6.f,
+          pybind11::arg("k_scale") = 1.f, pybind11::arg("fresh") = false);
+    m.def("render_heatmap_flat", &render_heatmap_flat, "Flat drawing with explicit mode.", pybind11::arg("heatmaps"),
+          pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("heatmap_idxes"),
+          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f, pybind11::arg("fresh") = false);
+    m.def("radius_center", &radius_center, "bbox -> (int32 centres, int32 radii); tests/_test_helpers.py:20-28 semantics.",
+          pybind11::arg("centers"), pybind11::arg("bboxes"), pybind11::arg("out_size_factor"));
+    m.def("render_heatmap_from_boxes", &render_heatmap_from_boxes,
+          "radius_center fused into the batched renderer (float boxes in, one launch).", pybind11::arg("heatmaps"),
+          pybind11::arg("centers"), pybind11::arg("bboxes"), pybind11::arg("out_size_factor"),
+          pybind11::arg("nums_targets"), pybind11::arg("labels") = pybind11::none(),
+          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f, pybind11::arg("fresh") = false);
+    m.def("fill_probe", &fill_probe, "Zero-fill a tensor with the renderer's store path (write-only ceiling).",
+          pybind11::arg("tensor"));
+    m.def("launch_count", []() { return dh_launch_count(); }, "Kernels launched by this library in this process.");
+    m.def("build_info", []() { return std::string(dh_build_info()); });
+}

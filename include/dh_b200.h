@@ -1,0 +1,151 @@
+/*
+ * dh_b200.h — C ABI of the B200-native (sm_100a) Gaussian heatmap renderer.
+ *
+ * This is the drop-in boundary for ONE hot path of ACCV-Lab: accvlab.draw_heatmap.
+ * Every entry point below replaces a C++-linkage launcher (or a torch-op chain) of the
+ * reference; citations are relative to /root/reference/packages/draw_heatmap ("DH").
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / ATen / C++ types cross this boundary;
+ *   - all data pointers are DEVICE pointers unless the name ends in `_host`;
+ *   - `stream` is a `cudaStream_t` passed as `void*` (NULL = legacy default stream);
+ *   - every call is asynchronous on `stream`, allocates nothing, keeps no state;
+ *   - return value: DH_OK (0), a negative DH_ERR_* code, or a positive `cudaError_t`
+ *     reported by the launch (the reference only printf()s launch errors,
+ *     DH/accvlab/draw_heatmap/csrc/draw_heatmap_cuda.cu:37-40,56-59; we return them);
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails.
+ *
+ * Arithmetic contract (fp32, IEEE round-to-nearest, no fast-math), restating
+ * DH/accvlab/draw_heatmap/include/draw_heatmap_cuda_kernel.cuh:36-49,61-68,90-97:
+ *     d = 2r+1; sigma = (float)d / factor; var = 2.0f*sigma*sigma; vinv = 1.0f/var
+ *     window: rows [y-r, y+r] x cols [x-r, x+r], clipped to the map (square, not a disc)
+ *     v(i,j) = expf(-((float)(i*i) + (float)(j*j)) * vinv) * k_scale
+ *     heat[p][y+i][x+j] = (heat >= v) ? heat : v
+ */
+#ifndef DH_B200_H
+#define DH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DH_B200_VERSION 100 /* 0.1.0 */
+
+/* status codes (negative = ours, positive = cudaError_t) */
+#define DH_OK 0
+#define DH_ERR_INVALID_ARGUMENT (-1)
+#define DH_ERR_WORKSPACE_TOO_SMALL (-2)
+#define DH_ERR_UNSUPPORTED_SHAPE (-3)
+#define DH_ERR_NO_DEVICE (-4)
+
+/* blend mode */
+#define DH_MODE_ACCUMULATE 0 /* reference semantics: max-blend into existing contents (read+write touched pixels) */
+#define DH_MODE_FRESH 1      /* zero-init fused: every pixel of every plane is written exactly once, nothing is read */
+
+/* dtype tag of the per-sample target counts (RaggedBatch.sample_sizes) */
+#define DH_SIZES_I32 0
+#define DH_SIZES_I64 1
+
+/* Limits checked by every entry point (DH_ERR_UNSUPPORTED_SHAPE otherwise):
+ *   1 <= height, width;  height*width < 2^31;  width <= 2^23;
+ *   objects with radius < 0 draw nothing (as in the reference: empty loops);
+ *   objects with radius > DH_MAX_RADIUS are skipped and counted in dh_status.skipped_radius. */
+#define DH_MAX_RADIUS 4194304
+
+/* Optional device-side status record (16 bytes, caller-zeroed, may be NULL).
+ * The reference traps on a bad label with a device assert (cuh:102) and never checks
+ * heatmap_idxes (cuh:59,70 — out-of-bounds write). We never write out of bounds: such
+ * objects are skipped and counted here. */
+typedef struct dh_status {
+    uint32_t skipped_label;  /* label outside [0, num_classes) */
+    uint32_t skipped_plane;  /* heatmap_idx outside [0, num_heatmaps) */
+    uint32_t skipped_radius; /* radius > DH_MAX_RADIUS */
+    uint32_t reserved;
+} dh_status;
+
+/* ---- introspection ------------------------------------------------------------------ */
+int dh_version(void);
+/* static string: compiler, arch (sm_100a), build flags */
+const char* dh_build_info(void);
+/* static string for any value returned by the functions below */
+const char* dh_status_string(int status);
+/* number of kernels launched by calls of this library in the calling process (for bench gpu_launches) */
+uint64_t dh_launch_count(void);
+
+/* ---- K1: bbox -> integer centre + radius ---------------------------------------------
+ * Replaces the torch-op chain get_centers_and_radii (DH/tests/_test_helpers.py:20-28):
+ *     radius = max(1, (int32) ceilf(min(cx-x1, cy-y1, x2-cx, y2-cy) / osf))
+ *     xi = (int32)(cx / osf); yi = (int32)(cy / osf)        (IEEE division, truncation)
+ * centers_xy  f32 [n,2] (x,y);  bboxes_xyxy f32 [n,4] (x1,y1,x2,y2)
+ * centers_out i32 [n,2];        radii_out   i32 [n]
+ * Padded RaggedBatch slots are computed like any other slot (the reference does the same). */
+int dh_radius_center(void* stream, const float* centers_xy, const float* bboxes_xyxy, float out_size_factor,
+                     int64_t n, int32_t* centers_out, int32_t* radii_out);
+
+/* ---- batched entry (RaggedBatch layout) ----------------------------------------------
+ * Replaces draw_heatmap_batched_cuda(cudaStream_t, float*, const int*, const int*, const int*,
+ *   int H, int W, int T, float factor, float k, int B, int C = 0, const int* labels = nullptr)
+ * (DH/accvlab/draw_heatmap/csrc/draw_heatmap_cuda.cu:43-60; kernel cuh:76-109).
+ *   heatmap      f32 [B,H,W] (labels == NULL) or [B,C,H,W] (labels != NULL), contiguous
+ *   centers      i32 [B,T,2] (x,y);  radii i32 [B,T];  labels i32 [B,T] or NULL
+ *   nums_targets [B], int32 or int64 per `nums_dtype`; values are clamped to [0,T]
+ *   num_classes  C; ignored (treated as 1) when labels == NULL
+ *   mode         DH_MODE_ACCUMULATE | DH_MODE_FRESH
+ *   status       optional device dh_status*, may be NULL
+ * Plane offsets are 64-bit (the reference overflows int32 at B*C*H*W >= 2^31, cuh:99-104). */
+int dh_draw_heatmap_batched(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
+                            const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t batch_size,
+                            int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
+                            float diameter_to_sigma_factor, float k_scale, int mode, dh_status* status);
+
+/* K1 fused in: same as dh_radius_center followed by dh_draw_heatmap_batched, one launch.
+ *   centers_xy f32 [B,T,2], bboxes_xyxy f32 [B,T,4]; optional outputs centers_out i32 [B,T,2] and
+ *   radii_out i32 [B,T] (both NULL or both non-NULL; all B*T slots are written, padded ones included). */
+int dh_draw_heatmap_batched_from_boxes(void* stream, float* heatmap, const float* centers_xy,
+                                       const float* bboxes_xyxy, float out_size_factor, const void* nums_targets,
+                                       int nums_dtype, const int32_t* labels, int64_t batch_size,
+                                       int64_t max_num_targets, int64_t num_classes, int64_t height,
+                                       int64_t width, float diameter_to_sigma_factor, float k_scale, int mode,
+                                       int32_t* centers_out, int32_t* radii_out, dh_status* status);
+
+/* ---- flat entry (concatenated objects + per-object plane index) ----------------------
+ * Replaces draw_heatmap_cuda(cudaStream_t, float*, const int*, const int*, const int*, int H, int W,
+ *   float factor, float k, int N, int M) (draw_heatmap_cuda.cu:29-41; kernel cuh:51-74).
+ *   heatmaps f32 [M,H,W]; centers i32 [N,2]; radii i32 [N]; heatmap_idxes i32 [N]
+ *   workspace: device scratch of at least dh_draw_heatmap_workspace_bytes(N, M) bytes, 16-byte aligned,
+ *              used for the object->plane bin lists (counting sort); contents undefined afterwards. */
+size_t dh_draw_heatmap_workspace_bytes(int64_t num_targets, int64_t num_heatmaps);
+int dh_draw_heatmap(void* stream, float* heatmaps, const int32_t* centers, const int32_t* radii,
+                    const int32_t* heatmap_idxes, int64_t num_targets, int64_t num_heatmaps, int64_t height,
+                    int64_t width, float diameter_to_sigma_factor, float k_scale, int mode, void* workspace,
+                    size_t workspace_bytes, dh_status* status);
+
+/* ---- host-buffer entry (end-to-end measurement and non-torch callers) -----------------
+ * Inputs and the output live in HOST memory (pinned for full speed); the call stages the inputs to the
+ * device, renders in FRESH mode and copies the heatmap back, in chunks of whole samples double-buffered
+ * over two internal streams that are joined to `stream`. `device_scratch` must hold
+ * dh_host_scratch_bytes(...) bytes of device memory. If heatmap_host is NULL the heatmap stays on the
+ * device in `heatmap_device` (which must then be non-NULL and hold the whole [B,(C),H,W] output). */
+size_t dh_host_scratch_bytes(int64_t batch_size, int64_t max_num_targets, int64_t num_classes, int64_t height,
+                             int64_t width, int has_labels, int64_t chunk_samples);
+int dh_draw_heatmap_batched_from_boxes_host(void* stream, float* heatmap_host, float* heatmap_device,
+                                            const float* centers_xy_host, const float* bboxes_xyxy_host,
+                                            float out_size_factor, const int64_t* nums_targets_host,
+                                            const int32_t* labels_host, int64_t batch_size,
+                                            int64_t max_num_targets, int64_t num_classes, int64_t height,
+                                            int64_t width, float diameter_to_sigma_factor, float k_scale,
+                                            void* device_scratch, size_t device_scratch_bytes,
+                                            int64_t chunk_samples);
+
+/* ---- measurement helper ---------------------------------------------------------------
+ * Pure 128-bit-store fill of `bytes` bytes (multiple of 16, 16-byte aligned) with zeros using the same
+ * store path and grid shape as the FRESH renderer: the write-only ceiling the renderer is compared to. */
+int dh_fill_probe(void* stream, void* dst, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DH_B200_H */

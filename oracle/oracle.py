@@ -1,0 +1,192 @@
+"""ctypes/numpy front end of the CPU oracle (oracle/dh_oracle.c).  TEST INFRASTRUCTURE ONLY.
+
+May be imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+The product package (accv-lab_b200/) must never import this module.
+
+Functions mirror the reference (paths relative to /root/reference/packages/draw_heatmap):
+  radius_center           tests/_test_helpers.py:20-28
+  draw_batched / draw_flat   accvlab/draw_heatmap/include/draw_heatmap_cuda_kernel.cuh:36-109 (fp32 "spec" family)
+  refcpu_draw_batched     tests/_gaussian_drawing.py:215-240 + tests/_test_helpers.py:41-74 (float64 "refcpu" family)
+  *_numpy                 independent numpy restatements used to cross-check the C code on small cases
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+def lib() -> ctypes.CDLL:
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "libdh_oracle.so")
+        if not os.path.exists(path):
+            from . import build_oracle  # type: ignore
+
+            build_oracle.build_c_oracle()
+        L = ctypes.CDLL(path)
+        c_f, c_i32, c_i64, c_p = ctypes.c_float, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p
+        L.dho_radius_center.argtypes = [c_p, c_p, c_f, c_i64, c_p, c_p]
+        L.dho_radius_center.restype = None
+        L.dho_draw_batched.argtypes = [c_p, c_p, c_p, c_p, c_p] + [c_i64] * 5 + [c_f, c_f]
+        L.dho_draw_batched.restype = None
+        L.dho_draw_flat.argtypes = [c_p, c_p, c_p, c_p] + [c_i64] * 4 + [c_f, c_f]
+        L.dho_draw_flat.restype = None
+        L.dho_refcpu_draw_batched.argtypes = [c_p, c_p, c_p, c_p, c_p] + [c_i64] * 5 + [ctypes.c_double, c_f,
+                                                                                       ctypes.c_int, ctypes.c_int]
+        L.dho_refcpu_draw_batched.restype = None
+        _LIB = L
+    return _LIB
+
+
+def _c(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def radius_center(centers, bboxes, out_size_factor):
+    """centers f32 [...,2], bboxes f32 [...,4] -> (centers_int i32 [...,2], radii i32 [...])."""
+    centers = _c(centers, np.float32)
+    bboxes = _c(bboxes, np.float32)
+    n = centers.size // 2
+    co = np.empty(centers.shape, np.int32)
+    ro = np.empty(centers.shape[:-1], np.int32)
+    lib().dho_radius_center(_ptr(centers), _ptr(bboxes), float(out_size_factor), n, _ptr(co), _ptr(ro))
+    return co, ro
+
+
+def draw_batched(heat, centers, radii, sizes, factor=6.0, k_scale=1.0, labels=None):
+    """In-place max-blend into `heat` (f32 [B,H,W] or [B,C,H,W] C-contiguous numpy array). Returns heat."""
+    assert heat.dtype == np.float32 and heat.flags.c_contiguous
+    centers = _c(centers, np.int32)
+    radii = _c(radii, np.int32)
+    sizes = _c(sizes, np.int64)
+    B, T = radii.shape
+    if labels is not None:
+        labels = _c(labels, np.int32)
+        assert heat.ndim == 4
+        C, H, W = heat.shape[1:]
+    else:
+        assert heat.ndim == 3
+        C, (H, W) = 1, heat.shape[1:]
+    assert heat.shape[0] == B
+    lib().dho_draw_batched(_ptr(heat), _ptr(centers), _ptr(radii), _ptr(sizes), _ptr(labels), B, T, C, H, W,
+                           float(factor), float(k_scale))
+    return heat
+
+
+def draw_flat(heat, centers, radii, heatmap_idxes, factor=6.0, k_scale=1.0):
+    assert heat.dtype == np.float32 and heat.flags.c_contiguous and heat.ndim == 3
+    centers = _c(centers, np.int32)
+    radii = _c(radii, np.int32)
+    idx = _c(heatmap_idxes, np.int32)
+    M, H, W = heat.shape
+    lib().dho_draw_flat(_ptr(heat), _ptr(centers), _ptr(radii), _ptr(idx), radii.shape[0], M, H, W, float(factor),
+                        float(k_scale))
+    return heat
+
+
+def refcpu_draw_batched(heat, centers, radii, sizes, factor=6.0, k_scale=1.0, labels=None, zero_first=False,
+                        nthreads=1):
+    """The reference's float64 CPU path over a padded [B,T] layout (C port), `nthreads` host threads over samples."""
+    assert heat.dtype == np.float32 and heat.flags.c_contiguous
+    centers = _c(centers, np.int32)
+    radii = _c(radii, np.int32)
+    sizes = _c(sizes, np.int64)
+    B, T = radii.shape
+    if labels is not None:
+        labels = _c(labels, np.int32)
+        C, H, W = heat.shape[1:]
+    else:
+        C, (H, W) = 1, heat.shape[1:]
+    lib().dho_refcpu_draw_batched(_ptr(heat), _ptr(centers), _ptr(radii), _ptr(sizes), _ptr(labels), B, T, C, H, W,
+                                  float(factor), float(k_scale), int(bool(zero_first)), int(nthreads))
+    return heat
+
+
+# ---- independent numpy restatements (small cases only) ------------------------------------------------
+def spec_draw_one_numpy(plane, x, y, r, factor, k_scale):
+    """cuh:36-49,61-68 for one object, vectorised over the window, fp32 throughout except the exp (f64->f32)."""
+    H, W = plane.shape
+    x, y, r = int(x), int(y), int(r)
+    if r < 0:
+        return
+    left, right = min(x, r), min(W - x, r + 1)
+    top, bottom = min(y, r), min(H - y, r + 1)
+    if top + bottom <= 0 or left + right <= 0:
+        return
+    f32 = np.float32
+    sigma = f32(2 * r + 1) / f32(factor)
+    var = f32(2.0) * sigma * sigma
+    var_inv = f32(1.0) / var
+    i = np.arange(-top, bottom, dtype=np.int64)
+    j = np.arange(-left, right, dtype=np.int64)
+    ii = (i * i).astype(f32)[:, None]
+    jj = (j * j).astype(f32)[None, :]
+    arg = (-(ii + jj)) * var_inv
+    assert arg.dtype == np.float32
+    g = np.exp(arg.astype(np.float64)).astype(f32) * f32(k_scale)
+    win = plane[y - top : y + bottom, x - left : x + right]
+    keep = win >= g
+    win[...] = np.where(keep, win, g)
+
+
+def draw_batched_numpy(heat, centers, radii, sizes, factor=6.0, k_scale=1.0, labels=None):
+    B, T = np.asarray(radii).shape
+    for s in range(B):
+        n = int(min(max(int(sizes[s]), 0), T))
+        for t in range(n):
+            if labels is not None:
+                lab = int(labels[s][t])
+                if lab < 0 or lab >= heat.shape[1]:
+                    continue
+                plane = heat[s, lab]
+            else:
+                plane = heat[s]
+            spec_draw_one_numpy(plane, centers[s][t][0], centers[s][t][1], radii[s][t], factor, k_scale)
+    return heat
+
+
+def radius_center_numpy(centers, bboxes, osf):
+    centers = np.asarray(centers, np.float32)
+    bboxes = np.asarray(bboxes, np.float32)
+    tl = centers - bboxes[..., :2]
+    br = bboxes[..., 2:] - centers
+    m = np.minimum(np.minimum(tl[..., 0], tl[..., 1]), np.minimum(br[..., 0], br[..., 1]))
+    r = np.ceil(m / np.float32(osf)).astype(np.int32)
+    r[r < 1] = 1
+    c = np.trunc(centers / np.float32(osf)).astype(np.int32)
+    return c, r
+
+
+def touched_mask_batched(shape, centers, radii, sizes, labels=None):
+    """Union of the clipped (2r+1)^2 windows: the pixels the reference kernel touches (cuh:40-47,65-68)."""
+    mask = np.zeros(shape, dtype=bool)
+    H, W = shape[-2:]
+    B, T = np.asarray(radii).shape
+    for s in range(B):
+        n = int(min(max(int(sizes[s]), 0), T))
+        for t in range(n):
+            x, y, r = int(centers[s][t][0]), int(centers[s][t][1]), int(radii[s][t])
+            if r < 0:
+                continue
+            x0, x1 = max(x - r, 0), min(x + r + 1, W)
+            y0, y1 = max(y - r, 0), min(y + r + 1, H)
+            if x0 >= x1 or y0 >= y1:
+                continue
+            if labels is not None:
+                lab = int(labels[s][t])
+                if lab < 0 or lab >= shape[1]:
+                    continue
+                mask[s, lab, y0:y1, x0:x1] = True
+            else:
+                mask[s, y0:y1, x0:x1] = True
+    return mask
