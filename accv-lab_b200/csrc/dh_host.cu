@@ -1,0 +1,255 @@
+// dh_host.cu — result checksum kernel and the host-buffer entry of the C ABI (include/dh_b200.h).
+//
+// Neither has a counterpart in the reference (its API is device-tensor in / device-tensor out,
+// /root/reference/packages/draw_heatmap/accvlab/draw_heatmap/csrc/draw_heatmap_cuda.cu:91-165, and it has no
+// multi-GPU path). They exist for (a) end-to-end measurement from host buffers, (b) non-torch callers,
+// (c) verifying that a batch sharded over G GPUs equals the unsharded result without gathering it.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <mutex>
+
+#include "dh_b200.h"
+
+namespace dh {
+
+extern void count_launches(uint64_t n);  // dh_kernels.cu
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {  // splitmix64 finaliser
+    z += 0x9e3779b97f4a7c15ull;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+
+__device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+// Grid-stride over float4 groups (scalar head/tail handled by the same loop at element granularity when the
+// pointer is not 16-byte aligned). Wrapping uint64 sums: exactly associative, so the digest is independent of the
+// grid shape and of how a batch is split over GPUs.
+__global__ void __launch_bounds__(256) checksum_kernel(const float* __restrict__ v, long long n, long long index_base,
+                                                       unsigned long long* __restrict__ out3, int vec_ok) {
+    unsigned long long s_bits = 0, s_hash = 0, s_cnt = 0;
+    const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long nthreads = (long long)gridDim.x * blockDim.x;
+    auto one = [&](float x, long long i) {
+        s_bits += (unsigned long long)__float_as_uint(x);
+        if (x > 0.0f) {
+            s_hash += mix64((unsigned long long)(index_base + i));
+            s_cnt += 1;
+        }
+    };
+    if (vec_ok) {
+        const long long n4 = n >> 2;
+        const float4* v4 = reinterpret_cast<const float4*>(v);
+        for (long long g = tid; g < n4; g += nthreads) {
+            const float4 q = __ldcs(v4 + g);
+            one(q.x, 4 * g);
+            one(q.y, 4 * g + 1);
+            one(q.z, 4 * g + 2);
+            one(q.w, 4 * g + 3);
+        }
+        for (long long i = (n4 << 2) + tid; i < n; i += nthreads) one(v[i], i);
+    } else {
+        for (long long i = tid; i < n; i += nthreads) one(v[i], i);
+    }
+    __shared__ unsigned long long sm[3][8];
+    s_bits = warp_sum(s_bits);
+    s_hash = warp_sum(s_hash);
+    s_cnt = warp_sum(s_cnt);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        sm[0][warp] = s_bits;
+        sm[1][warp] = s_hash;
+        sm[2][warp] = s_cnt;
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        unsigned long long t = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += sm[threadIdx.x][w];
+        atomicAdd(&out3[threadIdx.x], t);
+    }
+}
+
+// ---- helper streams of the host entry (per device, created once) ------------------------------------
+struct HostCtx {
+    bool ready = false;
+    cudaStream_t s[2] = {nullptr, nullptr};
+    cudaEvent_t fork = nullptr, join[2] = {nullptr, nullptr};
+};
+static HostCtx g_ctx[64];
+static std::mutex g_ctx_mu;
+
+static int host_ctx(HostCtx*& out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
+    HostCtx& c = g_ctx[dev];
+    if (!c.ready) {
+        for (int i = 0; i < 2; ++i) {
+            if ((e = cudaStreamCreateWithFlags(&c.s[i], cudaStreamNonBlocking)) != cudaSuccess) return (int)e;
+            if ((e = cudaEventCreateWithFlags(&c.join[i], cudaEventDisableTiming)) != cudaSuccess) return (int)e;
+        }
+        if ((e = cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming)) != cudaSuccess) return (int)e;
+        c.ready = true;
+    }
+    out = &c;
+    return DH_OK;
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct HostLayout {
+    size_t off_centers, off_bboxes, off_sizes, off_labels, off_cksum, off_stage[2], total;
+    int64_t chunk;
+};
+
+static HostLayout host_layout(int64_t B, int64_t T, int64_t C, int64_t H, int64_t W, bool has_labels, int64_t chunk,
+                              bool staging) {
+    HostLayout L{};
+    const int64_t planes_per_sample = has_labels ? C : 1;
+    const size_t sample_bytes = (size_t)planes_per_sample * (size_t)H * (size_t)W * 4;
+    if (chunk <= 0) {
+        chunk = sample_bytes ? (int64_t)((64ull << 20) / sample_bytes) : B;
+        if (chunk < 1) chunk = 1;
+    }
+    if (chunk > B) chunk = B > 0 ? B : 1;
+    L.chunk = chunk;
+    size_t o = 0;
+    L.off_centers = o; o += align256((size_t)B * T * 2 * 4);
+    L.off_bboxes = o;  o += align256((size_t)B * T * 4 * 4);
+    L.off_sizes = o;   o += align256((size_t)B * 8);
+    L.off_labels = o;  o += has_labels ? align256((size_t)B * T * 4) : 0;
+    L.off_cksum = o;   o += 256;
+    for (int i = 0; i < 2; ++i) {
+        L.off_stage[i] = o;
+        if (staging) o += align256((size_t)chunk * sample_bytes);
+    }
+    L.total = o;
+    return L;
+}
+
+}  // namespace dh
+
+extern "C" {
+
+int dh_checksum(void* stream, const float* values, int64_t n, int64_t index_base, uint64_t* out3) {
+    if (n < 0 || !out3) return DH_ERR_INVALID_ARGUMENT;
+    if (n == 0) return DH_OK;
+    if (!values) return DH_ERR_INVALID_ARGUMENT;
+    int dev = 0, sms = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return (int)e;
+    long long blocks = (n / 4 + 255) / 256;
+    if (blocks < 1) blocks = 1;
+    if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
+    const int vec_ok = (reinterpret_cast<uintptr_t>(values) & 15u) == 0;
+    dh::checksum_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(values, n, index_base,
+                                                                       (unsigned long long*)out3, vec_ok);
+    dh::count_launches(1);
+    return (int)cudaGetLastError();
+}
+
+size_t dh_host_scratch_bytes(int64_t B, int64_t T, int64_t C, int64_t H, int64_t W, int has_labels,
+                             int64_t chunk_samples, int staging_buffers) {
+    if (B < 0 || T < 0 || C < 0 || H < 0 || W < 0) return 0;
+    return dh::host_layout(B, T, C, H, W, has_labels != 0, chunk_samples, staging_buffers != 0).total;
+}
+
+int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, float* heatmap_device,
+                                            uint64_t* checksum_host, const float* centers_xy_host,
+                                            const float* bboxes_xyxy_host, float osf, const int64_t* nums_targets_host,
+                                            const int32_t* labels_host, int64_t B, int64_t T, int64_t C, int64_t H,
+                                            int64_t W, float factor, float k, void* device_scratch,
+                                            size_t device_scratch_bytes, int64_t chunk_samples) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (B < 0 || T < 0 || H < 1 || W < 1) return DH_ERR_INVALID_ARGUMENT;
+    const bool has_labels = labels_host != nullptr;
+    if (!has_labels) C = 1;
+    if (C < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (!heatmap_host && !heatmap_device) return DH_ERR_INVALID_ARGUMENT;
+    if (B == 0 || C == 0) {
+        if (checksum_host) checksum_host[0] = checksum_host[1] = checksum_host[2] = 0;
+        return DH_OK;
+    }
+    if (!nums_targets_host || (T > 0 && (!centers_xy_host || !bboxes_xyxy_host))) return DH_ERR_INVALID_ARGUMENT;
+    const bool staging = heatmap_host && !heatmap_device;
+    const dh::HostLayout L = dh::host_layout(B, T, C, H, W, has_labels, chunk_samples, staging);
+    if (!device_scratch || device_scratch_bytes < L.total) return DH_ERR_WORKSPACE_TOO_SMALL;
+    if (reinterpret_cast<uintptr_t>(device_scratch) & 15u) return DH_ERR_INVALID_ARGUMENT;
+
+    char* ws = (char*)device_scratch;
+    float* d_centers = (float*)(ws + L.off_centers);
+    float* d_bboxes = (float*)(ws + L.off_bboxes);
+    int64_t* d_sizes = (int64_t*)(ws + L.off_sizes);
+    int32_t* d_labels = has_labels ? (int32_t*)(ws + L.off_labels) : nullptr;
+    uint64_t* d_ck = (uint64_t*)(ws + L.off_cksum);
+
+    cudaError_t e;
+#define DH_TRY(x) do { if ((e = (x)) != cudaSuccess) return (int)e; } while (0)
+    // ---- inputs: host -> device, one copy per array ----
+    if (T > 0) {
+        DH_TRY(cudaMemcpyAsync(d_centers, centers_xy_host, (size_t)B * T * 2 * 4, cudaMemcpyHostToDevice, stream));
+        DH_TRY(cudaMemcpyAsync(d_bboxes, bboxes_xyxy_host, (size_t)B * T * 4 * 4, cudaMemcpyHostToDevice, stream));
+        if (has_labels)
+            DH_TRY(cudaMemcpyAsync(d_labels, labels_host, (size_t)B * T * 4, cudaMemcpyHostToDevice, stream));
+    }
+    DH_TRY(cudaMemcpyAsync(d_sizes, nums_targets_host, (size_t)B * 8, cudaMemcpyHostToDevice, stream));
+    if (checksum_host) DH_TRY(cudaMemsetAsync(d_ck, 0, 24, stream));
+
+    const int64_t sample_elems = C * H * W;
+    int st;
+    if (!heatmap_host) {  // result stays on the device: one launch
+        st = dh_draw_heatmap_batched_from_boxes(stream, heatmap_device, d_centers, d_bboxes, osf, d_sizes, DH_SIZES_I64,
+                                                d_labels, B, T, C, H, W, factor, k, DH_MODE_FRESH, nullptr, nullptr,
+                                                nullptr);
+        if (st != DH_OK) return st;
+        if (checksum_host) {
+            st = dh_checksum(stream, heatmap_device, B * sample_elems, 0, d_ck);
+            if (st != DH_OK) return st;
+            DH_TRY(cudaMemcpyAsync(checksum_host, d_ck, 24, cudaMemcpyDeviceToHost, stream));
+        }
+        return DH_OK;
+    }
+
+    // ---- chunked render + copy back, double-buffered over two helper streams ----
+    std::lock_guard<std::mutex> lock(dh::g_ctx_mu);
+    dh::HostCtx* ctx = nullptr;
+    st = dh::host_ctx(ctx);
+    if (st != DH_OK) return st;
+    DH_TRY(cudaEventRecord(ctx->fork, stream));
+    DH_TRY(cudaStreamWaitEvent(ctx->s[0], ctx->fork, 0));
+    DH_TRY(cudaStreamWaitEvent(ctx->s[1], ctx->fork, 0));
+    int64_t i = 0;
+    for (int64_t s0 = 0; s0 < B; s0 += L.chunk, ++i) {
+        const int64_t nb = (B - s0 < L.chunk) ? (B - s0) : L.chunk;
+        cudaStream_t cs = ctx->s[i & 1];
+        float* dst = staging ? (float*)(ws + L.off_stage[i & 1]) : heatmap_device + s0 * sample_elems;
+        st = dh_draw_heatmap_batched_from_boxes(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf, d_sizes + s0,
+                                                DH_SIZES_I64, has_labels ? d_labels + s0 * T : nullptr, nb, T, C, H, W,
+                                                factor, k, DH_MODE_FRESH, nullptr, nullptr, nullptr);
+        if (st != DH_OK) return st;
+        if (checksum_host) {
+            st = dh_checksum(cs, dst, nb * sample_elems, s0 * sample_elems, d_ck);
+            if (st != DH_OK) return st;
+        }
+        DH_TRY(cudaMemcpyAsync(heatmap_host + s0 * sample_elems, dst, (size_t)nb * sample_elems * 4,
+                               cudaMemcpyDeviceToHost, cs));
+    }
+    for (int j = 0; j < 2; ++j) {
+        DH_TRY(cudaEventRecord(ctx->join[j], ctx->s[j]));
+        DH_TRY(cudaStreamWaitEvent(stream, ctx->join[j], 0));
+    }
+    if (checksum_host) DH_TRY(cudaMemcpyAsync(checksum_host, d_ck, 24, cudaMemcpyDeviceToHost, stream));
+#undef DH_TRY
+    return DH_OK;
+}
+
+}  // extern "C"

@@ -506,9 +506,15 @@ __global__ void __launch_bounds__(kThreads) fill_probe_kernel(float4* __restrict
     }
 }
 
+__global__ void __launch_bounds__(256) expf_probe_kernel(unsigned start_bits, long long n, float* __restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = expf(__uint_as_float(start_bits + (unsigned)i));
+}
+
 // ------------------------------------------------------------------------------------------------
 // Host side
 std::atomic<uint64_t> g_launches{0};
+void count_launches(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }  // used by dh_host.cu
 
 struct DeviceInfo {
     int sms = 0;
@@ -802,6 +808,19 @@ int dh_fill_probe(void* stream, void* dst, size_t bytes) {
     const long long cap = (long long)di.sms * 8;
     dh::fill_probe_kernel<<<(int)(nchunks < cap ? nchunks : cap), dh::kThreads, 0, (cudaStream_t)stream>>>(
         (float4*)dst, n4, chunk4);
+    dh::g_launches.fetch_add(1, std::memory_order_relaxed);
+    return (int)cudaGetLastError();
+}
+
+int dh_expf_probe(void* stream, uint32_t start_bits, int64_t n, float* out) {
+    if (n < 0 || (n > 0 && !out)) return DH_ERR_INVALID_ARGUMENT;
+    if (n == 0) return DH_OK;
+    dh::DeviceInfo di;
+    int st = dh::device_info(di);
+    if (st != DH_OK) return st;
+    long long blocks = (n + 255) / 256;
+    if (blocks > (long long)di.sms * 16) blocks = (long long)di.sms * 16;
+    dh::expf_probe_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(start_bits, n, out);
     dh::g_launches.fetch_add(1, std::memory_order_relaxed);
     return (int)cudaGetLastError();
 }

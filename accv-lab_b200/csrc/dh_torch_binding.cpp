@@ -215,6 +215,91 @@ void render_heatmap_from_boxes(at::Tensor& heatmaps, const at::Tensor& centers, 
                  "render_heatmap_from_boxes");
 }
 
+// digest += checksum(values); digest is a CUDA int64[3] tensor (wrapping uint64 arithmetic, see dh_b200.h)
+void checksum_(const at::Tensor& values, at::Tensor& digest, int64_t index_base) {
+    CHECK_INPUT(values);
+    CHECK_INPUT(digest);
+    CHECK_DTYPE(values, at::kFloat);
+    CHECK_DTYPE(digest, at::kLong);
+    CHECK_SAME_DEVICE(digest, values);
+    TORCH_CHECK(digest.numel() == 3, "digest must have 3 int64 elements");
+    c10::cuda::CUDAGuard guard(values.device());
+    check_status(dh_checksum(at::cuda::getCurrentCUDAStream().stream(), values.data_ptr<float>(), values.numel(),
+                             index_base, reinterpret_cast<uint64_t*>(digest.data_ptr<int64_t>())),
+                 "checksum");
+}
+
+int64_t host_scratch_bytes(int64_t B, int64_t T, int64_t C, int64_t H, int64_t W, bool has_labels, int64_t chunk_samples,
+                           bool staging) {
+    return (int64_t)dh_host_scratch_bytes(B, T, C, H, W, has_labels, chunk_samples, staging);
+}
+
+// Host-buffer entry: CPU (ideally pinned) inputs -> heatmap on the host and/or the device (+ optional digest).
+void render_heatmap_from_boxes_host(const c10::optional<at::Tensor>& heatmap_host,
+                                    const c10::optional<at::Tensor>& heatmap_device,
+                                    const c10::optional<at::Tensor>& checksum_host, const at::Tensor& centers,
+                                    const at::Tensor& bboxes, double out_size_factor, const at::Tensor& nums_targets,
+                                    const c10::optional<at::Tensor>& labels, int64_t num_classes, int64_t height,
+                                    int64_t width, float diameter_to_sigma_factor, float k_scale, at::Tensor& scratch,
+                                    int64_t chunk_samples) {
+    auto check_cpu = [](const at::Tensor& t, const char* name) {
+        TORCH_CHECK(t.device().is_cpu(), name, " must be a CPU (host) tensor");
+        TORCH_CHECK(t.is_contiguous(), name, " must be contiguous");
+    };
+    check_cpu(centers, "centers");
+    check_cpu(bboxes, "bboxes");
+    check_cpu(nums_targets, "nums_targets");
+    CHECK_DTYPE(centers, at::kFloat);
+    CHECK_DTYPE(bboxes, at::kFloat);
+    CHECK_DTYPE(nums_targets, at::kLong);
+    TORCH_CHECK(centers.dim() == 3 && centers.size(2) == 2, "centers must be of shape [batch_size, num_targets, 2]");
+    TORCH_CHECK(bboxes.dim() == 3 && bboxes.size(2) == 4, "bboxes must be of shape [batch_size, num_targets, 4]");
+    const int64_t B = centers.size(0), T = centers.size(1);
+    TORCH_CHECK(bboxes.size(0) == B && bboxes.size(1) == T && nums_targets.dim() == 1 && nums_targets.size(0) == B,
+                "batch_size (dim 0) and num_targets (dim 1) need to be the same for all inputs");
+    const bool cw = labels.has_value();
+    if (cw) {
+        check_cpu(*labels, "labels");
+        CHECK_DTYPE((*labels), at::kInt);
+        TORCH_CHECK(labels->dim() == 2 && labels->size(0) == B && labels->size(1) == T,
+                    "labels shape must be [batch_size, num_targets]");
+    }
+    const int64_t C = cw ? num_classes : 1;
+    const int64_t numel = B * C * height * width;
+    float* hh = nullptr;
+    float* hd = nullptr;
+    if (heatmap_host.has_value()) {
+        check_cpu(*heatmap_host, "heatmap_host");
+        CHECK_DTYPE((*heatmap_host), at::kFloat);
+        TORCH_CHECK(heatmap_host->numel() == numel, "heatmap_host has the wrong number of elements");
+        hh = heatmap_host->data_ptr<float>();
+    }
+    CHECK_INPUT(scratch);
+    if (heatmap_device.has_value()) {
+        const at::Tensor& heatmap_device_ = *heatmap_device;
+        CHECK_INPUT(heatmap_device_);
+        CHECK_DTYPE(heatmap_device_, at::kFloat);
+        CHECK_SAME_DEVICE(heatmap_device_, scratch);
+        TORCH_CHECK(heatmap_device->numel() == numel, "heatmap_device has the wrong number of elements");
+        hd = heatmap_device->data_ptr<float>();
+    }
+    TORCH_CHECK(hh || hd, "at least one of heatmap_host / heatmap_device must be given");
+    uint64_t* ck = nullptr;
+    if (checksum_host.has_value()) {
+        check_cpu(*checksum_host, "checksum_host");
+        CHECK_DTYPE((*checksum_host), at::kLong);
+        TORCH_CHECK(checksum_host->numel() == 3, "checksum_host must have 3 int64 elements");
+        ck = reinterpret_cast<uint64_t*>(checksum_host->data_ptr<int64_t>());
+    }
+    c10::cuda::CUDAGuard guard(scratch.device());
+    check_status(dh_draw_heatmap_batched_from_boxes_host(
+                     at::cuda::getCurrentCUDAStream().stream(), hh, hd, ck, centers.data_ptr<float>(),
+                     bboxes.data_ptr<float>(), (float)out_size_factor, nums_targets.data_ptr<int64_t>(),
+                     cw ? labels->data_ptr<int>() : nullptr, B, T, C, height, width, diameter_to_sigma_factor, k_scale,
+                     scratch.data_ptr(), (size_t)scratch.nbytes(), chunk_samples),
+                 "render_heatmap_from_boxes_host");
+}
+
 void fill_probe(at::Tensor& t) {
     CHECK_INPUT(t);
     c10::cuda::CUDAGuard guard(t.device());
@@ -254,6 +339,18 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f, pybind11::arg("fresh") = false);
     m.def("fill_probe", &fill_probe, "Zero-fill a tensor with the renderer's store path (write-only ceiling).",
           pybind11::arg("tensor"));
+    m.def("checksum_", &checksum_, "digest[3] (int64, CUDA) += order-independent digest of a float32 CUDA tensor.",
+          pybind11::arg("values"), pybind11::arg("digest"), pybind11::arg("index_base") = 0);
+    m.def("host_scratch_bytes", &host_scratch_bytes, pybind11::arg("batch_size"), pybind11::arg("max_num_targets"),
+          pybind11::arg("num_classes"), pybind11::arg("height"), pybind11::arg("width"), pybind11::arg("has_labels"),
+          pybind11::arg("chunk_samples") = 0, pybind11::arg("staging") = false);
+    m.def("render_heatmap_from_boxes_host", &render_heatmap_from_boxes_host,
+          "Host-buffer entry: stage inputs, render (K1 fused, fresh), optionally copy the heatmap / a digest back.",
+          pybind11::arg("heatmap_host"), pybind11::arg("heatmap_device"), pybind11::arg("checksum_host"),
+          pybind11::arg("centers"), pybind11::arg("bboxes"), pybind11::arg("out_size_factor"),
+          pybind11::arg("nums_targets"), pybind11::arg("labels"), pybind11::arg("num_classes"), pybind11::arg("height"),
+          pybind11::arg("width"), pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f,
+          pybind11::arg("scratch"), pybind11::arg("chunk_samples") = 0);
     m.def("launch_count", []() { return dh_launch_count(); }, "Kernels launched by this library in this process.");
     m.def("build_info", []() { return std::string(dh_build_info()); });
 }

@@ -9,7 +9,8 @@
  *   - plain pointers and sizes only; no torch / ATen / C++ types cross this boundary;
  *   - all data pointers are DEVICE pointers unless the name ends in `_host`;
  *   - `stream` is a `cudaStream_t` passed as `void*` (NULL = legacy default stream);
- *   - every call is asynchronous on `stream`, allocates nothing, keeps no state;
+ *   - every call is asynchronous on `stream`, allocates no memory and keeps no state (exceptions: cached
+ *     device attributes, and the two helper streams of the host-buffer entry);
  *   - return value: DH_OK (0), a negative DH_ERR_* code, or a positive `cudaError_t`
  *     reported by the launch (the reference only printf()s launch errors,
  *     DH/accvlab/draw_heatmap/csrc/draw_heatmap_cuda.cu:37-40,56-59; we return them);
@@ -123,27 +124,52 @@ int dh_draw_heatmap(void* stream, float* heatmaps, const int32_t* centers, const
                     int64_t width, float diameter_to_sigma_factor, float k_scale, int mode, void* workspace,
                     size_t workspace_bytes, dh_status* status);
 
+/* ---- result checksum (multi-GPU verification and the e2e "result read") -----------------
+ * Order-independent, exactly additive digest of `n` fp32 values (so shards of a batch can be digested on
+ * different GPUs and summed with wrapping uint64 adds, e.g. an NCCL all_reduce(SUM) over int64):
+ *     out[0] += sum_i  bits(v_i)                          (fp32 bit patterns, wrapping uint64)
+ *     out[1] += sum_{i: v_i > 0} mix64(index_base + i)    (hash of the touched-pixel mask)
+ *     out[2] += #{i: v_i > 0}
+ * `out` is a DEVICE array of 3 uint64 that the caller zeroes (or carries over). No reference equivalent:
+ * the reference has no multi-GPU path. */
+int dh_checksum(void* stream, const float* values, int64_t n, int64_t index_base, uint64_t* out3);
+
 /* ---- host-buffer entry (end-to-end measurement and non-torch callers) -----------------
- * Inputs and the output live in HOST memory (pinned for full speed); the call stages the inputs to the
- * device, renders in FRESH mode and copies the heatmap back, in chunks of whole samples double-buffered
- * over two internal streams that are joined to `stream`. `device_scratch` must hold
- * dh_host_scratch_bytes(...) bytes of device memory. If heatmap_host is NULL the heatmap stays on the
- * device in `heatmap_device` (which must then be non-NULL and hold the whole [B,(C),H,W] output). */
+ * Inputs live in HOST memory (pinned for full speed). The call stages the inputs to the device with
+ * cudaMemcpyAsync, renders in FRESH mode with K1 fused (dh_draw_heatmap_batched_from_boxes), and
+ *   - heatmap_host != NULL: copies the heatmap back to the host in chunks of `chunk_samples` samples; render of
+ *     chunk i overlaps the device->host copy of chunk i-1 on two internal (per-device, lazily created,
+ *     process-lifetime) streams that are fork/joined to `stream` with events. If heatmap_device is NULL the
+ *     chunks are rendered into two staging buffers inside `device_scratch`, so device memory use is bounded
+ *     independent of B; otherwise they are rendered in place into heatmap_device [B,(C),H,W].
+ *   - heatmap_host == NULL: heatmap_device must be non-NULL; one render launch, the result stays on the device.
+ *   - checksum_host (optional, 3 x uint64, host): dh_checksum of the whole result, copied to the host.
+ * labels_host == NULL -> heatmap is [B,H,W] and num_classes is ignored. nums_targets_host is int64 [B].
+ * chunk_samples <= 0 selects a default (about 64 MiB of output per chunk).
+ * `device_scratch` (16-byte aligned) must hold dh_host_scratch_bytes(...) bytes for the same arguments.
+ * The call is asynchronous with respect to the host like every other entry: synchronise `stream` before
+ * reading heatmap_host / checksum_host. */
 size_t dh_host_scratch_bytes(int64_t batch_size, int64_t max_num_targets, int64_t num_classes, int64_t height,
-                             int64_t width, int has_labels, int64_t chunk_samples);
+                             int64_t width, int has_labels, int64_t chunk_samples, int staging_buffers);
 int dh_draw_heatmap_batched_from_boxes_host(void* stream, float* heatmap_host, float* heatmap_device,
-                                            const float* centers_xy_host, const float* bboxes_xyxy_host,
-                                            float out_size_factor, const int64_t* nums_targets_host,
-                                            const int32_t* labels_host, int64_t batch_size,
-                                            int64_t max_num_targets, int64_t num_classes, int64_t height,
-                                            int64_t width, float diameter_to_sigma_factor, float k_scale,
-                                            void* device_scratch, size_t device_scratch_bytes,
+                                            uint64_t* checksum_host, const float* centers_xy_host,
+                                            const float* bboxes_xyxy_host, float out_size_factor,
+                                            const int64_t* nums_targets_host, const int32_t* labels_host,
+                                            int64_t batch_size, int64_t max_num_targets, int64_t num_classes,
+                                            int64_t height, int64_t width, float diameter_to_sigma_factor,
+                                            float k_scale, void* device_scratch, size_t device_scratch_bytes,
                                             int64_t chunk_samples);
 
 /* ---- measurement helper ---------------------------------------------------------------
  * Pure 128-bit-store fill of `bytes` bytes (multiple of 16, 16-byte aligned) with zeros using the same
  * store path and grid shape as the FRESH renderer: the write-only ceiling the renderer is compared to. */
 int dh_fill_probe(void* stream, void* dst, size_t bytes);
+
+/* out[i] = expf(x_i) where x_i is the float whose bit pattern is start_bits + i, evaluated with exactly the
+ * exponential the renderer uses. Lets the tests check on the GPU (exhaustively over the argument range) that it
+ * is monotone — the property behind "one expf per pixel": max_o k*exp(a_o) == k*exp(max_o a_o) — and measure its
+ * ulp distance to a correctly rounded exp. */
+int dh_expf_probe(void* stream, uint32_t start_bits, int64_t n, float* out);
 
 #ifdef __cplusplus
 }
