@@ -1,0 +1,237 @@
+"""GPU: size-independent properties at full BASELINE sizes, edge cases, the host-buffer entry and the digest."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import _cabi
+import workloads
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev(a, dev, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.to(dev)
+
+
+def _upload(w, dev):
+    return (_dev(w.centers_f, dev), _dev(w.bboxes_f, dev), _dev(w.sizes, dev), _dev(w.labels, dev))
+
+
+def test_cfg3_full_size_properties(cabi, cuda_dev):
+    """fresh == zeros+accumulate; idempotence; accumulate keeps larger existing values; mask == union of windows
+    computed independently with torch ops; every value in [0, k]; centre pixels == k exactly."""
+    w = workloads.make("cfg3")
+    cfg = w.cfg
+    cf, bf, s, lab = _upload(w, cuda_dev)
+    shape = (w.B, cfg.C, cfg.H, cfg.W)
+    fresh = torch.full(shape, 9.0, device=cuda_dev)
+    _cabi.draw_from_boxes(cabi, fresh, cf, bf, float(cfg.osf), s, lab, 6.0, 0.8)
+    co, ro = _cabi.radius_center(cabi, cf, bf, float(cfg.osf))
+    acc = torch.zeros(shape, device=cuda_dev)
+    _cabi.draw_batched(cabi, acc, co, ro, s, lab, 6.0, 0.8)
+    assert torch.equal(fresh, acc)
+    _cabi.draw_batched(cabi, acc, co, ro, s, lab, 6.0, 0.8)  # idempotent
+    assert torch.equal(fresh, acc)
+    base = torch.full(shape, 0.25, device=cuda_dev)
+    _cabi.draw_batched(cabi, base, co, ro, s, lab, 6.0, 0.8)
+    assert torch.equal(base, torch.maximum(fresh, torch.tensor(0.25, device=cuda_dev)))
+    assert float(fresh.min()) >= 0.0 and float(fresh.max()) == np.float32(0.8)
+    # independent mask: scatter window corners into a 2-D difference image per plane, integrate
+    T = w.T
+    valid = torch.arange(T, device=cuda_dev)[None, :] < s[:, None]
+    x, y, r = co[..., 0].long(), co[..., 1].long(), ro.long()
+    x0, x1 = (x - r).clamp(0, cfg.W), (x + r + 1).clamp(0, cfg.W)
+    y0, y1 = (y - r).clamp(0, cfg.H), (y + r + 1).clamp(0, cfg.H)
+    valid &= (x0 < x1) & (y0 < y1)
+    plane = (torch.arange(w.B, device=cuda_dev)[:, None] * cfg.C + lab.long())[valid]
+    diff = torch.zeros((w.B * cfg.C, cfg.H + 1, cfg.W + 1), device=cuda_dev, dtype=torch.int32)
+    one = torch.ones_like(plane, dtype=torch.int32)
+    diff.index_put_((plane, y0[valid], x0[valid]), one, accumulate=True)
+    diff.index_put_((plane, y1[valid], x1[valid]), one, accumulate=True)
+    diff.index_put_((plane, y0[valid], x1[valid]), -one, accumulate=True)
+    diff.index_put_((plane, y1[valid], x0[valid]), -one, accumulate=True)
+    cover = diff.cumsum(1).cumsum(2)[:, : cfg.H, : cfg.W] > 0
+    assert torch.equal(cover.reshape(shape), fresh > 0)
+    inside = valid & (x >= 0) & (x < cfg.W) & (y >= 0) & (y < cfg.H)
+    pl = (torch.arange(w.B, device=cuda_dev)[:, None] * cfg.C + lab.long())[inside]
+    assert bool((fresh.reshape(-1, cfg.H, cfg.W)[pl, y[inside], x[inside]] == np.float32(0.8)).all())
+
+
+def test_sharded_equals_unsharded_digest(cabi, cuda_dev):
+    """G contiguous batch slices rendered independently give the unsharded result (digest additive)."""
+    w = workloads.make("cfg5", B=96)
+    cfg = w.cfg
+    cf, bf, s, lab = _upload(w, cuda_dev)
+    whole = torch.empty((w.B, cfg.C, cfg.H, cfg.W), device=cuda_dev)
+    _cabi.draw_from_boxes(cabi, whole, cf, bf, float(cfg.osf), s, lab)
+    d_whole = _cabi.checksum(cabi, whole)
+    sample_elems = cfg.C * cfg.H * cfg.W
+    for G in (2, 8):
+        d = torch.zeros(3, dtype=torch.int64, device=cuda_dev)
+        for g in range(G):
+            lo, hi = workloads.shard_range(w.B, g, G)
+            part = torch.empty((hi - lo, cfg.C, cfg.H, cfg.W), device=cuda_dev)
+            _cabi.draw_from_boxes(cabi, part, cf[lo:hi].contiguous(), bf[lo:hi].contiguous(), float(cfg.osf),
+                                  s[lo:hi].contiguous(), lab[lo:hi].contiguous())
+            assert torch.equal(part, whole[lo:hi])
+            _cabi.checksum(cabi, part, lo * sample_elems, d)
+        assert torch.equal(d, d_whole)
+
+
+def test_plane_offsets_are_64_bit(cabi, cuda_dev):
+    """F5: B*C*H*W >= 2^31 elements in one call (the reference's int index overflows there)."""
+    H = W = 1024
+    B = 2049  # 2049 * 2^20 > 2^31 elements, 8.6 GB
+    c = torch.zeros((B, 1, 2), dtype=torch.int32, device=cuda_dev)
+    c[:, 0, 0] = 1000
+    c[:, 0, 1] = 1020
+    r = torch.full((B, 1), 2, dtype=torch.int32, device=cuda_dev)
+    s = torch.ones(B, dtype=torch.int32, device=cuda_dev)
+    heat = torch.empty((B, H, W), device=cuda_dev)
+    _cabi.draw_batched(cabi, heat, c, r, s, None, 6.0, 1.0, _cabi.DH_MODE_FRESH)
+    assert float(heat[B - 1, 1020, 1000]) == 1.0 and float(heat[B - 1, 1020, 1003]) == 0.0
+    assert int((heat[B - 1] > 0).sum()) == 5 * 5 and int((heat[0] > 0).sum()) == 25
+    assert int(_cabi.checksum(cabi, heat)[2]) == 25 * B
+    del heat
+
+
+def test_edge_cases(cabi, cuda_dev, oracle):
+    dev = cuda_dev
+    H, W = 37, 53  # W % 4 != 0 -> scalar store path
+    objs = np.array([[5, 5, 2], [0, 0, 4], [52, 36, 3], [-2, 10, 3], [60, 10, 3], [20, -9, 3], [20, 20, 100],
+                     [10, 30, 0], [30, 10, -1], [53, 36, 1], [25, 18, 7]], np.int32)
+    n = len(objs)
+    c, r = _dev(objs[None, :, :2], dev), _dev(objs[None, :, 2], dev)
+    for k in (1.0, 0.8, 0.0, -0.5):
+        for factor in (6.0, 1.0, 12.0, 40.0):
+            for init in (0.0, 0.3):
+                want = np.full((1, H, W), init, np.float32)
+                oracle.draw_batched(want, objs[None, :, :2], objs[None, :, 2], np.array([n]), factor, k)
+                heat = torch.full((1, H, W), init, device=dev)
+                _cabi.draw_batched(cabi, heat, c, r, torch.tensor([n], device=dev), None, factor, k)
+                got = heat.cpu().numpy()
+                assert np.abs(got - want).max() <= 1e-6, (k, factor, init)
+                # masks must agree except where the value is an fp32 denormal (exp argument < -87.3, reachable only
+                # with factor >~ 13): there a 1-ulp difference between libdevice expf and the oracle's correctly
+                # rounded exp can flip v > 0. Against the reference GPU build (same expf) masks are always equal.
+                flip = (got > 0) != (want > 0)
+                assert not (flip & (np.maximum(got, want) >= 1e-37)).any(), (k, factor, init)
+    # sizes: 0, > T (clamped), negative (clamped to 0); T == 0; B == 0
+    heat = torch.full((3, H, W), 5.0, device=dev)
+    c3, r3 = c.expand(3, n, 2).contiguous(), r.expand(3, n).contiguous()
+    _cabi.draw_batched(cabi, heat, c3, r3, torch.tensor([0, n + 50, -3], device=dev), None, 6.0, 1.0, _cabi.DH_MODE_FRESH)
+    assert float(heat[0].abs().max()) == 0.0 and float(heat[2].abs().max()) == 0.0 and float(heat[1].max()) == 1.0
+    heat = torch.full((2, H, W), 5.0, device=dev)
+    e2 = torch.empty((2, 0, 2), dtype=torch.int32, device=dev)
+    _cabi.draw_batched(cabi, heat, e2, e2[..., 0].contiguous(), torch.zeros(2, dtype=torch.int64, device=dev), None, 6.0, 1.0,
+                       _cabi.DH_MODE_FRESH)
+    assert float(heat.abs().max()) == 0.0
+    # labels out of range never write out of bounds: skipped and counted
+    C = 3
+    lab = torch.tensor([[0, 1, 2, 3, -1, 7, 0, 1, 2, 0, 1]], dtype=torch.int32, device=dev)
+    guard = torch.full((1 + 2, C, H, W), 2.0, device=dev)
+    status = torch.zeros(4, dtype=torch.int32, device=dev)
+    _cabi.draw_batched(cabi, guard[1:2], c, r, torch.tensor([n], device=dev), lab, 6.0, 1.0, _cabi.DH_MODE_FRESH, status)
+    assert float(guard[0].min()) == 2.0 and float(guard[2].min()) == 2.0
+    assert status.tolist()[0] == 3
+    want = np.zeros((1, C, H, W), np.float32)
+    oracle.draw_batched(want, objs[None, :, :2], objs[None, :, 2], np.array([n]), 6.0, 1.0, lab.cpu().numpy())
+    assert np.abs(guard[1:2].cpu().numpy() - want).max() <= 1e-6
+    # flat entry: bad plane indices skipped and counted; big N goes through the counting-sort path
+    rng = np.random.default_rng(5)
+    N, M = 20000, 300
+    fc = np.stack([rng.integers(-5, W + 5, N), rng.integers(-5, H + 5, N)], 1).astype(np.int32)
+    fr = rng.integers(0, 6, N).astype(np.int32)
+    fi = rng.integers(-2, M + 2, N).astype(np.int32)
+    want = np.zeros((M, H, W), np.float32)
+    oracle.draw_flat(want, fc, fr, fi, 6.0, 1.0)
+    status.zero_()
+    heat = torch.zeros((M, H, W), device=dev)
+    _cabi.draw_flat(cabi, heat, _dev(fc, dev), _dev(fr, dev), _dev(fi, dev), 6.0, 1.0, _cabi.DH_MODE_ACCUMULATE, status)
+    got = heat.cpu().numpy()
+    assert np.abs(got - want).max() <= 1e-6 and np.array_equal(got > 0, want > 0)
+    assert status.tolist()[1] == int(((fi < 0) | (fi >= M)).sum())
+
+
+def test_more_objects_than_the_shared_list(cabi, cuda_dev, oracle):
+    """> 1024 overlapping objects in one plane: the renderer falls back to chunked passes over the source."""
+    rng = np.random.default_rng(9)
+    T, H, W = 3000, 64, 96
+    c = np.stack([rng.integers(0, W, T), rng.integers(0, H, T)], 1).astype(np.int32)[None]
+    r = rng.integers(20, 70, T).astype(np.int32)[None]
+    want = np.zeros((1, H, W), np.float32)
+    oracle.draw_batched(want, c, r, np.array([T]), 6.0, 1.0)
+    heat = torch.empty((1, H, W), device=cuda_dev)
+    _cabi.draw_batched(cabi, heat, _dev(c, cuda_dev), _dev(r, cuda_dev), torch.tensor([T], device=cuda_dev), None, 6.0, 1.0,
+                       _cabi.DH_MODE_FRESH)
+    assert np.abs(heat.cpu().numpy() - want).max() <= 1e-6
+
+
+def test_host_buffer_entry(cabi, cuda_dev, oracle):
+    w = workloads.make("cfg2")
+    cfg = w.cfg
+    ci, ri = oracle.radius_center(w.centers_f, w.bboxes_f, cfg.osf)
+    want = np.zeros((w.B, cfg.C, cfg.H, cfg.W), np.float32)
+    oracle.draw_batched(want, ci, ri, w.sizes, 6.0, 1.0, w.labels)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    cf, bf, s, lab = pin(w.centers_f), pin(w.bboxes_f), pin(w.sizes), pin(w.labels)
+    args = (w.B, w.T, cfg.C, cfg.H, cfg.W)
+    st = _cabi.stream_ptr()
+    for staging, chunk in ((1, 3), (0, 5), (1, 0)):
+        nbytes = cabi.dh_host_scratch_bytes(*args, 1, chunk, staging)
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=cuda_dev)
+        out = torch.full(want.shape, 3.0).pin_memory()
+        ck = torch.zeros(3, dtype=torch.int64).pin_memory()
+        hd = None if staging else torch.empty(want.shape, device=cuda_dev)
+        rc = cabi.dh_draw_heatmap_batched_from_boxes_host(
+            st, _cabi.ptr(out), _cabi.ptr(hd), _cabi.ptr(ck), _cabi.ptr(cf), _cabi.ptr(bf), float(cfg.osf), _cabi.ptr(s),
+            _cabi.ptr(lab), *args, 6.0, 1.0, _cabi.ptr(scratch), nbytes, chunk)
+        _cabi.check(cabi, rc, "host entry")
+        torch.cuda.synchronize()
+        assert np.abs(out.numpy() - want).max() <= 1e-6 and np.array_equal(out.numpy() > 0, want > 0)
+        assert np.array_equal(ck.numpy(), oracle.digest_numpy(out.numpy()))
+        if hd is not None:
+            assert np.array_equal(hd.cpu().numpy(), out.numpy())
+    # device-resident result + digest only
+    nbytes = cabi.dh_host_scratch_bytes(*args, 1, 0, 0)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=cuda_dev)
+    hd = torch.empty(want.shape, device=cuda_dev)
+    ck2 = torch.zeros(3, dtype=torch.int64).pin_memory()
+    rc = cabi.dh_draw_heatmap_batched_from_boxes_host(
+        st, None, _cabi.ptr(hd), _cabi.ptr(ck2), _cabi.ptr(cf), _cabi.ptr(bf), float(cfg.osf), _cabi.ptr(s), _cabi.ptr(lab),
+        *args, 6.0, 1.0, _cabi.ptr(scratch), nbytes, 0)
+    _cabi.check(cabi, rc, "host entry (device result)")
+    torch.cuda.synchronize()
+    assert np.array_equal(ck2.numpy(), ck.numpy())
+    assert cabi.dh_draw_heatmap_batched_from_boxes_host(
+        st, None, _cabi.ptr(hd), None, _cabi.ptr(cf), _cabi.ptr(bf), float(cfg.osf), _cabi.ptr(s), _cabi.ptr(lab), *args,
+        6.0, 1.0, _cabi.ptr(scratch), 16, 0) == _cabi.DH_ERR_WORKSPACE_TOO_SMALL
+
+
+def test_expf_is_monotone_and_close_to_correctly_rounded(cabi, cuda_dev):
+    """Exhaustive over every fp32 in [-104, -0]: the renderer's expf is monotone (so one expf per pixel is bit-identical
+    to max over per-object expf) and within 2 ulp of the correctly rounded value (the oracle's exp)."""
+    lo, hi = 0x80000000, 0xC2D00000  # -0.0 ... -104.0 (bit patterns increase as the value decreases)
+    step = 1 << 26
+    prev_last = None
+    worst = 0
+    for start in range(lo, hi, step):
+        n = min(step, hi - start) + 1
+        out = torch.empty(n, device=cuda_dev)
+        _cabi.check(cabi, cabi.dh_expf_probe(_cabi.stream_ptr(), ctypes.c_uint32(start), n, _cabi.ptr(out)), "expf_probe")
+        assert bool((out[1:] <= out[:-1]).all()), "expf not monotone"
+        if prev_last is not None:
+            assert float(out[0]) <= prev_last
+        prev_last = float(out[-1])
+        x = (torch.arange(n, device=cuda_dev, dtype=torch.int64) + start).to(torch.int32)  # wraps to the same bits
+        ref = torch.exp(x.view(torch.float32).double()).float()
+        normal = ref >= 1.1754944e-38
+        d = (out.view(torch.int32).long() - ref.view(torch.int32).long()).abs()[normal]
+        worst = max(worst, int(d.max()))
+        del out, x, ref, d
+    assert worst <= 2, worst
