@@ -422,6 +422,10 @@ __global__ void __launch_bounds__(kThreads) render_kernel(const RenderParams p) 
     }
 }
 
+}  // namespace dh
+#include "dh_rows_kernel.cuh"
+namespace dh {
+
 // ------------------------------------------------------------------------------------------------
 // Flat API binning: counting sort of objects by plane (match_any-aggregated counters).
 __global__ void __launch_bounds__(256) csr_count_kernel(const int32_t* __restrict__ plane_idx, long long n, long long m,
@@ -590,6 +594,50 @@ static void make_plan(RenderParams& p, int px, long long max_ctas) {
     p.total_units = p.num_planes * p.units_per_plane;
 }
 
+// Plan of the rows kernel: band = R whole rows (<= kTileBytes, a multiple of 8 rows when possible so the 8 warps
+// get equal shares), unit = up to 64 bands; enough units for >= 4 per resident CTA when the problem allows it.
+static void make_rows_plan(RenderParams& p, long long max_ctas) {
+    int R = kTilePx / p.W;
+    if (R >= 8) R &= ~7;
+    if (R > p.H) R = p.H;
+    if (R < 1) R = 1;
+    p.band_rows = R;
+    p.bands_y = (p.H + R - 1) / R;
+    p.bands_x = 1;
+    p.bands_per_plane = p.bands_y;
+    const long long total_bands = p.num_planes * p.bands_y;
+    long long bpu = total_bands / (4 * max_ctas);
+    if (bpu < 1) bpu = 1;
+    if (bpu > 64) bpu = 64;
+    if (bpu > p.bands_y) bpu = p.bands_y;
+    p.bands_per_unit = (int)bpu;
+    p.units_per_plane = (p.bands_y + p.bands_per_unit - 1) / p.bands_per_unit;
+    p.bands_per_unit = (p.bands_y + p.units_per_plane - 1) / p.units_per_plane;  // balance the last unit
+    p.units_per_plane = (p.bands_y + p.bands_per_unit - 1) / p.bands_per_unit;
+    p.total_units = p.num_planes * p.units_per_plane;
+}
+
+template <bool ACCUM, int SRC>
+static int launch_rows(cudaStream_t stream, RenderParams& p, int sms) {
+    static int occ = 0;  // per instantiation; also marks "attribute set"
+    if (occ == 0) {
+        cudaError_t e = cudaFuncSetAttribute(rows_kernel<ACCUM, SRC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kRowsSmemBytes);
+        if (e != cudaSuccess) return (int)e;
+        int nb = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, rows_kernel<ACCUM, SRC>, kRowsThreads, kRowsSmemBytes);
+        if (e != cudaSuccess) return (int)e;
+        occ = nb > 0 ? nb : 1;
+    }
+    const long long max_ctas = (long long)sms * occ;
+    make_rows_plan(p, max_ctas);
+    if (p.total_units == 0) return DH_OK;
+    const int grid = (int)(p.total_units < max_ctas ? p.total_units : max_ctas);
+    rows_kernel<ACCUM, SRC><<<grid, kRowsThreads, kRowsSmemBytes, stream>>>(p);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return (int)cudaGetLastError();
+}
+
 template <int SRC>
 static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
     DeviceInfo di;
@@ -597,6 +645,10 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
     if (st != DH_OK) return st;
     const bool vec = (p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0);
     const bool accum = (mode == DH_MODE_ACCUMULATE);
+    if (vec && p.W <= kTilePx) {  // main path: row-owner warps + shared-memory tiles + bulk stores
+        return accum ? launch_rows<true, SRC>(stream, p, di.sms) : launch_rows<false, SRC>(stream, p, di.sms);
+    }
+    // generic path (W not a multiple of 4, misaligned base, or rows wider than a tile): pixel-owner threads
     static int occ[2][2] = {{0, 0}, {0, 0}};
     int& o = occ[vec][accum];
     if (vec && accum) st = blocks_per_sm(render_kernel<4, true, SRC>, o);

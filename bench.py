@@ -302,6 +302,26 @@ def run_ours(args):
                 "traffic": traffic, "kernel": "dh::render_kernel<4,false,SRC_BOXES>", "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": launch_ms,
                 "frac_of_nominal_8TBs": achieved / 8000.0}
+    # ---- write-only ceilings on the same buffer (not part of any reported throughput) ----
+    ceil = {}
+    if rank == 0:
+        buf = heats[0]
+        for name, fn in (("fill_probe_st_v4", lambda: lib.dh_fill_probe(sp, _cabi.ptr(buf), buf.numel() * 4)),
+                         ("torch_zero_", lambda: buf.zero_())):
+            reps = max(3, min(50, int(2e9 // max(out_bytes, 1))))
+            for _ in range(3):
+                fn()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            a.record(stream)
+            for _ in range(reps):
+                fn()
+            b.record(stream)
+            torch.cuda.synchronize()
+            ceil[name + "_GBps"] = out_bytes * reps / (a.elapsed_time(b) * 1e-3) / 1e9
+        step(0)  # restore a rendered result in buffer 0
+        torch.cuda.synchronize()
+    roofline["write_only_ceilings"] = ceil
     return dict(torch=torch, lib=lib, _cabi=_cabi, dist=dist, dev=dev, rank=rank, world=world, w=w, w_all=w_all, lo=lo,
                 host=(h_cf, h_bf, h_sz, h_lab), heats=heats, value=value, ms_step=ms_step, launches=launches,
                 roofline=roofline, digest=digest, sampler=sampler, warm=warm, barrier=barrier)

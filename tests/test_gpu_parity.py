@@ -26,12 +26,16 @@ def _ulp(a, b):
     return int(np.abs(a - b).max()) if a.size else 0
 
 
-def _assert_parity(got, want, what=""):
+def _assert_parity(got, want, what="", max_ulp=2):
+    """max_ulp applies against the fp32 "spec" oracle (same arithmetic up to the exp; libdevice expf is within 2 ulp
+    of correctly rounded). Against the reference's float64 CPU output only the absolute bar applies: rounding of the
+    fp32 exp argument (|arg| <= 9 at factor 6) alone moves small values by a few ulp."""
     got = got.cpu().numpy() if hasattr(got, "cpu") else got
     assert np.array_equal(got > 0, want > 0), f"{what}: touched-pixel mask differs"
     err = float(np.abs(got.astype(np.float64) - want.astype(np.float64)).max()) if got.size else 0.0
     assert err <= ABS_TOL, f"{what}: max abs err {err}"
-    assert _ulp(got, want) <= 2, f"{what}: ulp distance {_ulp(got, want)}"
+    if max_ulp is not None:
+        assert _ulp(got, want) <= max_ulp, f"{what}: ulp distance {_ulp(got, want)}"
 
 
 GOLD = ["ref_batched_20x50", "ref_batched_45x63", "ref_classwise_20x50", "ref_classwise_64x64"]
@@ -52,7 +56,7 @@ def test_golden_batched(cabi, cuda_dev, golden, oracle, name, sizes_dtype):
     heat = torch.zeros(g["heat"].shape, device=cuda_dev)
     _cabi.draw_batched(cabi, heat, c, r, s, lab, factor, k, _cabi.DH_MODE_ACCUMULATE)
     _assert_parity(heat, want, name + " accumulate vs oracle")
-    _assert_parity(heat, g["heat"], name + " accumulate vs reference CPU golden")
+    _assert_parity(heat, g["heat"], name + " accumulate vs reference CPU golden", max_ulp=None)
     # fresh mode overwrites garbage
     heat2 = torch.full(g["heat"].shape, 123.0, device=cuda_dev)
     _cabi.draw_batched(cabi, heat2, c, r, s, lab, factor, k, _cabi.DH_MODE_FRESH)
@@ -91,10 +95,10 @@ def test_golden_edges_and_flat_entry(cabi, cuda_dev, golden, oracle):
     for mode in (_cabi.DH_MODE_ACCUMULATE, _cabi.DH_MODE_FRESH):
         heat = torch.zeros((n, H, W), device=cuda_dev)
         _cabi.draw_flat(cabi, heat, c, r, idx, factor, k, mode)
-        _assert_parity(heat, g["heat_each"], "edges, one plane per object")
+        _assert_parity(heat, g["heat_each"], "edges, one plane per object", max_ulp=None)
         heat1 = torch.zeros((1, H, W), device=cuda_dev)
         _cabi.draw_flat(cabi, heat1, c, r, torch.zeros_like(idx), factor, k, mode)
-        _assert_parity(heat1[0], g["heat_all"], "edges, all objects in one plane")
+        _assert_parity(heat1[0], g["heat_all"], "edges, all objects in one plane", max_ulp=None)
     heat_b = torch.zeros((1, H, W), device=cuda_dev)
     _cabi.draw_batched(cabi, heat_b, c[None].contiguous(), r[None].contiguous(),
                        torch.tensor([n], device=cuda_dev, dtype=torch.int32), None, factor, k)
@@ -109,13 +113,13 @@ def test_golden_reference_examples(cabi, cuda_dev, golden):
     c, r, s = _dev(g["centers"], cuda_dev), _dev(g["radii"], cuda_dev), _dev(g["sizes"], cuda_dev)
     heat = torch.zeros((B, H, W), device=cuda_dev)
     _cabi.draw_batched(cabi, heat, c, r, s, None, factor, k)
-    _assert_parity(heat, g["heat"], "examples")
+    _assert_parity(heat, g["heat"], "examples", max_ulp=None)
     heat_c = torch.zeros((B, C, H, W), device=cuda_dev)
     _cabi.draw_batched(cabi, heat_c, c, r, s, _dev(g["labels"], cuda_dev), factor, k)
     planes = heat_c.reshape(B * C, H, W).cpu().numpy()
     nz = np.nonzero(planes.reshape(B * C, -1).max(axis=1) > 0)[0]
     assert np.array_equal(nz, g["heat_cls_planes"])
-    _assert_parity(planes[nz], g["heat_cls_values"], "examples classwise")
+    _assert_parity(planes[nz], g["heat_cls_values"], "examples classwise", max_ulp=None)
 
 
 @pytest.mark.parametrize("name,B", [("cfg1", None), ("cfg2", None), ("cfg3", None), ("cfg4", 4), ("cfg5", 24)])

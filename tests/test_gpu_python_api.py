@@ -125,7 +125,7 @@ def test_error_conventions_on_device(cuda_dev):
     with pytest.raises(RuntimeError, match="contiguous"):
         dh.draw_heatmap_batched(heat.transpose(1, 2), rb(c), rb(r))
     with pytest.raises(RuntimeError, match="heatmap must be of shape"):
-        dh.draw_heatmap_batched(heat[None], rb(c), rb(r))
+        dh.draw_heatmap_batched(heat[:, None].contiguous(), rb(c), rb(r))
     with pytest.raises(RuntimeError, match="batch_size"):
         dh.draw_heatmap_batched(torch.zeros((3, 8, 8), device=cuda_dev), rb(c), rb(r))
     with pytest.raises(RuntimeError, match="dtype"):
