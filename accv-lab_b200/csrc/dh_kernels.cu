@@ -424,6 +424,7 @@ __global__ void __launch_bounds__(kThreads) render_kernel(const RenderParams p) 
 
 }  // namespace dh
 #include "dh_rows_kernel.cuh"
+#include "dh_wrows_kernel.cuh"
 namespace dh {
 
 // ------------------------------------------------------------------------------------------------
@@ -638,6 +639,47 @@ static int launch_rows(cudaStream_t stream, RenderParams& p, int sms) {
     return (int)cudaGetLastError();
 }
 
+// Plan of the warp-rows kernel: row group = G whole rows (<= 2 KB), band = 8 groups (one per warp), unit <= 64 bands.
+static void make_wrows_plan(RenderParams& p, long long max_ctas) {
+    int G = kWMaxW / p.W;
+    if (G < 1) G = 1;
+    p.band_cols = G;  // rows per group (field reused)
+    p.band_rows = kWWarps * G;
+    p.bands_y = (p.H + p.band_rows - 1) / p.band_rows;
+    p.bands_x = 1;
+    p.bands_per_plane = p.bands_y;
+    const long long total_bands = p.num_planes * p.bands_y;
+    long long bpu = total_bands / (4 * max_ctas);
+    if (bpu < 1) bpu = 1;
+    if (bpu > 64) bpu = 64;
+    if (bpu > p.bands_y) bpu = p.bands_y;
+    p.units_per_plane = (int)((p.bands_y + bpu - 1) / bpu);
+    p.bands_per_unit = (p.bands_y + p.units_per_plane - 1) / p.units_per_plane;  // balance the last unit
+    p.units_per_plane = (p.bands_y + p.bands_per_unit - 1) / p.bands_per_unit;
+    p.total_units = p.num_planes * p.units_per_plane;
+}
+
+template <bool ACCUM, int SRC>
+static int launch_wrows(cudaStream_t stream, RenderParams& p, int sms) {
+    static int occ = 0;
+    if (occ == 0) {
+        cudaError_t e = cudaFuncSetAttribute(wrows_kernel<ACCUM, SRC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kWSmemBytes);
+        if (e != cudaSuccess) return (int)e;
+        int nb = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wrows_kernel<ACCUM, SRC>, kWThreads, kWSmemBytes);
+        if (e != cudaSuccess) return (int)e;
+        occ = nb > 0 ? nb : 1;
+    }
+    const long long max_ctas = (long long)sms * occ;
+    make_wrows_plan(p, max_ctas);
+    if (p.total_units == 0) return DH_OK;
+    const int grid = (int)(p.total_units < max_ctas ? p.total_units : max_ctas);
+    wrows_kernel<ACCUM, SRC><<<grid, kWThreads, kWSmemBytes, stream>>>(p);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return (int)cudaGetLastError();
+}
+
 template <int SRC>
 static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
     DeviceInfo di;
@@ -645,7 +687,10 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
     if (st != DH_OK) return st;
     const bool vec = (p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0);
     const bool accum = (mode == DH_MODE_ACCUMULATE);
-    if (vec && p.W <= kTilePx) {  // main path: row-owner warps + shared-memory tiles + bulk stores
+    if (vec && p.W <= kWMaxW) {  // main path: warp-autonomous row groups, per-warp staging + bulk stores
+        return accum ? launch_wrows<true, SRC>(stream, p, di.sms) : launch_wrows<false, SRC>(stream, p, di.sms);
+    }
+    if (vec && p.W <= kTilePx) {  // wide maps: block-cooperative bands + bulk stores
         return accum ? launch_rows<true, SRC>(stream, p, di.sms) : launch_rows<false, SRC>(stream, p, di.sms);
     }
     // generic path (W not a multiple of 4, misaligned base, or rows wider than a tile): pixel-owner threads

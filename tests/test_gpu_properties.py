@@ -235,3 +235,44 @@ def test_expf_is_monotone_and_close_to_correctly_rounded(cabi, cuda_dev):
         worst = max(worst, int(d.max()))
         del out, x, ref, d
     assert worst <= 2, worst
+
+
+@pytest.mark.parametrize("H,W,T", [(40, 1024, 300), (9, 4096, 50), (24, 640, 1500), (5, 8192, 40)])
+def test_wide_maps_use_the_block_cooperative_and_generic_kernels(cabi, cuda_dev, oracle, H, W, T):
+    """W in (512, 4096] -> rows_kernel (block-cooperative bands); W > 4096 -> generic pixel-owner kernel.
+    T = 1500 exceeds the shared list (multi-pass with a persistent tile)."""
+    rng = np.random.default_rng(H * W + T)
+    B, C = 3, 2
+    c = np.stack([rng.integers(-20, W + 20, (B, T)), rng.integers(-5, H + 5, (B, T))], 2).astype(np.int32)
+    r = rng.integers(0, 40, (B, T)).astype(np.int32)
+    lab = rng.integers(0, C, (B, T)).astype(np.int32)
+    sizes = np.array([T, T // 2, 0], np.int64)
+    for k, init in ((1.0, 0.0), (0.7, 0.2), (-1.0, 0.0)):
+        want = np.full((B, C, H, W), init, np.float32)
+        oracle.draw_batched(want, c, r, sizes, 6.0, k, lab)
+        heat = torch.full((B, C, H, W), init, device=cuda_dev)
+        _cabi.draw_batched(cabi, heat, _dev(c, cuda_dev), _dev(r, cuda_dev), _dev(sizes, cuda_dev), _dev(lab, cuda_dev), 6.0, k)
+        got = heat.cpu().numpy()
+        assert np.abs(got - want).max() <= 1e-6 and np.array_equal(got > 0, want > 0), (k, init)
+        if init == 0.0:
+            fresh = torch.full((B, C, H, W), 7.0, device=cuda_dev)
+            _cabi.draw_batched(cabi, fresh, _dev(c, cuda_dev), _dev(r, cuda_dev), _dev(sizes, cuda_dev), _dev(lab, cuda_dev),
+                               6.0, k, _cabi.DH_MODE_FRESH)
+            assert torch.equal(fresh, heat)
+
+
+@pytest.mark.parametrize("H,W", [(16, 4), (300, 8), (33, 128), (7, 512), (64, 256)])
+def test_small_and_odd_shapes_on_the_warp_kernel(cabi, cuda_dev, oracle, H, W):
+    """Row groups of several rows (W < 512), partial last bands/groups, H smaller than a band."""
+    rng = np.random.default_rng(H * 1000 + W)
+    B, T = 5, 40
+    c = np.stack([rng.integers(-3, W + 3, (B, T)), rng.integers(-3, H + 3, (B, T))], 2).astype(np.int32)
+    r = rng.integers(0, 12, (B, T)).astype(np.int32)
+    sizes = rng.integers(0, T + 1, B).astype(np.int64)
+    want = np.zeros((B, H, W), np.float32)
+    oracle.draw_batched(want, c, r, sizes, 6.0, 1.0)
+    for mode in (_cabi.DH_MODE_FRESH, _cabi.DH_MODE_ACCUMULATE):
+        heat = torch.zeros((B, H, W), device=cuda_dev) if mode == _cabi.DH_MODE_ACCUMULATE else torch.full((B, H, W), 3.0, device=cuda_dev)
+        _cabi.draw_batched(cabi, heat, _dev(c, cuda_dev), _dev(r, cuda_dev), _dev(sizes, cuda_dev), None, 6.0, 1.0, mode)
+        got = heat.cpu().numpy()
+        assert np.abs(got - want).max() <= 1e-6 and np.array_equal(got > 0, want > 0), mode
