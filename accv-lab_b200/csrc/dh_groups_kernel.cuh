@@ -1,0 +1,471 @@
+// dh_groups_kernel.cuh — the main renderer (maps up to kGMaxW pixels wide: every BASELINE config).
+// Included by dh_kernels.cu after dh_rows_kernel.cuh (shares ObjI, load_slot, make_obji, finalize_row, PTX wrappers).
+//
+// Replaces the reference's one-thread-per-object renderer with its global CAS loop per pixel
+// (/root/reference/packages/draw_heatmap/accvlab/draw_heatmap/include/draw_heatmap_cuda_kernel.cuh:26-109) by an
+// OUTPUT-partitioned one. What the measurements behind it said (profiles/micro/*.cu, profiles/r01_*):
+//   * the same stores run at 7.0-7.4 TB/s when work is handed out in address order by the block scheduler and at
+//     6.1 TB/s from a static persistent grid-stride loop  -> ONE CTA PER UNIT, flat grid;
+//   * the previous kernel was instruction-issue bound (64 % issue-active, ~300 warp instructions per touched row)
+//     -> rows nobody touches cost nothing per row, touched rows take a register-only path when <= 2 objects hit them.
+//
+// Geometry: a row group = G whole rows of one plane (one contiguous byte range <= kGStageCap); a unit = up to 64
+// consecutive groups of one plane (~192 KB). Per unit:
+//   K1/K2  the sample's T slots are scanned once (all loads issued up front), radius/centre computed when the source
+//          is float boxes, objects culled against the unit rows and compacted with warp ballot + popc prefix into a
+//          shared-memory list; every object ORs the groups it overlaps into a 64-bit occupancy mask.
+//   K4a    FRESH: runs of untouched groups leave as cp.async.bulk (shared -> global, SASS UBLKCP) from a constant
+//          zero tile: no per-row work at all.
+//   K3     touched groups are striped over the 8 warps (group g -> warp g % 8). With <= 32 objects in the unit every
+//          lane keeps one list entry in registers for the whole unit, so the per-group hit test is a compare + ballot.
+//            sparse path (<= 2 hits): per 32-pixel chunk of the hit span each lane evaluates its pixel for both
+//              objects in registers (min of m = (i^2+j^2)/var) and applies ONE expf: no shared-memory read-modify-write;
+//            dense path: objects are swept into the staging rows as order-preserving uints (max == min m), then the
+//              span union is finalised in place with one expf per touched pixel.
+//   K4b    FRESH: the staging buffer (G rows, final fp32 values, zeros elsewhere) leaves with one bulk store issued by
+//          the warp itself; two buffers per warp alternate. Buffers are all-zero whenever idle: after the copy engine
+//          has read one, only the span that was written is cleared.
+//          ACCUMULATE (reference semantics): touched pixels only are read-max-written in place with plain ld/st.
+// No block barrier after the list build; no atomics on the heatmap anywhere.
+#pragma once
+
+namespace dh {
+
+#ifndef DH_G_MINB
+#define DH_G_MINB 3  // resident CTAs per SM the register budget is cut for
+#endif
+#ifndef DH_G_STAGE_CAP
+#define DH_G_STAGE_CAP 4096
+#endif
+constexpr int kGThreads = 256;
+constexpr int kGWarps = kGThreads / 32;
+constexpr int kGStageCap = DH_G_STAGE_CAP;  // bytes of one staging buffer (one row group)
+constexpr int kGMaxW = kGStageCap / 4;      // widest map served by this kernel
+constexpr int kGZeroBytes = 8192;           // constant zero tile
+constexpr int kGCap = 512;                  // unit list capacity
+constexpr int kGMaxGroups = 64;             // groups per unit (bits of the occupancy mask)
+
+// dynamic shared memory: zero tile | 8 warps x 2 staging buffers of `stage` bytes | unit list
+__host__ __device__ constexpr size_t groups_smem_bytes(int stage) {
+    return (size_t)kGZeroBytes + (size_t)kGWarps * 2 * (size_t)stage + (size_t)kGCap * sizeof(ObjI);
+}
+
+__device__ __forceinline__ unsigned enc_m(float m, bool kneg) {
+    const unsigned b = __float_as_uint(m);
+    return kneg ? b + 1u : ~b;
+}
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {  // splitmix64 finaliser (== dh_host.cu)
+    z += 0x9e3779b97f4a7c15ull;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+
+struct Digest {
+    unsigned long long bits = 0, hash = 0, cnt = 0;
+    __device__ __forceinline__ void add(float v, long long index) {
+        bits += (unsigned long long)__float_as_uint(v);
+        if (v > 0.0f) {
+            hash += mix64((unsigned long long)index);
+            cnt += 1;
+        }
+    }
+};
+
+// Dense path, one object into the rows [y0, y0+nrows) held in `buf` (row stride W). Warp-collective.
+__device__ __forceinline__ void sweep_obj(unsigned* __restrict__ buf, int y0, int nrows, int W, const ObjI& o, bool kneg,
+                                          int lane, int& ux0, int& ux1) {
+    const int x0 = max(o.x - o.r, 0), x1 = min(o.x + o.r, W - 1);
+    ux0 = min(ux0, x0);
+    ux1 = max(ux1, x1);
+    for (int rr = 0; rr < nrows; ++rr) {
+        const int dy = y0 + rr - o.y;
+        if (abs(dy) > o.r) continue;  // warp-uniform
+        unsigned* const rowp = buf + rr * W;
+        const float fdy = (float)dy;
+        const float fi = __fmul_rn(fdy, fdy);
+        if (x1 - x0 < 32) {  // narrow span: one pixel per lane
+            const int x = x0 + lane;
+            if (x <= x1) {
+                const float fdx = (float)(x - o.x);
+                const unsigned t = enc_m(__fmul_rn(__fadd_rn(fi, __fmul_rn(fdx, fdx)), o.w), kneg);
+                rowp[x] = max(rowp[x], t);
+            }
+        } else {  // wide span: four pixels per lane, 128-bit shared-memory accesses
+            for (int xv = (x0 & ~3) + 4 * lane; xv <= x1; xv += 128) {
+                uint4 q = *reinterpret_cast<uint4*>(rowp + xv);
+                unsigned* qc = reinterpret_cast<unsigned*>(&q);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int x = xv + c;
+                    const float fdx = (float)(x - o.x);
+                    const unsigned t = enc_m(__fmul_rn(__fadd_rn(fi, __fmul_rn(fdx, fdx)), o.w), kneg);
+                    if (x >= x0 && x <= x1) qc[c] = max(qc[c], t);
+                }
+                *reinterpret_cast<uint4*>(rowp + xv) = q;
+            }
+        }
+    }
+}
+
+// Dense path, K4: the span union of one staged row, one expf per touched pixel (cuh:45), in place.
+template <bool ACCUM, bool DIGEST>
+__device__ __forceinline__ void finish_row(unsigned* __restrict__ rowp, float* __restrict__ grow, long long gindex, int x0,
+                                           int x1, bool kneg, float k, int lane, Digest& dg) {
+    for (int x = x0 + lane; x <= x1; x += 32) {
+        const unsigned t = rowp[x];
+        if (t != 0u) {
+            const float m = __uint_as_float(kneg ? t - 1u : ~t);
+            const float v = __fmul_rn(expf(-m), k);
+            if constexpr (ACCUM) {
+                rowp[x] = 0u;  // the staging row is scratch here: back to all-zero
+                const float g = grow[x];
+                if (!(g >= v)) grow[x] = v;  // cuh:30: keep old iff old >= v
+            } else {
+                const float f = (0.0f >= v) ? 0.0f : v;  // max-blend into the fused zero-init
+                rowp[x] = __float_as_uint(f);
+                if constexpr (DIGEST) dg.add(f, gindex + x);
+            }
+        }
+    }
+}
+
+// Sparse path: at most two objects (A, and B when hasB) overlap the group's rows. Register-only evaluation, 32 pixels
+// at a time over the span the row is hit in; arithmetic of cuh:45 with the sign pulled out of the exponential:
+//   k >= 0: max_o k*expf(-m_o) = k*expf(-min_o m_o);  k < 0: the max picks max_o m_o = -min_o(-m_o)
+// (expf is monotone: verified exhaustively on the device by tests/test_gpu_properties.py), so `ws` = +-1/var and one
+// fminf cover both signs; negation is exact, so every rounding is the reference's.
+template <bool ACCUM, bool DIGEST>
+__device__ __forceinline__ void sparse_group(unsigned* __restrict__ buf, float* __restrict__ gdst, long long gindex, int y0,
+                                             int nrows, int W, const ObjI& A, const ObjI& B, bool hasB, bool kneg, float k,
+                                             int lane, int& ux0, int& ux1, Digest& dg) {
+    const int ax0 = max(A.x - A.r, 0), ax1 = min(A.x + A.r, W - 1);
+    const int bx0 = max(B.x - B.r, 0), bx1 = min(B.x + B.r, W - 1);
+    const float aw = kneg ? -A.w : A.w, bw = kneg ? -B.w : B.w;
+    for (int rr = 0; rr < nrows; ++rr) {
+        const int dya = y0 + rr - A.y, dyb = y0 + rr - B.y;
+        const bool inA = abs(dya) <= A.r, inB = hasB && abs(dyb) <= B.r;  // warp-uniform
+        if (!(inA || inB)) continue;
+        const float fa = (float)dya, fb = (float)dyb;
+        const float fia = __fmul_rn(fa, fa), fib = __fmul_rn(fb, fb);
+        const int rx0 = inA ? (inB ? min(ax0, bx0) : ax0) : bx0;
+        const int rx1 = inA ? (inB ? max(ax1, bx1) : ax1) : bx1;
+        ux0 = min(ux0, rx0);
+        ux1 = max(ux1, rx1);
+        for (int xb = rx0; xb <= rx1; xb += 32) {
+            const int x = xb + lane;
+            const int dxa = x - A.x, dxb = x - B.x;
+            float acc = 0.0f;
+            bool touched = false;
+            if (inA && abs(dxa) <= A.r) {
+                const float fdx = (float)dxa;
+                acc = __fmul_rn(__fadd_rn(fia, __fmul_rn(fdx, fdx)), aw);
+                touched = true;
+            }
+            if (inB && abs(dxb) <= B.r) {
+                const float fdx = (float)dxb;
+                const float m = __fmul_rn(__fadd_rn(fib, __fmul_rn(fdx, fdx)), bw);
+                acc = touched ? fminf(acc, m) : m;
+                touched = true;
+            }
+            if (touched && x <= rx1) {
+                const float v = __fmul_rn(expf(kneg ? acc : -acc), k);  // = expf(-m) * k
+                if constexpr (ACCUM) {
+                    float* const gp = gdst + (long long)rr * W + x;
+                    const float g = *gp;
+                    if (!(g >= v)) *gp = v;  // cuh:30
+                } else {
+                    const float f = (0.0f >= v) ? 0.0f : v;
+                    buf[rr * W + x] = __float_as_uint(f);
+                    if constexpr (DIGEST) dg.add(f, gindex + (long long)rr * W + x);
+                }
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ ObjI shfl_obj(const ObjI& o, int src) {
+    ObjI r;
+    r.x = __shfl_sync(0xffffffffu, o.x, src);
+    r.y = __shfl_sync(0xffffffffu, o.y, src);
+    r.r = __shfl_sync(0xffffffffu, o.r, src);
+    r.w = __shfl_sync(0xffffffffu, o.w, src);
+    return r;
+}
+
+template <bool ACCUM, int SRC, bool DIGEST>
+__global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const RenderParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float4* const zero_tile = reinterpret_cast<float4*>(smem_raw);
+    const int stage = p.stage_bytes;  // G*W*4 rounded up to 128
+    ObjI* const s_unit = reinterpret_cast<ObjI*>(smem_raw + kGZeroBytes + kGWarps * 2 * stage);
+    __shared__ int s_cnt;
+    __shared__ unsigned long long s_mask;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned* const wbuf0 = reinterpret_cast<unsigned*>(smem_raw + kGZeroBytes + warp * 2 * stage);
+    unsigned* const wbuf1 = wbuf0 + stage / 4;
+    const bool kneg = p.k < 0.0f;
+    const int W = p.W, H = p.H, G = p.band_cols /* rows per group */;
+    const long long plane_elems = (long long)H * W;
+
+    {  // zero tile and staging buffers start all-zero (contiguous in shared memory)
+        const int n16 = (kGZeroBytes + kGWarps * 2 * stage) / 16;
+        for (int i = tid; i < n16; i += kGThreads) zero_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if constexpr (!ACCUM) fence_proxy_async();
+    }
+    int cur = 0;
+    int c0x0 = 1, c0x1 = 0, c1x0 = 1, c1x1 = 0;  // span written into wbuf0 / wbuf1 by their last use (empty)
+    Digest dg;
+
+    for (long long u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+        const long long plane = u / p.units_per_plane;
+        const int ug = (int)(u - plane * p.units_per_plane);
+        float* const plane_ptr = p.heat + plane * plane_elems;
+        const int uy0 = ug * p.bands_per_unit * G, uy1 = min(uy0 + p.bands_per_unit * G, H);
+        const int ngroups = (uy1 - uy0 + G - 1) / G;
+
+        long long src_base = 0;
+        int n = 0, cls = 0, nscan = 0;
+        bool count_skips = false;
+        if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+            const long long sample = plane / p.C;
+            cls = (int)(plane - sample * p.C);
+            long long ns = p.sizes_i64 ? __ldg(reinterpret_cast<const long long*>(p.sizes) + sample)
+                                       : (long long)__ldg(reinterpret_cast<const int*>(p.sizes) + sample);
+            ns = ns < 0 ? 0 : (ns > p.T ? p.T : ns);
+            n = (int)ns;
+            src_base = sample * p.T;
+            count_skips = (ug == 0 && cls == 0);
+            nscan = p.T;  // scan bound that does not depend on a load
+        } else if constexpr (SRC == SRC_CSR) {
+            const int o0 = p.csr_off[plane], o1 = p.csr_off[plane + 1];
+            src_base = o0;
+            n = o1 - o0;
+            count_skips = (ug == 0);
+            nscan = n;
+        } else {
+            n = (int)p.num_objects;
+            count_skips = (u == 0);
+            nscan = n;
+        }
+
+        // ---- K1/K2: unit list (ballot + popc-prefix compaction) and group-occupancy mask ------------------------
+        __syncthreads();  // every warp is done with the previous unit's list (and shared memory is initialised)
+        if (tid == 0) {
+            s_cnt = 0;
+            s_mask = 0ull;
+        }
+        __syncthreads();
+        for (int base = 0; base < nscan; base += kGThreads) {
+            const int t = base + tid;
+            ObjI o;
+            bool pred = false;
+            if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+                // Every load of the slot is issued before anything depends on it (the sample size was requested
+                // above): one global round trip per unit instead of size -> label -> box. Padded slots (t >= n) are
+                // valid memory in the RaggedBatch layout and are dropped after the fact (cuh:84).
+                if (t < p.T) {
+                    const long long i = src_base + t;
+                    int lab = cls;
+                    if (p.labels != nullptr) lab = __ldg(p.labels + i);
+                    int x = 0, y = 0, r = -1;
+                    if constexpr (SRC == SRC_BOXES) {
+                        const float2 c = __ldg(reinterpret_cast<const float2*>(p.centers_f) + i);
+                        const float4 b = __ldg(reinterpret_cast<const float4*>(p.bboxes_f) + i);
+                        if (lab == cls) radius_center_one(c.x, c.y, b.x, b.y, b.z, b.w, p.osf, x, y, r);
+                    } else {
+                        const int2 c = __ldg(reinterpret_cast<const int2*>(p.centers) + i);
+                        r = __ldg(p.radii + i);
+                        x = c.x;
+                        y = c.y;
+                    }
+                    if (t < n) {
+                        if (lab == cls)
+                            pred = make_obji(x, y, r, p.factor, uy0, uy1, W, o, p.status, count_skips);
+                        else if (count_skips && p.status && (lab < 0 || lab >= p.C))
+                            atomicAdd(&p.status->skipped_label, 1u);
+                    }
+                }
+            } else if (t < n) {
+                int x, y, r;
+                if (load_slot<SRC>(p, src_base, t, cls, plane, count_skips, x, y, r))
+                    pred = make_obji(x, y, r, p.factor, uy0, uy1, W, o, p.status, count_skips);
+            }
+            unsigned long long bits = 0ull;
+            if (pred) {
+                const int lo = (max(o.y - o.r, uy0) - uy0) / G, hi = (min(o.y + o.r, uy1 - 1) - uy0) / G;
+                bits = ((2ull << (hi - lo)) - 1ull) << lo;
+            }
+            const unsigned blo = __reduce_or_sync(0xffffffffu, (unsigned)bits);
+            const unsigned bhi = __reduce_or_sync(0xffffffffu, (unsigned)(bits >> 32));
+            if (lane == 0 && (blo | bhi)) atomicOr(&s_mask, ((unsigned long long)bhi << 32) | blo);
+            const unsigned bal = __ballot_sync(0xffffffffu, pred);
+            if (bal) {
+                int pos = 0;
+                if (lane == 0) pos = atomicAdd(&s_cnt, __popc(bal));
+                pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(bal & ((1u << lane) - 1u));
+                if (pred && pos < kGCap) s_unit[pos] = o;
+            }
+        }
+        __syncthreads();
+        const int ucnt = s_cnt;
+        const unsigned long long mask = s_mask;
+        const bool overflow = ucnt > kGCap;  // rare: warps then scan the source instead of the shared list
+        const int lim = overflow ? n : ucnt;
+        const bool small = ucnt <= 32;  // one list entry per lane, kept in registers for the whole unit
+        ObjI mine;
+        mine.x = mine.y = 0;
+        mine.r = -1;
+        mine.w = 0.f;
+        if (small && lane < ucnt) mine = s_unit[lane];
+
+        // ---- K4a FRESH: runs of untouched groups leave as bulk stores of the zero tile (warp w: groups 8w..8w+7) ---
+        if constexpr (!ACCUM) {
+            const int gbase = 8 * warp;
+            if (lane == 0 && gbase < ngroups) {
+                unsigned z = (unsigned)((~mask >> gbase) & 0xffull) & ((1u << min(8, ngroups - gbase)) - 1u);
+                while (z) {
+                    const int s = __ffs(z) - 1;
+                    const int run = __ffs(~(z >> s)) - 1;  // consecutive untouched groups starting at s
+                    z &= ~(((1u << run) - 1u) << s);
+                    const int r0 = uy0 + (gbase + s) * G, r1 = min(r0 + run * G, uy1);
+                    char* dst = reinterpret_cast<char*>(plane_ptr + (long long)r0 * W);
+                    int bytes = (r1 - r0) * W * 4;
+                    while (bytes > 0) {
+                        const int c = min(bytes, kGZeroBytes);
+                        bulk_store(dst, zero_tile, (unsigned)c);
+                        dst += c;
+                        bytes -= c;
+                    }
+                }
+                bulk_commit();
+            }
+        }
+
+        // ---- K3/K4b: touched groups, striped over the warps; no block barrier in here ------------------------------
+        unsigned long long gm = mask & (0x0101010101010101ull << warp);
+        while (gm) {
+            const int g = __ffsll((long long)gm) - 1;
+            gm &= gm - 1ull;
+            if (g >= ngroups) break;
+            const int y0 = uy0 + g * G;
+            const int nrows = min(G, uy1 - y0), y1 = y0 + nrows - 1;
+            float* const gdst = plane_ptr + (long long)y0 * W;
+            const long long gindex = p.digest_base + plane * plane_elems + (long long)y0 * W;
+            unsigned* const buf = cur ? wbuf1 : wbuf0;
+            if constexpr (!ACCUM) {
+                if (lane == 0) bulk_wait_read<1>();  // the store that last read `buf` is older than my latest one
+                __syncwarp();
+                const int cx0 = cur ? c1x0 : c0x0, cx1 = cur ? c1x1 : c0x1;
+                if (cx1 >= cx0) {  // back to all-zero: clear only what its last use wrote
+                    for (int rr = 0; rr < G; ++rr)
+                        for (int x = cx0 + lane; x <= cx1; x += 32) buf[rr * W + x] = 0u;
+                    __syncwarp();
+                }
+            }
+            int ux0 = W, ux1 = -1;
+            bool finish = false;  // dense path used: staged uints still need K4
+            if (small) {
+                const bool hit = (mine.r >= 0) && (mine.y + mine.r >= y0) && (mine.y - mine.r <= y1);
+                unsigned bal = __ballot_sync(0xffffffffu, hit);
+                const int nh = __popc(bal);
+                if (nh <= 2) {
+                    if (nh > 0) {
+                        const int sa = __ffs(bal) - 1;
+                        const unsigned rest = bal & (bal - 1u);
+                        const int sb = rest ? __ffs(rest) - 1 : sa;
+                        const ObjI A = shfl_obj(mine, sa), B = shfl_obj(mine, sb);
+                        sparse_group<ACCUM, DIGEST>(buf, gdst, gindex, y0, nrows, W, A, B, rest != 0u, kneg, p.k, lane, ux0,
+                                                    ux1, dg);
+                    }
+                } else {
+                    finish = true;
+                    while (bal) {
+                        const int src = __ffs(bal) - 1;
+                        bal &= bal - 1u;
+                        const ObjI ob = shfl_obj(mine, src);
+                        sweep_obj(buf, y0, nrows, W, ob, kneg, lane, ux0, ux1);
+                        __syncwarp();
+                    }
+                }
+            } else {
+                finish = true;
+                for (int base = 0; base < lim; base += 32) {
+                    const int e = base + lane;
+                    ObjI o;
+                    o.x = o.y = o.r = 0;
+                    o.w = 0.f;
+                    bool hit = false;
+                    if (e < lim) {
+                        if (!overflow) {
+                            o = s_unit[e];
+                            hit = (o.y + o.r >= y0) && (o.y - o.r <= y1);
+                        } else {
+                            int x, y, r;
+                            if (load_slot<SRC>(p, src_base, e, cls, plane, false, x, y, r))
+                                hit = make_obji(x, y, r, p.factor, y0, y1 + 1, W, o, nullptr, false);
+                        }
+                    }
+                    unsigned bal = __ballot_sync(0xffffffffu, hit);
+                    while (bal) {
+                        const int src = __ffs(bal) - 1;
+                        bal &= bal - 1u;
+                        const ObjI ob = shfl_obj(o, src);
+                        sweep_obj(buf, y0, nrows, W, ob, kneg, lane, ux0, ux1);
+                        __syncwarp();
+                    }
+                }
+            }
+            if (finish && ux1 >= ux0) {
+                for (int rr = 0; rr < nrows; ++rr)
+                    finish_row<ACCUM, DIGEST>(buf + rr * W, gdst + (long long)rr * W, gindex + (long long)rr * W, ux0, ux1,
+                                              kneg, p.k, lane, dg);
+            }
+            if constexpr (!ACCUM) {
+                fence_proxy_async();  // my generic-proxy writes to `buf` -> visible to the bulk-copy engine
+                __syncwarp();
+                if (lane == 0) {
+                    bulk_store(gdst, buf, (unsigned)(nrows * W * 4));
+                    bulk_commit();
+                }
+                if (cur) {
+                    c1x0 = ux0;
+                    c1x1 = ux1;
+                } else {
+                    c0x0 = ux0;
+                    c0x1 = ux1;
+                }
+                cur ^= 1;
+            } else {
+                __syncwarp();
+            }
+        }
+    }
+    if constexpr (!ACCUM) bulk_wait_read<0>();  // shared memory must outlive every bulk read issued by this thread
+    if constexpr (DIGEST) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            dg.bits += __shfl_xor_sync(0xffffffffu, dg.bits, d);
+            dg.hash += __shfl_xor_sync(0xffffffffu, dg.hash, d);
+            dg.cnt += __shfl_xor_sync(0xffffffffu, dg.cnt, d);
+        }
+        // one triple of global atomics per CTA (the three words are shared by the whole grid)
+        __shared__ unsigned long long s_dg[3][kGWarps];
+        if (lane == 0) {
+            s_dg[0][warp] = dg.bits;
+            s_dg[1][warp] = dg.hash;
+            s_dg[2][warp] = dg.cnt;
+        }
+        __syncthreads();
+        if (tid < 3 && p.digest != nullptr) {
+            unsigned long long t = 0;
+#pragma unroll
+            for (int w = 0; w < kGWarps; ++w) t += s_dg[tid][w];
+            if (t != 0ull) atomicAdd(p.digest + tid, t);
+        }
+    }
+}
+
+}  // namespace dh

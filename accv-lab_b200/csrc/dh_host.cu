@@ -207,15 +207,19 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
     const int64_t sample_elems = C * H * W;
     int st;
     if (!heatmap_host) {  // result stays on the device: one launch
-        st = dh_draw_heatmap_batched_from_boxes(stream, heatmap_device, d_centers, d_bboxes, osf, d_sizes, DH_SIZES_I64,
-                                                d_labels, B, T, C, H, W, factor, k, DH_MODE_FRESH, nullptr, nullptr,
-                                                nullptr);
-        if (st != DH_OK) return st;
-        if (checksum_host) {
-            st = dh_checksum(stream, heatmap_device, B * sample_elems, 0, d_ck);
-            if (st != DH_OK) return st;
-            DH_TRY(cudaMemcpyAsync(checksum_host, d_ck, 24, cudaMemcpyDeviceToHost, stream));
+        st = DH_ERR_UNSUPPORTED_SHAPE;
+        if (checksum_host)  // digest fused into the render launch: the heatmap is never re-read
+            st = dh_draw_heatmap_batched_from_boxes_digest(stream, heatmap_device, d_centers, d_bboxes, osf, d_sizes,
+                                                           DH_SIZES_I64, d_labels, B, T, C, H, W, factor, k, 0, d_ck,
+                                                           nullptr);
+        if (st == DH_ERR_UNSUPPORTED_SHAPE) {
+            st = dh_draw_heatmap_batched_from_boxes(stream, heatmap_device, d_centers, d_bboxes, osf, d_sizes,
+                                                    DH_SIZES_I64, d_labels, B, T, C, H, W, factor, k, DH_MODE_FRESH,
+                                                    nullptr, nullptr, nullptr);
+            if (st == DH_OK && checksum_host) st = dh_checksum(stream, heatmap_device, B * sample_elems, 0, d_ck);
         }
+        if (st != DH_OK) return st;
+        if (checksum_host) DH_TRY(cudaMemcpyAsync(checksum_host, d_ck, 24, cudaMemcpyDeviceToHost, stream));
         return DH_OK;
     }
 
@@ -232,14 +236,19 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
         const int64_t nb = (B - s0 < L.chunk) ? (B - s0) : L.chunk;
         cudaStream_t cs = ctx->s[i & 1];
         float* dst = staging ? (float*)(ws + L.off_stage[i & 1]) : heatmap_device + s0 * sample_elems;
-        st = dh_draw_heatmap_batched_from_boxes(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf, d_sizes + s0,
-                                                DH_SIZES_I64, has_labels ? d_labels + s0 * T : nullptr, nb, T, C, H, W,
-                                                factor, k, DH_MODE_FRESH, nullptr, nullptr, nullptr);
-        if (st != DH_OK) return st;
-        if (checksum_host) {
-            st = dh_checksum(cs, dst, nb * sample_elems, s0 * sample_elems, d_ck);
-            if (st != DH_OK) return st;
+        st = DH_ERR_UNSUPPORTED_SHAPE;
+        if (checksum_host)
+            st = dh_draw_heatmap_batched_from_boxes_digest(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
+                                                           d_sizes + s0, DH_SIZES_I64,
+                                                           has_labels ? d_labels + s0 * T : nullptr, nb, T, C, H, W,
+                                                           factor, k, s0 * sample_elems, d_ck, nullptr);
+        if (st == DH_ERR_UNSUPPORTED_SHAPE) {
+            st = dh_draw_heatmap_batched_from_boxes(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
+                                                    d_sizes + s0, DH_SIZES_I64, has_labels ? d_labels + s0 * T : nullptr,
+                                                    nb, T, C, H, W, factor, k, DH_MODE_FRESH, nullptr, nullptr, nullptr);
+            if (st == DH_OK && checksum_host) st = dh_checksum(cs, dst, nb * sample_elems, s0 * sample_elems, d_ck);
         }
+        if (st != DH_OK) return st;
         DH_TRY(cudaMemcpyAsync(heatmap_host + s0 * sample_elems, dst, (size_t)nb * sample_elems * 4,
                                cudaMemcpyDeviceToHost, cs));
     }

@@ -19,6 +19,7 @@
 //                         fused (FRESH mode writes zeros where nothing was drawn and never reads).
 // No tensor cores: this is HBM-write-bound byte work, not a contraction.
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <stdint.h>
 
 #include <atomic>
@@ -59,6 +60,9 @@ struct RenderParams {
     int C, T, H, W;
     int wunits;  // W / PX
     int band_rows, band_cols, bands_x, bands_y, bands_per_plane, bands_per_unit, units_per_plane;
+    int stage_bytes;  // groups_kernel: bytes of one per-warp staging buffer
+    unsigned long long* digest;  // optional fused result digest (FRESH groups_kernel only): bits, hash, count
+    long long digest_base;       // element index of heat[0] in the unsharded result
     long long total_units;
     float factor, k;
     dh_status* status;
@@ -424,7 +428,7 @@ __global__ void __launch_bounds__(kThreads) render_kernel(const RenderParams p) 
 
 }  // namespace dh
 #include "dh_rows_kernel.cuh"
-#include "dh_wrows_kernel.cuh"
+#include "dh_groups_kernel.cuh"
 namespace dh {
 
 // ------------------------------------------------------------------------------------------------
@@ -639,43 +643,68 @@ static int launch_rows(cudaStream_t stream, RenderParams& p, int sms) {
     return (int)cudaGetLastError();
 }
 
-// Plan of the warp-rows kernel: row group = G whole rows (<= 2 KB), band = 8 groups (one per warp), unit <= 64 bands.
-static void make_wrows_plan(RenderParams& p, long long max_ctas) {
-    int G = kWMaxW / p.W;
+// Tuning hooks (environment, read once): DH_G_UNIT_BYTES = target bytes per unit, DH_G_PERSISTENT=1 = static
+// grid-stride launch (kept for A/B measurements of the block-scheduler effect).
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 196608);
+static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
+
+// Plan of the groups kernel: row group = G whole rows (<= kGStageCap bytes), unit = up to 64 groups of one plane,
+// ~192 KB when the problem is large (amortises the per-unit list build; measured optimum on cfg5), smaller when it
+// is not, so that every resident CTA slot still sees several units.
+static void make_groups_plan(RenderParams& p, long long max_ctas) {
+    // rows per group: as many as a staging buffer holds while DH_G_MINB CTAs still fit the SM's shared memory
+    const long long smem_budget = (227ll * 1024) / DH_G_MINB - 1024;
+    const long long stage_budget = (smem_budget - (long long)groups_smem_bytes(0)) / (2 * kGWarps);
+    int G = (int)((stage_budget < kGStageCap ? stage_budget : kGStageCap) / (p.W * 4));
     if (G < 1) G = 1;
-    p.band_cols = G;  // rows per group (field reused)
-    p.band_rows = kWWarps * G;
-    p.bands_y = (p.H + p.band_rows - 1) / p.band_rows;
+    if (G > p.H) G = p.H;
+    p.band_cols = G;  // rows per group
+    p.band_rows = G;
+    const int groups_y = (p.H + G - 1) / G;
+    p.bands_y = groups_y;
     p.bands_x = 1;
-    p.bands_per_plane = p.bands_y;
-    const long long total_bands = p.num_planes * p.bands_y;
-    long long bpu = total_bands / (4 * max_ctas);
-    if (bpu < 1) bpu = 1;
-    if (bpu > 64) bpu = 64;
-    if (bpu > p.bands_y) bpu = p.bands_y;
-    p.units_per_plane = (int)((p.bands_y + bpu - 1) / bpu);
-    p.bands_per_unit = (p.bands_y + p.units_per_plane - 1) / p.units_per_plane;  // balance the last unit
-    p.units_per_plane = (p.bands_y + p.bands_per_unit - 1) / p.bands_per_unit;
+    p.bands_per_plane = groups_y;
+    const long long group_bytes = (long long)G * p.W * 4;
+    const long long total_groups = p.num_planes * groups_y;
+    long long gpu = total_groups / (4 * max_ctas);
+    const long long cap = (g_unit_bytes + group_bytes - 1) / group_bytes;
+    if (gpu > cap) gpu = cap;
+    if (gpu < kGWarps) gpu = kGWarps;  // at least one group per warp, however small the problem
+    if (gpu > kGMaxGroups) gpu = kGMaxGroups;
+    if (gpu > groups_y) gpu = groups_y;
+    p.units_per_plane = (int)((groups_y + gpu - 1) / gpu);
+    p.bands_per_unit = (groups_y + p.units_per_plane - 1) / p.units_per_plane;  // balance the last unit
+    p.units_per_plane = (groups_y + p.bands_per_unit - 1) / p.bands_per_unit;
     p.total_units = p.num_planes * p.units_per_plane;
+    p.stage_bytes = (int)((group_bytes + 127) & ~127ll);
 }
 
-template <bool ACCUM, int SRC>
-static int launch_wrows(cudaStream_t stream, RenderParams& p, int sms) {
-    static int occ = 0;
-    if (occ == 0) {
-        cudaError_t e = cudaFuncSetAttribute(wrows_kernel<ACCUM, SRC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)kWSmemBytes);
+template <bool ACCUM, int SRC, bool DIGEST>
+static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)groups_smem_bytes(kGStageCap));
         if (e != cudaSuccess) return (int)e;
-        int nb = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wrows_kernel<ACCUM, SRC>, kWThreads, kWSmemBytes);
-        if (e != cudaSuccess) return (int)e;
-        occ = nb > 0 ? nb : 1;
+        attr_set = true;
     }
-    const long long max_ctas = (long long)sms * occ;
-    make_wrows_plan(p, max_ctas);
+    const long long max_ctas = (long long)sms * DH_G_MINB;
+    make_groups_plan(p, max_ctas);
     if (p.total_units == 0) return DH_OK;
-    const int grid = (int)(p.total_units < max_ctas ? p.total_units : max_ctas);
-    wrows_kernel<ACCUM, SRC><<<grid, kWThreads, kWSmemBytes, stream>>>(p);
+    const size_t smem = groups_smem_bytes(p.stage_bytes);
+    // Flat grid: the block scheduler hands units out dynamically and in address order, which balances SMs that see
+    // different effective store bandwidth; a static grid-stride loop runs at the pace of the slowest SM (measured:
+    // 6.1 vs 7.0-7.4 TB/s for the same stores, profiles/micro/fill_bw3.cu). The kernel keeps its unit loop so a
+    // persistent launch stays possible (DH_G_PERSISTENT=1, and grids beyond 2^31-1 units).
+    long long g = p.total_units;
+    if (g_persistent && g > max_ctas) g = max_ctas;
+    if (g > 0x7fffffffll) g = 0x7fffffffll;
+    groups_kernel<ACCUM, SRC, DIGEST><<<(int)g, kGThreads, smem, stream>>>(p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return (int)cudaGetLastError();
 }
@@ -687,9 +716,12 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
     if (st != DH_OK) return st;
     const bool vec = (p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0);
     const bool accum = (mode == DH_MODE_ACCUMULATE);
-    if (vec && p.W <= kWMaxW) {  // main path: warp-autonomous row groups, per-warp staging + bulk stores
-        return accum ? launch_wrows<true, SRC>(stream, p, di.sms) : launch_wrows<false, SRC>(stream, p, di.sms);
+    if (vec && p.W <= kGMaxW) {  // main path: row groups striped over warps, per-warp staging + bulk stores
+        if (accum) return launch_groups<true, SRC, false>(stream, p, di.sms);
+        if (p.digest != nullptr) return launch_groups<false, SRC, true>(stream, p, di.sms);
+        return launch_groups<false, SRC, false>(stream, p, di.sms);
     }
+    if (p.digest != nullptr) return DH_ERR_UNSUPPORTED_SHAPE;  // fused digest exists on the main path only
     if (vec && p.W <= kTilePx) {  // wide maps: block-cooperative bands + bulk stores
         return accum ? launch_rows<true, SRC>(stream, p, di.sms) : launch_rows<false, SRC>(stream, p, di.sms);
     }
@@ -760,7 +792,8 @@ int dh_radius_center(void* stream, const float* centers_xy, const float* bboxes_
 static int batched_common(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
                           const float* centers_f, const float* bboxes_f, float osf, const void* nums_targets,
                           int nums_dtype, const int32_t* labels, int64_t B, int64_t T, int64_t C, int64_t H, int64_t W,
-                          float factor, float k, int mode, dh_status* status) {
+                          float factor, float k, int mode, dh_status* status, uint64_t* digest = nullptr,
+                          int64_t digest_base = 0) {
     if (B < 0 || T < 0) return DH_ERR_INVALID_ARGUMENT;
     if (mode != DH_MODE_ACCUMULATE && mode != DH_MODE_FRESH) return DH_ERR_INVALID_ARGUMENT;
     if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
@@ -791,6 +824,8 @@ static int batched_common(void* stream, float* heatmap, const int32_t* centers, 
     p.factor = factor;
     p.k = k;
     p.status = status;
+    p.digest = reinterpret_cast<unsigned long long*>(digest);
+    p.digest_base = digest_base;
     if (centers_f) return dh::launch_render<dh::SRC_BOXES>((cudaStream_t)stream, p, mode);
     return dh::launch_render<dh::SRC_BATCHED>((cudaStream_t)stream, p, mode);
 }
@@ -823,6 +858,20 @@ int dh_draw_heatmap_batched_from_boxes(void* stream, float* heatmap, const float
     return batched_common(stream, heatmap, nullptr, nullptr, centers_xy, bboxes_xyxy, out_size_factor, nums_targets,
                           nums_dtype, labels, batch_size, max_num_targets, num_classes, height, width,
                           diameter_to_sigma_factor, k_scale, mode, status);
+}
+
+int dh_draw_heatmap_batched_from_boxes_digest(void* stream, float* heatmap, const float* centers_xy,
+                                              const float* bboxes_xyxy, float out_size_factor,
+                                              const void* nums_targets, int nums_dtype, const int32_t* labels,
+                                              int64_t batch_size, int64_t max_num_targets, int64_t num_classes,
+                                              int64_t height, int64_t width, float diameter_to_sigma_factor,
+                                              float k_scale, int64_t index_base, uint64_t* digest_out3,
+                                              dh_status* status) {
+    if (!digest_out3) return DH_ERR_INVALID_ARGUMENT;
+    if (batch_size > 0 && max_num_targets > 0 && (!centers_xy || !bboxes_xyxy)) return DH_ERR_INVALID_ARGUMENT;
+    return batched_common(stream, heatmap, nullptr, nullptr, centers_xy, bboxes_xyxy, out_size_factor, nums_targets,
+                          nums_dtype, labels, batch_size, max_num_targets, num_classes, height, width,
+                          diameter_to_sigma_factor, k_scale, DH_MODE_FRESH, status, digest_out3, index_base);
 }
 
 // Flat path: direct scan when (units x objects) is small, else counting sort by plane.

@@ -299,7 +299,7 @@ def run_ours(args):
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "dh::wrows_kernel<false,SRC_BOXES>", "peak_source": peak_src,
+                "traffic": traffic, "kernel": "dh::groups_kernel<false,SRC_BOXES,false>", "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": launch_ms,
                 "frac_of_nominal_8TBs": achieved / 8000.0}
     # ---- write-only ceilings on the same buffer (not part of any reported throughput) ----

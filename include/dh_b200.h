@@ -112,6 +112,21 @@ int dh_draw_heatmap_batched_from_boxes(void* stream, float* heatmap, const float
                                        int64_t width, float diameter_to_sigma_factor, float k_scale, int mode,
                                        int32_t* centers_out, int32_t* radii_out, dh_status* status);
 
+/* dh_draw_heatmap_batched_from_boxes in DH_MODE_FRESH with the result digest FUSED into the render launch: while
+ * every touched pixel is finalised the kernel accumulates dh_checksum's three sums (see below; untouched pixels are
+ * +0.0f and contribute nothing) and adds them to `digest_out3` (DEVICE, 3 x uint64, zeroed or carried over by the
+ * caller) — the heatmap is not read back from HBM for it. `index_base` is the element index of heatmap[0] in the
+ * unsharded result (rank offset when a batch is split over GPUs). Equals dh_checksum(heatmap) bit for bit.
+ * Returns DH_ERR_UNSUPPORTED_SHAPE for shapes the main kernel does not serve (width % 4 != 0, width > 1024 or a
+ * heatmap base that is not 16-byte aligned): call the plain entry + dh_checksum then. */
+int dh_draw_heatmap_batched_from_boxes_digest(void* stream, float* heatmap, const float* centers_xy,
+                                              const float* bboxes_xyxy, float out_size_factor,
+                                              const void* nums_targets, int nums_dtype, const int32_t* labels,
+                                              int64_t batch_size, int64_t max_num_targets, int64_t num_classes,
+                                              int64_t height, int64_t width, float diameter_to_sigma_factor,
+                                              float k_scale, int64_t index_base, uint64_t* digest_out3,
+                                              dh_status* status);
+
 /* ---- flat entry (concatenated objects + per-object plane index) ----------------------
  * Replaces draw_heatmap_cuda(cudaStream_t, float*, const int*, const int*, const int*, int H, int W,
  *   float factor, float k, int N, int M) (draw_heatmap_cuda.cu:29-41; kernel cuh:51-74).
@@ -143,7 +158,8 @@ int dh_checksum(void* stream, const float* values, int64_t n, int64_t index_base
  *     chunks are rendered into two staging buffers inside `device_scratch`, so device memory use is bounded
  *     independent of B; otherwise they are rendered in place into heatmap_device [B,(C),H,W].
  *   - heatmap_host == NULL: heatmap_device must be non-NULL; one render launch, the result stays on the device.
- *   - checksum_host (optional, 3 x uint64, host): dh_checksum of the whole result, copied to the host.
+ *   - checksum_host (optional, 3 x uint64, host): dh_checksum of the whole result, copied to the host (computed
+ *     inside the render launch when the shape allows it, by a separate dh_checksum pass otherwise).
  * labels_host == NULL -> heatmap is [B,H,W] and num_classes is ignored. nums_targets_host is int64 [B].
  * chunk_samples <= 0 selects a default (about 64 MiB of output per chunk).
  * `device_scratch` (16-byte aligned) must hold dh_host_scratch_bytes(...) bytes for the same arguments.

@@ -34,6 +34,8 @@ SIGNATURES = {
     "dh_draw_heatmap_batched": (_i, [_p, _p, _p, _p, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f, _i, _p]),
     "dh_draw_heatmap_batched_from_boxes": (_i, [_p, _p, _p, _p, _f, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f,
                                                 _i, _p, _p, _p]),
+    "dh_draw_heatmap_batched_from_boxes_digest": (_i, [_p, _p, _p, _p, _f, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f,
+                                                       _f, _i64, _p, _p]),
     "dh_draw_heatmap_workspace_bytes": (_sz, [_i64, _i64]),
     "dh_draw_heatmap": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _i, _p, _sz, _p]),
     "dh_checksum": (_i, [_p, _p, _i64, _i64, _p]),
@@ -55,9 +57,10 @@ def declared_functions():
 
 
 def load() -> ctypes.CDLL:
-    if not os.path.exists(LIB_PATH):
-        raise RuntimeError(f"{LIB_PATH} is missing: run `python accv-lab_b200/build.py` (there is no CPU fallback)")
-    lib = ctypes.CDLL(LIB_PATH)
+    path = os.environ.get("DH_B200_LIB") or LIB_PATH  # override = A/B builds of the same ABI (tuning runs only)
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} is missing: run `python accv-lab_b200/build.py` (there is no CPU fallback)")
+    lib = ctypes.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype = res
@@ -116,6 +119,26 @@ def draw_from_boxes(lib, heat, centers_f, bboxes_f, osf, sizes, labels=None, fac
                                                 ptr(radii_out), None)
     check(lib, st, "dh_draw_heatmap_batched_from_boxes")
     return heat
+
+
+def draw_from_boxes_digest(lib, heat, centers_f, bboxes_f, osf, sizes, labels=None, factor=6.0, k=1.0, index_base=0,
+                           digest=None):
+    """FRESH render with the digest fused into the launch; returns the int64[3] device digest (wrapping uint64)."""
+    import torch
+
+    B, T = centers_f.shape[:2]
+    if labels is not None:
+        C, H, W = heat.shape[1:]
+    else:
+        C, (H, W) = 1, heat.shape[1:]
+    if digest is None:
+        digest = torch.zeros(3, dtype=torch.int64, device=heat.device)
+    tag = DH_SIZES_I64 if sizes.dtype == torch.int64 else DH_SIZES_I32
+    st = lib.dh_draw_heatmap_batched_from_boxes_digest(stream_ptr(), ptr(heat), ptr(centers_f), ptr(bboxes_f), osf,
+                                                       ptr(sizes), tag, ptr(labels), B, T, C, H, W, factor, k, index_base,
+                                                       ptr(digest), None)
+    check(lib, st, "dh_draw_heatmap_batched_from_boxes_digest")
+    return digest
 
 
 def draw_flat(lib, heat, centers, radii, idx, factor=6.0, k=1.0, mode=DH_MODE_ACCUMULATE, status=None):

@@ -237,10 +237,10 @@ def test_expf_is_monotone_and_close_to_correctly_rounded(cabi, cuda_dev):
     assert worst <= 2, worst
 
 
-@pytest.mark.parametrize("H,W,T", [(40, 1024, 300), (9, 4096, 50), (24, 640, 1500), (5, 8192, 40)])
+@pytest.mark.parametrize("H,W,T", [(40, 1024, 300), (9, 4096, 50), (24, 640, 1500), (5, 8192, 40), (12, 2048, 1500)])
 def test_wide_maps_use_the_block_cooperative_and_generic_kernels(cabi, cuda_dev, oracle, H, W, T):
-    """W in (512, 4096] -> rows_kernel (block-cooperative bands); W > 4096 -> generic pixel-owner kernel.
-    T = 1500 exceeds the shared list (multi-pass with a persistent tile)."""
+    """W <= 1024 -> groups_kernel (T = 1500 overflows its shared list: warps scan the source); W in (1024, 4096] ->
+    rows_kernel (block-cooperative bands; T = 1500: multi-pass with a persistent tile); W > 4096 -> generic kernel."""
     rng = np.random.default_rng(H * W + T)
     B, C = 3, 2
     c = np.stack([rng.integers(-20, W + 20, (B, T)), rng.integers(-5, H + 5, (B, T))], 2).astype(np.int32)
@@ -276,3 +276,55 @@ def test_small_and_odd_shapes_on_the_warp_kernel(cabi, cuda_dev, oracle, H, W):
         _cabi.draw_batched(cabi, heat, _dev(c, cuda_dev), _dev(r, cuda_dev), _dev(sizes, cuda_dev), None, 6.0, 1.0, mode)
         got = heat.cpu().numpy()
         assert np.abs(got - want).max() <= 1e-6 and np.array_equal(got > 0, want > 0), mode
+
+
+@pytest.mark.parametrize("H,W", [(232, 400), (64, 256), (50, 1024), (31, 36)])
+def test_sparse_register_path_all_signs_and_modes(cabi, cuda_dev, oracle, H, W):
+    """<= 2 objects per row group: the register-only path of groups_kernel (no staged read-modify-write), for
+    k > 0, k < 0 and k == 0, FRESH and ACCUMULATE into non-zero planes, clipped at every border."""
+    rng = np.random.default_rng(H * 7 + W)
+    B, T, C = 8, 3, 2
+    c = np.stack([rng.integers(-4, W + 4, (B, T)), rng.integers(-4, H + 4, (B, T))], 2).astype(np.int32)
+    r = rng.integers(0, 25, (B, T)).astype(np.int32)
+    lab = rng.integers(0, C, (B, T)).astype(np.int32)
+    sizes = rng.integers(0, T + 1, B).astype(np.int32)
+    args = (_dev(c, cuda_dev), _dev(r, cuda_dev), _dev(sizes, cuda_dev), _dev(lab, cuda_dev))
+    for k in (1.0, 0.8, -0.5, 0.0):
+        for init in (0.0, 0.3, -0.2):
+            want = np.full((B, C, H, W), init, np.float32)
+            oracle.draw_batched(want, c, r, sizes.astype(np.int64), 6.0, k, lab)
+            heat = torch.full((B, C, H, W), init, device=cuda_dev)
+            _cabi.draw_batched(cabi, heat, *args, 6.0, k)
+            got = heat.cpu().numpy()
+            assert np.abs(got - want).max() <= 1e-6 and np.array_equal(got > 0, want > 0), (k, init)
+        fresh = torch.full((B, C, H, W), 5.0, device=cuda_dev)
+        _cabi.draw_batched(cabi, fresh, *args, 6.0, k, _cabi.DH_MODE_FRESH)
+        zero = torch.zeros((B, C, H, W), device=cuda_dev)
+        _cabi.draw_batched(cabi, zero, *args, 6.0, k)
+        assert torch.equal(fresh, zero), k
+
+
+@pytest.mark.parametrize("name,nb", [("cfg1", None), ("cfg2", None), ("cfg3", 24), ("cfg4", 3)])
+def test_fused_digest_equals_checksum_pass(cabi, cuda_dev, name, nb):
+    """dh_draw_heatmap_batched_from_boxes_digest: the digest accumulated inside the render launch equals dh_checksum
+    of the rendered heatmap bit for bit (sparse and dense paths), and is additive over batch shards."""
+    w = workloads.make(name, B=nb)
+    cfg = w.cfg
+    cf, bf, s, lab = _upload(w, cuda_dev)
+    shape = (w.B, cfg.C, cfg.H, cfg.W)
+    plain = torch.empty(shape, device=cuda_dev)
+    _cabi.draw_from_boxes(cabi, plain, cf, bf, float(cfg.osf), s, lab, 6.0, 0.9)
+    want = _cabi.checksum(cabi, plain)
+    fused = torch.full(shape, 2.0, device=cuda_dev)
+    got = _cabi.draw_from_boxes_digest(cabi, fused, cf, bf, float(cfg.osf), s, lab, 6.0, 0.9)
+    assert torch.equal(fused, plain)
+    assert torch.equal(got, want), (got.tolist(), want.tolist())
+    assert int(want[2]) == int((plain > 0).sum())
+    sample_elems = cfg.C * cfg.H * cfg.W
+    d = torch.zeros(3, dtype=torch.int64, device=cuda_dev)
+    for g in range(2):
+        lo, hi = workloads.shard_range(w.B, g, 2)
+        part = torch.empty((hi - lo,) + shape[1:], device=cuda_dev)
+        _cabi.draw_from_boxes_digest(cabi, part, cf[lo:hi].contiguous(), bf[lo:hi].contiguous(), float(cfg.osf),
+                                     s[lo:hi].contiguous(), lab[lo:hi].contiguous(), 6.0, 0.9, lo * sample_elems, d)
+    assert torch.equal(d, want)
