@@ -185,6 +185,54 @@ __device__ __forceinline__ void sparse_group(unsigned* __restrict__ buf, float* 
     }
 }
 
+// ---- cluster launch control (sm_100): a resident CTA asks the hardware block scheduler for the index of a CTA of
+// this grid that has not been launched yet, cancels that launch and does its work itself. The grid still has one CTA
+// per unit and units are still handed out dynamically and in address order, but shared-memory set-up is paid once per
+// resident CTA and — the point — a CTA starts the next unit's list build while its bulk stores are still draining.
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "DH_MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DH_MBAR_DONE;\n"
+        "bra DH_MBAR_WAIT;\n"
+        "DH_MBAR_DONE:\n"
+        "}" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void clc_try_cancel(void* response16, unsigned long long* bar) {
+    asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];" ::"r"(
+                     smem_u32(response16)),
+                 "r"(smem_u32(bar))
+                 : "memory");
+}
+// returns true and the x index of the cancelled CTA, or false when the grid has no CTA left to hand out
+__device__ __forceinline__ bool clc_response(const void* response16, unsigned& ctaid_x) {
+    unsigned valid, x;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b128 r;\n"
+        "ld.shared.b128 r, [%2];\n"
+        "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p, r;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "mov.u32 %1, 0;\n"
+        "@p clusterlaunchcontrol.query_cancel.get_first_ctaid::x.b32.b128 %1, r;\n"
+        "}"
+        : "=r"(valid), "=r"(x)
+        : "r"(smem_u32(response16))
+        : "memory");
+    ctaid_x = x;
+    return valid != 0u;
+}
+
 __device__ __forceinline__ ObjI shfl_obj(const ObjI& o, int src) {
     ObjI r;
     r.x = __shfl_sync(0xffffffffu, o.x, src);
@@ -202,6 +250,8 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
     ObjI* const s_unit = reinterpret_cast<ObjI*>(smem_raw + kGZeroBytes + kGWarps * 2 * stage);
     __shared__ int s_cnt;
     __shared__ unsigned long long s_mask;
+    __shared__ __align__(16) uint4 s_clc;          // cluster-launch-control response
+    __shared__ __align__(8) unsigned long long s_bar;  // its mbarrier
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned* const wbuf0 = reinterpret_cast<unsigned*>(smem_raw + kGZeroBytes + warp * 2 * stage);
@@ -213,13 +263,16 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
     {  // zero tile and staging buffers start all-zero (contiguous in shared memory)
         const int n16 = (kGZeroBytes + kGWarps * 2 * stage) / 16;
         for (int i = tid; i < n16; i += kGThreads) zero_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if constexpr (!ACCUM) fence_proxy_async();
+        if (tid == 0) mbar_init(&s_bar, 1);
+        fence_proxy_async();  // zero tile and mbarrier -> visible to the async proxy
     }
+    unsigned clc_phase = 0;
     int cur = 0;
     int c0x0 = 1, c0x1 = 0, c1x0 = 1, c1x1 = 0;  // span written into wbuf0 / wbuf1 by their last use (empty)
     Digest dg;
 
-    for (long long u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+    long long u = blockIdx.x;
+    for (;;) {
         const long long plane = u / p.units_per_plane;
         const int ug = (int)(u - plane * p.units_per_plane);
         float* const plane_ptr = p.heat + plane * plane_elems;
@@ -256,6 +309,11 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         if (tid == 0) {
             s_cnt = 0;
             s_mask = 0ull;
+            if (p.use_clc) {  // ask for the next unit now; the answer lands while this one is rendered
+                fence_proxy_async();
+                mbar_expect_tx(&s_bar, 16);
+                clc_try_cancel(&s_clc, &s_bar);
+            }
         }
         __syncthreads();
         for (int base = 0; base < nscan; base += kGThreads) {
@@ -441,6 +499,17 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
             } else {
                 __syncwarp();
             }
+        }
+        // ---- next unit: the one the block scheduler hands over (cluster launch control), else the static stride --
+        if (p.use_clc) {
+            mbar_wait(&s_bar, clc_phase);
+            clc_phase ^= 1u;
+            unsigned nx;
+            if (!clc_response(&s_clc, nx)) break;
+            u = nx;
+        } else {
+            u += gridDim.x;
+            if (u >= p.total_units) break;
         }
     }
     if constexpr (!ACCUM) bulk_wait_read<0>();  // shared memory must outlive every bulk read issued by this thread

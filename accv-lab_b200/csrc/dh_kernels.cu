@@ -63,6 +63,7 @@ struct RenderParams {
     int stage_bytes;  // groups_kernel: bytes of one per-warp staging buffer
     unsigned long long* digest;  // optional fused result digest (FRESH groups_kernel only): bits, hash, count
     long long digest_base;       // element index of heat[0] in the unsharded result
+    int use_clc;                 // groups_kernel: fetch further units through cluster launch control
     long long total_units;
     float factor, k;
     dh_status* status;
@@ -651,6 +652,7 @@ static int env_int(const char* name, int dflt) {
 }
 static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 196608);
 static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
+static const int g_no_clc = env_int("DH_G_NOCLC", 0);
 
 // Plan of the groups kernel: row group = G whole rows (<= kGStageCap bytes), unit = up to 64 groups of one plane,
 // ~192 KB when the problem is large (amortises the per-unit list build; measured optimum on cfg5), smaller when it
@@ -702,6 +704,7 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     // 6.1 vs 7.0-7.4 TB/s for the same stores, profiles/micro/fill_bw3.cu). The kernel keeps its unit loop so a
     // persistent launch stays possible (DH_G_PERSISTENT=1, and grids beyond 2^31-1 units).
     long long g = p.total_units;
+    p.use_clc = !g_persistent && !g_no_clc && g <= 0x7fffffffll;  // a clamped grid falls back to the static stride
     if (g_persistent && g > max_ctas) g = max_ctas;
     if (g > 0x7fffffffll) g = 0x7fffffffll;
     groups_kernel<ACCUM, SRC, DIGEST><<<(int)g, kGThreads, smem, stream>>>(p);
