@@ -417,9 +417,11 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
                 if (lane == 0) bulk_wait_read<1>();  // the store that last read `buf` is older than my latest one
                 __syncwarp();
                 const int cx0 = cur ? c1x0 : c0x0, cx1 = cur ? c1x1 : c0x1;
-                if (cx1 >= cx0) {  // back to all-zero: clear only what its last use wrote
+                if (cx1 >= cx0) {  // back to all-zero: clear only what its last use wrote (128-bit stores, W % 4 == 0)
+                    const int q0 = cx0 >> 2, q1 = cx1 >> 2, w4 = W >> 2;
+                    uint4* const b4 = reinterpret_cast<uint4*>(buf);
                     for (int rr = 0; rr < G; ++rr)
-                        for (int x = cx0 + lane; x <= cx1; x += 32) buf[rr * W + x] = 0u;
+                        for (int q = q0 + lane; q <= q1; q += 32) b4[rr * w4 + q] = make_uint4(0u, 0u, 0u, 0u);
                     __syncwarp();
                 }
             }

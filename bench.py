@@ -24,6 +24,9 @@ import sys
 import threading
 import time
 
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":  # at this level NCCL prints its banner on STDOUT, and the
+    os.environ["NCCL_DEBUG"] = "WARN"                       # contract is ONE JSON line there (set before torch loads)
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -215,6 +218,7 @@ def run_ours(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
+
 
         dist.init_process_group("nccl", device_id=dev)
     lib = _cabi.load()  # raises if libdh_b200.so is missing: no fallback

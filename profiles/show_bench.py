@@ -2,7 +2,7 @@
 import json, sys
 for f in sys.argv[1:]:
     try:
-        d = json.load(open(f))
+        d = json.loads([l for l in open(f).read().splitlines() if l.startswith('{')][-1])
     except Exception as e:
         print(f, "unreadable", e); continue
     r = d.get("roofline") or {}
