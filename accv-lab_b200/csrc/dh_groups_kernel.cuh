@@ -242,6 +242,255 @@ __device__ __forceinline__ ObjI shfl_obj(const ObjI& o, int src) {
     return r;
 }
 
+// Per-warp staging state: two buffers that are all-zero whenever idle, and the span their last use wrote.
+struct WarpStage {
+    unsigned* buf0;
+    unsigned* buf1;
+    int cur = 0;
+    int c0x0 = 1, c0x1 = 0, c1x0 = 1, c1x1 = 0;
+};
+
+// Where a unit's objects come from (needed again by the overflow path, which re-scans the source per group).
+struct UnitSrc {
+    long long plane = 0, src_base = 0;
+    int n = 0, cls = 0;
+};
+
+// K3 + K4b for ONE touched row group, by one warp. `list`/`ucnt` is the unit list in shared memory, `mine` the
+// lane's own entry when the unit has <= 32 objects (`small`). FRESH: the group leaves with one bulk store.
+template <bool ACCUM, int SRC, bool DIGEST>
+__device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& ws, float* __restrict__ plane_ptr,
+                                             long long plane_index0, int y0, int nrows, int W, int G, bool kneg, int lane,
+                                             bool small, const ObjI& mine, const ObjI* __restrict__ list, int ucnt,
+                                             const UnitSrc& us, Digest& dg) {
+    const int y1 = y0 + nrows - 1;
+    float* const gdst = plane_ptr + (long long)y0 * W;
+    const long long gindex = plane_index0 + (long long)y0 * W;
+    unsigned* const buf = ws.cur ? ws.buf1 : ws.buf0;
+    if constexpr (!ACCUM) {
+        if (lane == 0) bulk_wait_read<1>();  // the store that last read `buf` is older than my latest one
+        __syncwarp();
+        const int cx0 = ws.cur ? ws.c1x0 : ws.c0x0, cx1 = ws.cur ? ws.c1x1 : ws.c0x1;
+        if (cx1 >= cx0) {  // back to all-zero: clear only what its last use wrote (128-bit stores, W % 4 == 0)
+            const int q0 = cx0 >> 2, q1 = cx1 >> 2, w4 = W >> 2;
+            uint4* const b4 = reinterpret_cast<uint4*>(buf);
+            for (int rr = 0; rr < G; ++rr)
+                for (int q = q0 + lane; q <= q1; q += 32) b4[rr * w4 + q] = make_uint4(0u, 0u, 0u, 0u);
+            __syncwarp();
+        }
+    }
+    int ux0 = W, ux1 = -1;
+    bool finish = false;  // dense path used: staged uints still need K4
+    if (small) {
+        const bool hit = (mine.r >= 0) && (mine.y + mine.r >= y0) && (mine.y - mine.r <= y1);
+        unsigned bal = __ballot_sync(0xffffffffu, hit);
+        const int nh = __popc(bal);
+        if (nh <= 2) {
+            if (nh > 0) {
+                const int sa = __ffs(bal) - 1;
+                const unsigned rest = bal & (bal - 1u);
+                const int sb = rest ? __ffs(rest) - 1 : sa;
+                const ObjI A = shfl_obj(mine, sa), B = shfl_obj(mine, sb);
+                sparse_group<ACCUM, DIGEST>(buf, gdst, gindex, y0, nrows, W, A, B, rest != 0u, kneg, p.k, lane, ux0, ux1, dg);
+            }
+        } else {
+            finish = true;
+            while (bal) {
+                const int src = __ffs(bal) - 1;
+                bal &= bal - 1u;
+                const ObjI ob = shfl_obj(mine, src);
+                sweep_obj(buf, y0, nrows, W, ob, kneg, lane, ux0, ux1);
+                __syncwarp();
+            }
+        }
+    } else {
+        finish = true;
+        const bool overflow = ucnt > kGCap;  // rare: scan the source instead of the (truncated) shared list
+        const int lim = overflow ? us.n : ucnt;
+        for (int base = 0; base < lim; base += 32) {
+            const int e = base + lane;
+            ObjI o;
+            o.x = o.y = o.r = 0;
+            o.w = 0.f;
+            bool hit = false;
+            if (e < lim) {
+                if (!overflow) {
+                    o = list[e];
+                    hit = (o.y + o.r >= y0) && (o.y - o.r <= y1);
+                } else {
+                    int x, y, r;
+                    if (load_slot<SRC>(p, us.src_base, e, us.cls, us.plane, false, x, y, r))
+                        hit = make_obji(x, y, r, p.factor, y0, y1 + 1, W, o, nullptr, false);
+                }
+            }
+            unsigned bal = __ballot_sync(0xffffffffu, hit);
+            while (bal) {
+                const int src = __ffs(bal) - 1;
+                bal &= bal - 1u;
+                const ObjI ob = shfl_obj(o, src);
+                sweep_obj(buf, y0, nrows, W, ob, kneg, lane, ux0, ux1);
+                __syncwarp();
+            }
+        }
+    }
+    if (finish && ux1 >= ux0) {
+        for (int rr = 0; rr < nrows; ++rr)
+            finish_row<ACCUM, DIGEST>(buf + rr * W, gdst + (long long)rr * W, gindex + (long long)rr * W, ux0, ux1, kneg, p.k,
+                                      lane, dg);
+    }
+    if constexpr (!ACCUM) {
+        fence_proxy_async();  // my generic-proxy writes to `buf` -> visible to the bulk-copy engine
+        __syncwarp();
+        if (lane == 0) {
+            bulk_store(gdst, buf, (unsigned)(nrows * W * 4));
+            bulk_commit();
+        }
+        if (ws.cur) {
+            ws.c1x0 = ux0;
+            ws.c1x1 = ux1;
+        } else {
+            ws.c0x0 = ux0;
+            ws.c0x1 = ux1;
+        }
+        ws.cur ^= 1;
+    } else {
+        __syncwarp();
+    }
+}
+
+// Unit -> plane, rows, source range. Returns the number of slots to scan (`nscan`, independent of any load).
+template <int SRC>
+__device__ __forceinline__ int unit_header(const RenderParams& p, long long u, int G, UnitSrc& us, int& uy0, int& uy1,
+                                           bool& count_skips) {
+    us.plane = u / p.units_per_plane;
+    const int ug = (int)(u - us.plane * p.units_per_plane);
+    uy0 = ug * p.bands_per_unit * G;
+    uy1 = min(uy0 + p.bands_per_unit * G, p.H);
+    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+        const long long sample = us.plane / p.C;
+        us.cls = (int)(us.plane - sample * p.C);
+        long long ns = p.sizes_i64 ? __ldg(reinterpret_cast<const long long*>(p.sizes) + sample)
+                                   : (long long)__ldg(reinterpret_cast<const int*>(p.sizes) + sample);
+        ns = ns < 0 ? 0 : (ns > p.T ? p.T : ns);
+        us.n = (int)ns;
+        us.src_base = sample * p.T;
+        count_skips = (ug == 0 && us.cls == 0);
+        return p.T;  // scan bound that does not depend on a load
+    } else if constexpr (SRC == SRC_CSR) {
+        const int o0 = p.csr_off[us.plane], o1 = p.csr_off[us.plane + 1];
+        us.src_base = o0;
+        us.n = o1 - o0;
+        count_skips = (ug == 0);
+        return us.n;
+    } else {
+        us.n = (int)p.num_objects;
+        count_skips = (u == 0);
+        return us.n;
+    }
+}
+
+// K1 + cull for slot t of the unit's source: true if the slot is an object of this plane that overlaps rows
+// [uy0, uy1). For the batched sources every load of the slot is issued before anything depends on it (one global
+// round trip per scan step instead of size -> label -> box); padded slots (t >= n) are valid memory in the RaggedBatch
+// layout and are dropped after the fact (cuh:84).
+template <int SRC>
+__device__ __forceinline__ bool scan_slot(const RenderParams& p, const UnitSrc& us, int t, int nscan, int uy0, int uy1, int W,
+                                          bool count_skips, ObjI& o) {
+    bool pred = false;
+    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+        if (t < nscan) {
+            const long long i = us.src_base + t;
+            int lab = us.cls;
+            if (p.labels != nullptr) lab = __ldg(p.labels + i);
+            int x = 0, y = 0, r = -1;
+            if constexpr (SRC == SRC_BOXES) {
+                const float2 c = __ldg(reinterpret_cast<const float2*>(p.centers_f) + i);
+                const float4 b = __ldg(reinterpret_cast<const float4*>(p.bboxes_f) + i);
+                if (lab == us.cls) radius_center_one(c.x, c.y, b.x, b.y, b.z, b.w, p.osf, x, y, r);
+            } else {
+                const int2 c = __ldg(reinterpret_cast<const int2*>(p.centers) + i);
+                r = __ldg(p.radii + i);
+                x = c.x;
+                y = c.y;
+            }
+            if (t < us.n) {
+                if (lab == us.cls)
+                    pred = make_obji(x, y, r, p.factor, uy0, uy1, W, o, p.status, count_skips);
+                else if (count_skips && p.status && (lab < 0 || lab >= p.C))
+                    atomicAdd(&p.status->skipped_label, 1u);
+            }
+        }
+    } else if (t < us.n) {
+        int x, y, r;
+        if (load_slot<SRC>(p, us.src_base, t, us.cls, us.plane, count_skips, x, y, r))
+            pred = make_obji(x, y, r, p.factor, uy0, uy1, W, o, p.status, count_skips);
+    }
+    return pred;
+}
+
+// groups (relative to the unit) an object overlaps, as a bit range
+__device__ __forceinline__ unsigned long long group_bits(const ObjI& o, int uy0, int uy1, int G) {
+    const int lo = (max(o.y - o.r, uy0) - uy0) / G, hi = (min(o.y + o.r, uy1 - 1) - uy0) / G;
+    return ((2ull << (hi - lo)) - 1ull) << lo;
+}
+
+// K4a for the groups whose bit is set in `z` (untouched ones): each maximal run leaves as bulk stores of the zero tile.
+// Called by lanes in parallel: lane `g` starts the run that begins at group g (and g + 32).
+__device__ __forceinline__ void zero_runs(unsigned long long z, int lane, float* __restrict__ plane_ptr, int uy0, int uy1,
+                                          int W, int G, const float4* zero_tile) {
+    bool any = false;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int g = lane + 32 * h;
+        const bool start = ((z >> g) & 1ull) && (g == 0 || !((z >> (g - 1)) & 1ull));
+        if (start) {
+            const unsigned long long inv = ~(z >> g);
+            const int run = inv ? __ffsll((long long)inv) - 1 : 64 - g;
+            const int r0 = uy0 + g * G, r1 = min(r0 + run * G, uy1);
+            char* dst = reinterpret_cast<char*>(plane_ptr + (long long)r0 * W);
+            int bytes = (r1 - r0) * W * 4;
+            while (bytes > 0) {
+                const int c = min(bytes, kGZeroBytes);
+                bulk_store(dst, zero_tile, (unsigned)c);
+                dst += c;
+                bytes -= c;
+            }
+            any = true;
+        }
+    }
+    if (any) bulk_commit();
+}
+
+// Warp-reduce the per-lane digests, combine the warps in shared memory and issue ONE triple of global atomics per
+// CTA (the three words are shared by the whole grid). Contains a block barrier: every thread of the CTA calls it.
+__device__ __forceinline__ void digest_flush(Digest& dg, unsigned long long* out3, int tid, int lane, int warp) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        dg.bits += __shfl_xor_sync(0xffffffffu, dg.bits, d);
+        dg.hash += __shfl_xor_sync(0xffffffffu, dg.hash, d);
+        dg.cnt += __shfl_xor_sync(0xffffffffu, dg.cnt, d);
+    }
+    __shared__ unsigned long long s_dg[3][kGWarps];
+    if (lane == 0) {
+        s_dg[0][warp] = dg.bits;
+        s_dg[1][warp] = dg.hash;
+        s_dg[2][warp] = dg.cnt;
+    }
+    __syncthreads();
+    if (tid < 3 && out3 != nullptr) {
+        unsigned long long t = 0;
+#pragma unroll
+        for (int w = 0; w < kGWarps; ++w) t += s_dg[tid][w];
+        if (t != 0ull) atomicAdd(out3 + tid, t);
+    }
+}
+
+// The kernel: one CTA per unit (flat grid), resident CTAs take over not-yet-launched ones through cluster launch
+// control. Per unit all 8 warps build the list together (three block barriers), warp 7 sends the untouched runs off,
+// and the touched groups are rendered striped over the warps (group g -> warp g % 8) with no block barrier.
+// Tried and measured slower on B200 (profiles/r01/experiments.md): claiming groups dynamically with shared-memory
+// atomics (+23 % instructions, -15 % throughput) and a producer/consumer warp pipeline over two list stages (equal at
+// best, 10-25 % slower for units under 128 KB).
 template <bool ACCUM, int SRC, bool DIGEST>
 __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const RenderParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -250,61 +499,34 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
     ObjI* const s_unit = reinterpret_cast<ObjI*>(smem_raw + kGZeroBytes + kGWarps * 2 * stage);
     __shared__ int s_cnt;
     __shared__ unsigned long long s_mask;
-    __shared__ __align__(16) uint4 s_clc;          // cluster-launch-control response
+    __shared__ __align__(16) uint4 s_clc;              // cluster-launch-control response
     __shared__ __align__(8) unsigned long long s_bar;  // its mbarrier
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    unsigned* const wbuf0 = reinterpret_cast<unsigned*>(smem_raw + kGZeroBytes + warp * 2 * stage);
-    unsigned* const wbuf1 = wbuf0 + stage / 4;
     const bool kneg = p.k < 0.0f;
-    const int W = p.W, H = p.H, G = p.band_cols /* rows per group */;
-    const long long plane_elems = (long long)H * W;
-
+    const int W = p.W, G = p.band_cols /* rows per group */;
+    const long long plane_elems = (long long)p.H * W;
     {  // zero tile and staging buffers start all-zero (contiguous in shared memory)
         const int n16 = (kGZeroBytes + kGWarps * 2 * stage) / 16;
         for (int i = tid; i < n16; i += kGThreads) zero_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (tid == 0) mbar_init(&s_bar, 1);
         fence_proxy_async();  // zero tile and mbarrier -> visible to the async proxy
     }
+    WarpStage ws;
+    ws.buf0 = reinterpret_cast<unsigned*>(smem_raw + kGZeroBytes + warp * 2 * stage);
+    ws.buf1 = ws.buf0 + stage / 4;
     unsigned clc_phase = 0;
-    int cur = 0;
-    int c0x0 = 1, c0x1 = 0, c1x0 = 1, c1x1 = 0;  // span written into wbuf0 / wbuf1 by their last use (empty)
     Digest dg;
 
     long long u = blockIdx.x;
     for (;;) {
-        const long long plane = u / p.units_per_plane;
-        const int ug = (int)(u - plane * p.units_per_plane);
-        float* const plane_ptr = p.heat + plane * plane_elems;
-        const int uy0 = ug * p.bands_per_unit * G, uy1 = min(uy0 + p.bands_per_unit * G, H);
+        UnitSrc us;
+        int uy0, uy1;
+        bool count_skips;
+        const int nscan = unit_header<SRC>(p, u, G, us, uy0, uy1, count_skips);
+        float* const plane_ptr = p.heat + us.plane * plane_elems;
         const int ngroups = (uy1 - uy0 + G - 1) / G;
 
-        long long src_base = 0;
-        int n = 0, cls = 0, nscan = 0;
-        bool count_skips = false;
-        if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
-            const long long sample = plane / p.C;
-            cls = (int)(plane - sample * p.C);
-            long long ns = p.sizes_i64 ? __ldg(reinterpret_cast<const long long*>(p.sizes) + sample)
-                                       : (long long)__ldg(reinterpret_cast<const int*>(p.sizes) + sample);
-            ns = ns < 0 ? 0 : (ns > p.T ? p.T : ns);
-            n = (int)ns;
-            src_base = sample * p.T;
-            count_skips = (ug == 0 && cls == 0);
-            nscan = p.T;  // scan bound that does not depend on a load
-        } else if constexpr (SRC == SRC_CSR) {
-            const int o0 = p.csr_off[plane], o1 = p.csr_off[plane + 1];
-            src_base = o0;
-            n = o1 - o0;
-            count_skips = (ug == 0);
-            nscan = n;
-        } else {
-            n = (int)p.num_objects;
-            count_skips = (u == 0);
-            nscan = n;
-        }
-
-        // ---- K1/K2: unit list (ballot + popc-prefix compaction) and group-occupancy mask ------------------------
         __syncthreads();  // every warp is done with the previous unit's list (and shared memory is initialised)
         if (tid == 0) {
             s_cnt = 0;
@@ -316,53 +538,20 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
             }
         }
         __syncthreads();
+        // K1/K2: unit list (ballot + popc-prefix compaction) and group-occupancy mask
         for (int base = 0; base < nscan; base += kGThreads) {
-            const int t = base + tid;
             ObjI o;
-            bool pred = false;
-            if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
-                // Every load of the slot is issued before anything depends on it (the sample size was requested
-                // above): one global round trip per unit instead of size -> label -> box. Padded slots (t >= n) are
-                // valid memory in the RaggedBatch layout and are dropped after the fact (cuh:84).
-                if (t < p.T) {
-                    const long long i = src_base + t;
-                    int lab = cls;
-                    if (p.labels != nullptr) lab = __ldg(p.labels + i);
-                    int x = 0, y = 0, r = -1;
-                    if constexpr (SRC == SRC_BOXES) {
-                        const float2 c = __ldg(reinterpret_cast<const float2*>(p.centers_f) + i);
-                        const float4 b = __ldg(reinterpret_cast<const float4*>(p.bboxes_f) + i);
-                        if (lab == cls) radius_center_one(c.x, c.y, b.x, b.y, b.z, b.w, p.osf, x, y, r);
-                    } else {
-                        const int2 c = __ldg(reinterpret_cast<const int2*>(p.centers) + i);
-                        r = __ldg(p.radii + i);
-                        x = c.x;
-                        y = c.y;
-                    }
-                    if (t < n) {
-                        if (lab == cls)
-                            pred = make_obji(x, y, r, p.factor, uy0, uy1, W, o, p.status, count_skips);
-                        else if (count_skips && p.status && (lab < 0 || lab >= p.C))
-                            atomicAdd(&p.status->skipped_label, 1u);
-                    }
-                }
-            } else if (t < n) {
-                int x, y, r;
-                if (load_slot<SRC>(p, src_base, t, cls, plane, count_skips, x, y, r))
-                    pred = make_obji(x, y, r, p.factor, uy0, uy1, W, o, p.status, count_skips);
-            }
-            unsigned long long bits = 0ull;
-            if (pred) {
-                const int lo = (max(o.y - o.r, uy0) - uy0) / G, hi = (min(o.y + o.r, uy1 - 1) - uy0) / G;
-                bits = ((2ull << (hi - lo)) - 1ull) << lo;
-            }
-            const unsigned blo = __reduce_or_sync(0xffffffffu, (unsigned)bits);
-            const unsigned bhi = __reduce_or_sync(0xffffffffu, (unsigned)(bits >> 32));
-            if (lane == 0 && (blo | bhi)) atomicOr(&s_mask, ((unsigned long long)bhi << 32) | blo);
+            const bool pred = scan_slot<SRC>(p, us, base + tid, nscan, uy0, uy1, W, count_skips, o);
+            const unsigned long long bits = pred ? group_bits(o, uy0, uy1, G) : 0ull;
             const unsigned bal = __ballot_sync(0xffffffffu, pred);
             if (bal) {
+                const unsigned blo = __reduce_or_sync(0xffffffffu, (unsigned)bits);
+                const unsigned bhi = __reduce_or_sync(0xffffffffu, (unsigned)(bits >> 32));
                 int pos = 0;
-                if (lane == 0) pos = atomicAdd(&s_cnt, __popc(bal));
+                if (lane == 0) {
+                    atomicOr(&s_mask, ((unsigned long long)bhi << 32) | blo);
+                    pos = atomicAdd(&s_cnt, __popc(bal));
+                }
                 pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(bal & ((1u << lane) - 1u));
                 if (pred && pos < kGCap) s_unit[pos] = o;
             }
@@ -370,8 +559,6 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         __syncthreads();
         const int ucnt = s_cnt;
         const unsigned long long mask = s_mask;
-        const bool overflow = ucnt > kGCap;  // rare: warps then scan the source instead of the shared list
-        const int lim = overflow ? n : ucnt;
         const bool small = ucnt <= 32;  // one list entry per lane, kept in registers for the whole unit
         ObjI mine;
         mine.x = mine.y = 0;
@@ -379,130 +566,23 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         mine.w = 0.f;
         if (small && lane < ucnt) mine = s_unit[lane];
 
-        // ---- K4a FRESH: runs of untouched groups leave as bulk stores of the zero tile (warp w: groups 8w..8w+7) ---
-        if constexpr (!ACCUM) {
-            const int gbase = 8 * warp;
-            if (lane == 0 && gbase < ngroups) {
-                unsigned z = (unsigned)((~mask >> gbase) & 0xffull) & ((1u << min(8, ngroups - gbase)) - 1u);
-                while (z) {
-                    const int s = __ffs(z) - 1;
-                    const int run = __ffs(~(z >> s)) - 1;  // consecutive untouched groups starting at s
-                    z &= ~(((1u << run) - 1u) << s);
-                    const int r0 = uy0 + (gbase + s) * G, r1 = min(r0 + run * G, uy1);
-                    char* dst = reinterpret_cast<char*>(plane_ptr + (long long)r0 * W);
-                    int bytes = (r1 - r0) * W * 4;
-                    while (bytes > 0) {
-                        const int c = min(bytes, kGZeroBytes);
-                        bulk_store(dst, zero_tile, (unsigned)c);
-                        dst += c;
-                        bytes -= c;
-                    }
-                }
-                bulk_commit();
+        if constexpr (!ACCUM) {  // K4a: untouched runs, by warp 7 (it gets the fewest striped groups in a short unit)
+            if (warp == kGWarps - 1) {
+                const unsigned long long valid = ngroups >= 64 ? ~0ull : ((1ull << ngroups) - 1ull);
+                zero_runs(~mask & valid, lane, plane_ptr, uy0, uy1, W, G, zero_tile);
             }
         }
-
-        // ---- K3/K4b: touched groups, striped over the warps; no block barrier in here ------------------------------
+        // K3/K4b: touched groups, striped over the warps; no block barrier in here
+        const long long plane_index0 = p.digest_base + us.plane * plane_elems;
         unsigned long long gm = mask & (0x0101010101010101ull << warp);
         while (gm) {
             const int g = __ffsll((long long)gm) - 1;
             gm &= gm - 1ull;
-            if (g >= ngroups) break;
             const int y0 = uy0 + g * G;
-            const int nrows = min(G, uy1 - y0), y1 = y0 + nrows - 1;
-            float* const gdst = plane_ptr + (long long)y0 * W;
-            const long long gindex = p.digest_base + plane * plane_elems + (long long)y0 * W;
-            unsigned* const buf = cur ? wbuf1 : wbuf0;
-            if constexpr (!ACCUM) {
-                if (lane == 0) bulk_wait_read<1>();  // the store that last read `buf` is older than my latest one
-                __syncwarp();
-                const int cx0 = cur ? c1x0 : c0x0, cx1 = cur ? c1x1 : c0x1;
-                if (cx1 >= cx0) {  // back to all-zero: clear only what its last use wrote (128-bit stores, W % 4 == 0)
-                    const int q0 = cx0 >> 2, q1 = cx1 >> 2, w4 = W >> 2;
-                    uint4* const b4 = reinterpret_cast<uint4*>(buf);
-                    for (int rr = 0; rr < G; ++rr)
-                        for (int q = q0 + lane; q <= q1; q += 32) b4[rr * w4 + q] = make_uint4(0u, 0u, 0u, 0u);
-                    __syncwarp();
-                }
-            }
-            int ux0 = W, ux1 = -1;
-            bool finish = false;  // dense path used: staged uints still need K4
-            if (small) {
-                const bool hit = (mine.r >= 0) && (mine.y + mine.r >= y0) && (mine.y - mine.r <= y1);
-                unsigned bal = __ballot_sync(0xffffffffu, hit);
-                const int nh = __popc(bal);
-                if (nh <= 2) {
-                    if (nh > 0) {
-                        const int sa = __ffs(bal) - 1;
-                        const unsigned rest = bal & (bal - 1u);
-                        const int sb = rest ? __ffs(rest) - 1 : sa;
-                        const ObjI A = shfl_obj(mine, sa), B = shfl_obj(mine, sb);
-                        sparse_group<ACCUM, DIGEST>(buf, gdst, gindex, y0, nrows, W, A, B, rest != 0u, kneg, p.k, lane, ux0,
-                                                    ux1, dg);
-                    }
-                } else {
-                    finish = true;
-                    while (bal) {
-                        const int src = __ffs(bal) - 1;
-                        bal &= bal - 1u;
-                        const ObjI ob = shfl_obj(mine, src);
-                        sweep_obj(buf, y0, nrows, W, ob, kneg, lane, ux0, ux1);
-                        __syncwarp();
-                    }
-                }
-            } else {
-                finish = true;
-                for (int base = 0; base < lim; base += 32) {
-                    const int e = base + lane;
-                    ObjI o;
-                    o.x = o.y = o.r = 0;
-                    o.w = 0.f;
-                    bool hit = false;
-                    if (e < lim) {
-                        if (!overflow) {
-                            o = s_unit[e];
-                            hit = (o.y + o.r >= y0) && (o.y - o.r <= y1);
-                        } else {
-                            int x, y, r;
-                            if (load_slot<SRC>(p, src_base, e, cls, plane, false, x, y, r))
-                                hit = make_obji(x, y, r, p.factor, y0, y1 + 1, W, o, nullptr, false);
-                        }
-                    }
-                    unsigned bal = __ballot_sync(0xffffffffu, hit);
-                    while (bal) {
-                        const int src = __ffs(bal) - 1;
-                        bal &= bal - 1u;
-                        const ObjI ob = shfl_obj(o, src);
-                        sweep_obj(buf, y0, nrows, W, ob, kneg, lane, ux0, ux1);
-                        __syncwarp();
-                    }
-                }
-            }
-            if (finish && ux1 >= ux0) {
-                for (int rr = 0; rr < nrows; ++rr)
-                    finish_row<ACCUM, DIGEST>(buf + rr * W, gdst + (long long)rr * W, gindex + (long long)rr * W, ux0, ux1,
-                                              kneg, p.k, lane, dg);
-            }
-            if constexpr (!ACCUM) {
-                fence_proxy_async();  // my generic-proxy writes to `buf` -> visible to the bulk-copy engine
-                __syncwarp();
-                if (lane == 0) {
-                    bulk_store(gdst, buf, (unsigned)(nrows * W * 4));
-                    bulk_commit();
-                }
-                if (cur) {
-                    c1x0 = ux0;
-                    c1x1 = ux1;
-                } else {
-                    c0x0 = ux0;
-                    c0x1 = ux1;
-                }
-                cur ^= 1;
-            } else {
-                __syncwarp();
-            }
+            render_group<ACCUM, SRC, DIGEST>(p, ws, plane_ptr, plane_index0, y0, min(G, uy1 - y0), W, G, kneg, lane, small, mine,
+                                             s_unit, ucnt, us, dg);
         }
-        // ---- next unit: the one the block scheduler hands over (cluster launch control), else the static stride --
+        // next unit: the one the block scheduler hands over (cluster launch control), else the static stride
         if (p.use_clc) {
             mbar_wait(&s_bar, clc_phase);
             clc_phase ^= 1u;
@@ -515,28 +595,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         }
     }
     if constexpr (!ACCUM) bulk_wait_read<0>();  // shared memory must outlive every bulk read issued by this thread
-    if constexpr (DIGEST) {
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) {
-            dg.bits += __shfl_xor_sync(0xffffffffu, dg.bits, d);
-            dg.hash += __shfl_xor_sync(0xffffffffu, dg.hash, d);
-            dg.cnt += __shfl_xor_sync(0xffffffffu, dg.cnt, d);
-        }
-        // one triple of global atomics per CTA (the three words are shared by the whole grid)
-        __shared__ unsigned long long s_dg[3][kGWarps];
-        if (lane == 0) {
-            s_dg[0][warp] = dg.bits;
-            s_dg[1][warp] = dg.hash;
-            s_dg[2][warp] = dg.cnt;
-        }
-        __syncthreads();
-        if (tid < 3 && p.digest != nullptr) {
-            unsigned long long t = 0;
-#pragma unroll
-            for (int w = 0; w < kGWarps; ++w) t += s_dg[tid][w];
-            if (t != 0ull) atomicAdd(p.digest + tid, t);
-        }
-    }
+    if constexpr (DIGEST) digest_flush(dg, p.digest, tid, lane, warp);
 }
 
 }  // namespace dh

@@ -650,12 +650,12 @@ static int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
 }
-static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 196608);
+static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 131072);
 static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
 static const int g_no_clc = env_int("DH_G_NOCLC", 0);
 
-// Plan of the groups kernel: row group = G whole rows (<= kGStageCap bytes), unit = up to 64 groups of one plane,
-// ~192 KB when the problem is large (amortises the per-unit list build; measured optimum on cfg5), smaller when it
+// Plan of the groups kernels: row group = G whole rows (<= kGStageCap bytes), unit = up to 64 groups of one plane,
+// ~128 KB when the problem is large (amortises the per-unit list build; measured optimum on cfg5: 3 units per plane), smaller when it
 // is not, so that every resident CTA slot still sees several units.
 static void make_groups_plan(RenderParams& p, long long max_ctas) {
     // rows per group: as many as a staging buffer holds while DH_G_MINB CTAs still fit the SM's shared memory
@@ -689,25 +689,24 @@ template <bool ACCUM, int SRC, bool DIGEST>
 static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     static bool attr_set = false;
     if (!attr_set) {
+        const int cap = (int)groups_smem_bytes(kGStageCap);  // widest map: fewer CTAs per SM then
         cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)groups_smem_bytes(kGStageCap));
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
     const long long max_ctas = (long long)sms * DH_G_MINB;
     make_groups_plan(p, max_ctas);
     if (p.total_units == 0) return DH_OK;
-    const size_t smem = groups_smem_bytes(p.stage_bytes);
-    // Flat grid: the block scheduler hands units out dynamically and in address order, which balances SMs that see
-    // different effective store bandwidth; a static grid-stride loop runs at the pace of the slowest SM (measured:
-    // 6.1 vs 7.0-7.4 TB/s for the same stores, profiles/micro/fill_bw3.cu). The kernel keeps its unit loop so a
-    // persistent launch stays possible (DH_G_PERSISTENT=1, and grids beyond 2^31-1 units).
+    // Flat grid, one CTA per unit: the block scheduler hands units out dynamically and in address order, which
+    // balances SMs that see different effective store bandwidth; a static grid-stride loop runs at the pace of the
+    // slowest SM (6.1 vs 7.0-7.4 TB/s for the same stores, profiles/micro/fill_bw3.cu). Resident CTAs then take
+    // over the not-yet-launched ones through cluster launch control, so only ~sms*DH_G_MINB CTAs ever start.
     long long g = p.total_units;
     p.use_clc = !g_persistent && !g_no_clc && g <= 0x7fffffffll;  // a clamped grid falls back to the static stride
     if (g_persistent && g > max_ctas) g = max_ctas;
     if (g > 0x7fffffffll) g = 0x7fffffffll;
-    groups_kernel<ACCUM, SRC, DIGEST><<<(int)g, kGThreads, smem, stream>>>(p);
+    groups_kernel<ACCUM, SRC, DIGEST><<<(int)g, kGThreads, groups_smem_bytes(p.stage_bytes), stream>>>(p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return (int)cudaGetLastError();
 }
