@@ -55,20 +55,26 @@ __device__ __forceinline__ unsigned enc_m(float m, bool kneg) {
     return kneg ? b + 1u : ~b;
 }
 
-__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {  // splitmix64 finaliser (== dh_host.cu)
-    z += 0x9e3779b97f4a7c15ull;
-    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
-    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
-    return z ^ (z >> 31);
+// Pixel index -> 64-bit digest contribution (== dh_host.cu, oracle/oracle.py:_mix_index): 32-bit IMADs only — the
+// renderer is instruction-issue bound, a 64-bit splitmix per touched pixel cost 12 % of the step.
+__device__ __forceinline__ unsigned long long mix_index(unsigned long long i) {
+    const unsigned lo = (unsigned)i, hi = (unsigned)(i >> 32);
+    unsigned h = lo ^ (hi * 0x9E3779B1u);
+    h *= 0x85EBCA6Bu;
+    h ^= h >> 13;
+    h *= 0xC2B2AE35u;
+    h ^= h >> 16;
+    return ((unsigned long long)h << 32) | (unsigned long long)(h * 0x27D4EB2Fu + lo);
 }
 
 struct Digest {
-    unsigned long long bits = 0, hash = 0, cnt = 0;
+    unsigned long long bits = 0, hash = 0;
+    unsigned cnt = 0;  // per lane; widened when the lanes are combined
     __device__ __forceinline__ void add(float v, long long index) {
         bits += (unsigned long long)__float_as_uint(v);
         if (v > 0.0f) {
-            hash += mix64((unsigned long long)index);
-            cnt += 1;
+            hash += mix_index((unsigned long long)index);
+            cnt += 1u;
         }
     }
 };
@@ -464,17 +470,18 @@ __device__ __forceinline__ void zero_runs(unsigned long long z, int lane, float*
 // Warp-reduce the per-lane digests, combine the warps in shared memory and issue ONE triple of global atomics per
 // CTA (the three words are shared by the whole grid). Contains a block barrier: every thread of the CTA calls it.
 __device__ __forceinline__ void digest_flush(Digest& dg, unsigned long long* out3, int tid, int lane, int warp) {
+    unsigned long long cnt = dg.cnt;
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         dg.bits += __shfl_xor_sync(0xffffffffu, dg.bits, d);
         dg.hash += __shfl_xor_sync(0xffffffffu, dg.hash, d);
-        dg.cnt += __shfl_xor_sync(0xffffffffu, dg.cnt, d);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
     }
     __shared__ unsigned long long s_dg[3][kGWarps];
     if (lane == 0) {
         s_dg[0][warp] = dg.bits;
         s_dg[1][warp] = dg.hash;
-        s_dg[2][warp] = dg.cnt;
+        s_dg[2][warp] = cnt;
     }
     __syncthreads();
     if (tid < 3 && out3 != nullptr) {

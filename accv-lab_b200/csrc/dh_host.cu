@@ -15,11 +15,15 @@ namespace dh {
 
 extern void count_launches(uint64_t n);  // dh_kernels.cu
 
-__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {  // splitmix64 finaliser
-    z += 0x9e3779b97f4a7c15ull;
-    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
-    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
-    return z ^ (z >> 31);
+// == dh_groups_kernel.cuh mix_index, oracle/oracle.py:_mix_index
+__device__ __forceinline__ unsigned long long mix_index(unsigned long long i) {
+    const unsigned lo = (unsigned)i, hi = (unsigned)(i >> 32);
+    unsigned h = lo ^ (hi * 0x9E3779B1u);
+    h *= 0x85EBCA6Bu;
+    h ^= h >> 13;
+    h *= 0xC2B2AE35u;
+    h ^= h >> 16;
+    return ((unsigned long long)h << 32) | (unsigned long long)(h * 0x27D4EB2Fu + lo);
 }
 
 __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
@@ -39,7 +43,7 @@ __global__ void __launch_bounds__(256) checksum_kernel(const float* __restrict__
     auto one = [&](float x, long long i) {
         s_bits += (unsigned long long)__float_as_uint(x);
         if (x > 0.0f) {
-            s_hash += mix64((unsigned long long)(index_base + i));
+            s_hash += mix_index((unsigned long long)(index_base + i));
             s_cnt += 1;
         }
     };
@@ -77,10 +81,13 @@ __global__ void __launch_bounds__(256) checksum_kernel(const float* __restrict__
 }
 
 // ---- helper streams of the host entry (per device, created once) ------------------------------------
+constexpr int kHostMaxChunks = 16;  // input chunks of the pipelined device-output path
 struct HostCtx {
     bool ready = false;
     cudaStream_t s[2] = {nullptr, nullptr};
+    cudaStream_t copy = nullptr;  // H2D of input chunk c+1 runs here while chunk c is rendered
     cudaEvent_t fork = nullptr, join[2] = {nullptr, nullptr};
+    cudaEvent_t arrived[kHostMaxChunks] = {};
 };
 static HostCtx g_ctx[64];
 static std::mutex g_ctx_mu;
@@ -97,6 +104,9 @@ static int host_ctx(HostCtx*& out) {
             if ((e = cudaEventCreateWithFlags(&c.join[i], cudaEventDisableTiming)) != cudaSuccess) return (int)e;
         }
         if ((e = cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming)) != cudaSuccess) return (int)e;
+        if ((e = cudaStreamCreateWithFlags(&c.copy, cudaStreamNonBlocking)) != cudaSuccess) return (int)e;
+        for (int i = 0; i < kHostMaxChunks; ++i)
+            if ((e = cudaEventCreateWithFlags(&c.arrived[i], cudaEventDisableTiming)) != cudaSuccess) return (int)e;
         c.ready = true;
     }
     out = &c;
@@ -115,7 +125,7 @@ static HostLayout host_layout(int64_t B, int64_t T, int64_t C, int64_t H, int64_
     HostLayout L{};
     const int64_t planes_per_sample = has_labels ? C : 1;
     const size_t sample_bytes = (size_t)planes_per_sample * (size_t)H * (size_t)W * 4;
-    if (chunk <= 0) {
+    if (chunk <= 0) {  // default
         chunk = sample_bytes ? (int64_t)((64ull << 20) / sample_bytes) : B;
         if (chunk < 1) chunk = 1;
     }
@@ -194,6 +204,70 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
 
     cudaError_t e;
 #define DH_TRY(x) do { if ((e = (x)) != cudaSuccess) return (int)e; } while (0)
+    const int64_t sample_elems = C * H * W;
+    // samples [s0, s0+nb) of the device-resident inputs -> `dst` on stream `cs` (digest fused when the shape allows)
+    auto render_range = [&](cudaStream_t cs, float* dst, int64_t s0, int64_t nb) -> int {
+        int r = DH_ERR_UNSUPPORTED_SHAPE;
+        const int32_t* lab = has_labels ? d_labels + s0 * T : nullptr;
+        if (checksum_host)  // digest fused into the render launch: the heatmap is never re-read
+            r = dh_draw_heatmap_batched_from_boxes_digest(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
+                                                          d_sizes + s0, DH_SIZES_I64, lab, nb, T, C, H, W, factor, k,
+                                                          s0 * sample_elems, d_ck, nullptr);
+        if (r == DH_ERR_UNSUPPORTED_SHAPE) {
+            r = dh_draw_heatmap_batched_from_boxes(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
+                                                   d_sizes + s0, DH_SIZES_I64, lab, nb, T, C, H, W, factor, k,
+                                                   DH_MODE_FRESH, nullptr, nullptr, nullptr);
+            if (r == DH_OK && checksum_host) r = dh_checksum(cs, dst, nb * sample_elems, s0 * sample_elems, d_ck);
+        }
+        return r;
+    };
+    int st;
+
+    // ---- result stays on the device and the inputs are large: pipeline H2D against rendering ----------------
+    // Input chunk c+1 crosses PCIe on the copy stream while chunk c is rendered; consecutive chunks alternate
+    // between two render streams so the tail of one launch overlaps the head of the next.
+    const size_t slot_bytes = 24 + (has_labels ? 4 : 0);
+    const size_t in_bytes = (size_t)B * T * slot_bytes;
+    if (!heatmap_host && in_bytes >= ((size_t)2 << 20) && B >= 2 && chunk_samples >= 0) {
+        int64_t nch = (int64_t)(in_bytes >> 20);  // ~1 MB of inputs per chunk
+        if (chunk_samples > 0) nch = (B + chunk_samples - 1) / chunk_samples;
+        if (nch > dh::kHostMaxChunks) nch = dh::kHostMaxChunks;
+        if (nch > B) nch = B;
+        if (nch < 2) nch = 2;
+        std::lock_guard<std::mutex> lock(dh::g_ctx_mu);
+        dh::HostCtx* ctx = nullptr;
+        st = dh::host_ctx(ctx);
+        if (st != DH_OK) return st;
+        DH_TRY(cudaMemcpyAsync(d_sizes, nums_targets_host, (size_t)B * 8, cudaMemcpyHostToDevice, stream));
+        if (checksum_host) DH_TRY(cudaMemsetAsync(d_ck, 0, 24, stream));
+        DH_TRY(cudaEventRecord(ctx->fork, stream));  // everything that read the scratch inputs before is done
+        DH_TRY(cudaStreamWaitEvent(ctx->copy, ctx->fork, 0));
+        DH_TRY(cudaStreamWaitEvent(ctx->s[0], ctx->fork, 0));
+        DH_TRY(cudaStreamWaitEvent(ctx->s[1], ctx->fork, 0));
+        for (int64_t c = 0; c < nch; ++c) {
+            const int64_t s0 = B * c / nch, s1 = B * (c + 1) / nch, nb = s1 - s0;
+            if (nb <= 0) continue;
+            DH_TRY(cudaMemcpyAsync(d_centers + s0 * T * 2, centers_xy_host + s0 * T * 2, (size_t)nb * T * 8,
+                                   cudaMemcpyHostToDevice, ctx->copy));
+            DH_TRY(cudaMemcpyAsync(d_bboxes + s0 * T * 4, bboxes_xyxy_host + s0 * T * 4, (size_t)nb * T * 16,
+                                   cudaMemcpyHostToDevice, ctx->copy));
+            if (has_labels)
+                DH_TRY(cudaMemcpyAsync(d_labels + s0 * T, labels_host + s0 * T, (size_t)nb * T * 4,
+                                       cudaMemcpyHostToDevice, ctx->copy));
+            DH_TRY(cudaEventRecord(ctx->arrived[c], ctx->copy));
+            cudaStream_t rs = ctx->s[c & 1];
+            DH_TRY(cudaStreamWaitEvent(rs, ctx->arrived[c], 0));
+            st = render_range(rs, heatmap_device + s0 * sample_elems, s0, nb);
+            if (st != DH_OK) return st;
+        }
+        for (int j = 0; j < 2; ++j) {
+            DH_TRY(cudaEventRecord(ctx->join[j], ctx->s[j]));
+            DH_TRY(cudaStreamWaitEvent(stream, ctx->join[j], 0));
+        }
+        if (checksum_host) DH_TRY(cudaMemcpyAsync(checksum_host, d_ck, 24, cudaMemcpyDeviceToHost, stream));
+        return DH_OK;
+    }
+
     // ---- inputs: host -> device, one copy per array ----
     if (T > 0) {
         DH_TRY(cudaMemcpyAsync(d_centers, centers_xy_host, (size_t)B * T * 2 * 4, cudaMemcpyHostToDevice, stream));
@@ -204,20 +278,8 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
     DH_TRY(cudaMemcpyAsync(d_sizes, nums_targets_host, (size_t)B * 8, cudaMemcpyHostToDevice, stream));
     if (checksum_host) DH_TRY(cudaMemsetAsync(d_ck, 0, 24, stream));
 
-    const int64_t sample_elems = C * H * W;
-    int st;
-    if (!heatmap_host) {  // result stays on the device: one launch
-        st = DH_ERR_UNSUPPORTED_SHAPE;
-        if (checksum_host)  // digest fused into the render launch: the heatmap is never re-read
-            st = dh_draw_heatmap_batched_from_boxes_digest(stream, heatmap_device, d_centers, d_bboxes, osf, d_sizes,
-                                                           DH_SIZES_I64, d_labels, B, T, C, H, W, factor, k, 0, d_ck,
-                                                           nullptr);
-        if (st == DH_ERR_UNSUPPORTED_SHAPE) {
-            st = dh_draw_heatmap_batched_from_boxes(stream, heatmap_device, d_centers, d_bboxes, osf, d_sizes,
-                                                    DH_SIZES_I64, d_labels, B, T, C, H, W, factor, k, DH_MODE_FRESH,
-                                                    nullptr, nullptr, nullptr);
-            if (st == DH_OK && checksum_host) st = dh_checksum(stream, heatmap_device, B * sample_elems, 0, d_ck);
-        }
+    if (!heatmap_host) {  // result stays on the device, small inputs: one launch
+        st = render_range(stream, heatmap_device, 0, B);
         if (st != DH_OK) return st;
         if (checksum_host) DH_TRY(cudaMemcpyAsync(checksum_host, d_ck, 24, cudaMemcpyDeviceToHost, stream));
         return DH_OK;
@@ -236,18 +298,7 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
         const int64_t nb = (B - s0 < L.chunk) ? (B - s0) : L.chunk;
         cudaStream_t cs = ctx->s[i & 1];
         float* dst = staging ? (float*)(ws + L.off_stage[i & 1]) : heatmap_device + s0 * sample_elems;
-        st = DH_ERR_UNSUPPORTED_SHAPE;
-        if (checksum_host)
-            st = dh_draw_heatmap_batched_from_boxes_digest(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
-                                                           d_sizes + s0, DH_SIZES_I64,
-                                                           has_labels ? d_labels + s0 * T : nullptr, nb, T, C, H, W,
-                                                           factor, k, s0 * sample_elems, d_ck, nullptr);
-        if (st == DH_ERR_UNSUPPORTED_SHAPE) {
-            st = dh_draw_heatmap_batched_from_boxes(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
-                                                    d_sizes + s0, DH_SIZES_I64, has_labels ? d_labels + s0 * T : nullptr,
-                                                    nb, T, C, H, W, factor, k, DH_MODE_FRESH, nullptr, nullptr, nullptr);
-            if (st == DH_OK && checksum_host) st = dh_checksum(cs, dst, nb * sample_elems, s0 * sample_elems, d_ck);
-        }
+        st = render_range(cs, dst, s0, nb);
         if (st != DH_OK) return st;
         DH_TRY(cudaMemcpyAsync(heatmap_host + s0 * sample_elems, dst, (size_t)nb * sample_elems * 4,
                                cudaMemcpyDeviceToHost, cs));

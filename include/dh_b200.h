@@ -143,7 +143,8 @@ int dh_draw_heatmap(void* stream, float* heatmaps, const int32_t* centers, const
  * Order-independent, exactly additive digest of `n` fp32 values (so shards of a batch can be digested on
  * different GPUs and summed with wrapping uint64 adds, e.g. an NCCL all_reduce(SUM) over int64):
  *     out[0] += sum_i  bits(v_i)                          (fp32 bit patterns, wrapping uint64)
- *     out[1] += sum_{i: v_i > 0} mix64(index_base + i)    (hash of the touched-pixel mask)
+ *     out[1] += sum_{i: v_i > 0} mix(index_base + i)      (hash of the touched-pixel mask; mix = 32-bit
+ *                                                          murmur3-finaliser of the index, widened to 64 bits)
  *     out[2] += #{i: v_i > 0}
  * `out` is a DEVICE array of 3 uint64 that the caller zeroes (or carries over). No reference equivalent:
  * the reference has no multi-GPU path. */
@@ -157,11 +158,15 @@ int dh_checksum(void* stream, const float* values, int64_t n, int64_t index_base
  *     process-lifetime) streams that are fork/joined to `stream` with events. If heatmap_device is NULL the
  *     chunks are rendered into two staging buffers inside `device_scratch`, so device memory use is bounded
  *     independent of B; otherwise they are rendered in place into heatmap_device [B,(C),H,W].
- *   - heatmap_host == NULL: heatmap_device must be non-NULL; one render launch, the result stays on the device.
+ *   - heatmap_host == NULL: heatmap_device must be non-NULL and the result stays on the device. When the inputs
+ *     are large (>= 2 MiB) they are cut into up to 16 sample chunks (~1 MiB each, or `chunk_samples` samples when
+ *     > 0): chunk c+1 crosses PCIe on an internal copy stream while chunk c is rendered, consecutive chunks
+ *     alternating between the two internal render streams; otherwise (or with chunk_samples < 0) one copy per
+ *     array and ONE render launch on `stream`.
  *   - checksum_host (optional, 3 x uint64, host): dh_checksum of the whole result, copied to the host (computed
  *     inside the render launch when the shape allows it, by a separate dh_checksum pass otherwise).
  * labels_host == NULL -> heatmap is [B,H,W] and num_classes is ignored. nums_targets_host is int64 [B].
- * chunk_samples <= 0 selects a default (about 64 MiB of output per chunk).
+ * chunk_samples == 0 selects a default (host output: about 64 MiB of output per chunk); < 0 disables input pipelining.
  * `device_scratch` (16-byte aligned) must hold dh_host_scratch_bytes(...) bytes for the same arguments.
  * The call is asynchronous with respect to the host like every other entry: synchronise `stream` before
  * reading heatmap_host / checksum_host. */

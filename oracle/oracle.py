@@ -193,18 +193,26 @@ def touched_mask_batched(shape, centers, radii, sizes, labels=None):
 
 
 # ---- digest (include/dh_b200.h: dh_checksum), numpy restatement --------------------------------------
-def _mix64(z):
-    z = (z + np.uint64(0x9E3779B97F4A7C15)).astype(np.uint64)
-    z = ((z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)).astype(np.uint64)
-    z = ((z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)).astype(np.uint64)
-    return z ^ (z >> np.uint64(31))
+def _mix_index(i):
+    """Pixel index (uint64) -> 64-bit contribution: a 32-bit multiply/xorshift mixer (murmur3 finaliser) over the low
+    word folded with the high word, widened with one more multiply. Cheap on the GPU (32-bit IMADs only)."""
+    i = np.asarray(i, dtype=np.uint64)
+    lo = (i & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    hi = (i >> np.uint64(32)).astype(np.uint32)
+    h = lo ^ (hi * np.uint32(0x9E3779B1))
+    h = h * np.uint32(0x85EBCA6B)
+    h = h ^ (h >> np.uint32(13))
+    h = h * np.uint32(0xC2B2AE35)
+    h = h ^ (h >> np.uint32(16))
+    low = h * np.uint32(0x27D4EB2F) + lo
+    return (h.astype(np.uint64) << np.uint64(32)) | low.astype(np.uint64)
 
 
 def digest_numpy(values, index_base=0):
-    """(sum of fp32 bit patterns, sum of mix64(index) over v>0, count of v>0), all wrapping uint64 -> int64 view."""
+    """(sum of fp32 bit patterns, sum of mix_index(index) over v>0, count of v>0), all wrapping uint64 -> int64 view."""
     v = np.ascontiguousarray(values, dtype=np.float32).reshape(-1)
     with np.errstate(over="ignore"):
         s_bits = v.view(np.uint32).astype(np.uint64).sum(dtype=np.uint64)
         idx = np.nonzero(v > 0)[0].astype(np.uint64) + np.uint64(index_base)
-        s_hash = _mix64(idx).sum(dtype=np.uint64) if idx.size else np.uint64(0)
+        s_hash = _mix_index(idx).sum(dtype=np.uint64) if idx.size else np.uint64(0)
     return np.array([s_bits, s_hash, np.uint64(idx.size)], dtype=np.uint64).view(np.int64)

@@ -213,6 +213,64 @@ def test_host_buffer_entry(cabi, cuda_dev, oracle):
         6.0, 1.0, _cabi.ptr(scratch), 16, 0) == _cabi.DH_ERR_WORKSPACE_TOO_SMALL
 
 
+def test_host_entry_pipelines_large_inputs(cabi, cuda_dev, oracle):
+    """Inputs >= 2 MiB: the host entry copies them in chunks on its copy stream while earlier chunks render on two
+    alternating streams. Result and digest must equal the single-launch path (chunk_samples < 0) and the oracle."""
+    cfg = workloads.Config("pipe", 2048, 2, 32, 64, 4, 0, 64, 64, 96, 777)
+    w = workloads.make(cfg)
+    assert w.B * w.T * 28 >= (2 << 20)
+    ci, ri = oracle.radius_center(w.centers_f, w.bboxes_f, cfg.osf)
+    want = np.zeros((w.B, cfg.C, cfg.H, cfg.W), np.float32)
+    oracle.draw_batched(want, ci, ri, w.sizes, 6.0, 1.0, w.labels)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    cf, bf, s, lab = pin(w.centers_f), pin(w.bboxes_f), pin(w.sizes), pin(w.labels)
+    args = (w.B, w.T, cfg.C, cfg.H, cfg.W)
+    st = _cabi.stream_ptr()
+    nbytes = cabi.dh_host_scratch_bytes(*args, 1, 0, 0)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=cuda_dev)
+    ref_ck = oracle.digest_numpy(want)
+    results = []
+    for chunk in (-1, 0, 100, 1, 0):  # single launch | default chunks | 21 -> 16 chunks | B chunks -> 16 | again (reuse)
+        hd = torch.full(want.shape, 7.0, device=cuda_dev)
+        ck = torch.zeros(3, dtype=torch.int64).pin_memory()
+        l0 = cabi.dh_launch_count()
+        rc = cabi.dh_draw_heatmap_batched_from_boxes_host(
+            st, None, _cabi.ptr(hd), _cabi.ptr(ck), _cabi.ptr(cf), _cabi.ptr(bf), float(cfg.osf), _cabi.ptr(s),
+            _cabi.ptr(lab), *args, 6.0, 1.0, _cabi.ptr(scratch), nbytes, chunk)
+        _cabi.check(cabi, rc, "host entry (pipelined)")
+        torch.cuda.synchronize()
+        nl = cabi.dh_launch_count() - l0
+        assert (nl == 1) if chunk < 0 else (2 <= nl <= 16)
+        results.append(hd.cpu().numpy())
+        assert np.array_equal(ck.numpy(), oracle.digest_numpy(results[-1]))
+    for r in results[1:]:
+        assert np.array_equal(r, results[0])
+    assert np.abs(results[0] - want).max() <= 1e-6 and np.array_equal(results[0] > 0, want > 0)
+    del ref_ck
+
+
+def test_digest_index_bases_beyond_32_bits(cabi, cuda_dev, oracle):
+    """dh_checksum and the digest fused into the renderer agree with the numpy restatement when pixel indices need
+    more than 32 bits (index_base of a late shard of a very large job)."""
+    rng = np.random.default_rng(11)
+    v = (rng.random(50001, dtype=np.float32) * (rng.random(50001) < 0.3)).astype(np.float32)
+    for base in (0, (1 << 32) - 7, (1 << 33) + 5, (1 << 40) + 123):
+        d = _cabi.checksum(cabi, _dev(v, cuda_dev), base).cpu().numpy()
+        assert np.array_equal(d, oracle.digest_numpy(v, base))
+    w = workloads.make("cfg1")
+    cfg = w.cfg
+    heat = torch.empty((w.B, cfg.C, cfg.H, cfg.W), device=cuda_dev)
+    for base in (0, (1 << 32) - 1000, (1 << 35) + 64):
+        dg = torch.zeros(3, dtype=torch.int64, device=cuda_dev)
+        rc = cabi.dh_draw_heatmap_batched_from_boxes_digest(
+            _cabi.stream_ptr(), _cabi.ptr(heat), _cabi.ptr(_dev(w.centers_f, cuda_dev)), _cabi.ptr(_dev(w.bboxes_f, cuda_dev)),
+            float(cfg.osf), _cabi.ptr(_dev(w.sizes, cuda_dev)), _cabi.DH_SIZES_I64, _cabi.ptr(_dev(w.labels, cuda_dev)),
+            w.B, w.T, cfg.C, cfg.H, cfg.W, 6.0, 1.0, base, _cabi.ptr(dg), None)
+        _cabi.check(cabi, rc, "fused digest")
+        torch.cuda.synchronize()
+        assert np.array_equal(dg.cpu().numpy(), oracle.digest_numpy(heat.cpu().numpy(), base))
+
+
 def test_expf_is_monotone_and_close_to_correctly_rounded(cabi, cuda_dev):
     """Exhaustive over every fp32 in [-104, -0]: the renderer's expf is monotone (so one expf per pixel is bit-identical
     to max over per-object expf) and within 2 ulp of the correctly rounded value (the oracle's exp)."""
