@@ -7,11 +7,14 @@
 * :func:`render_heatmap_from_boxes` — K1 fused into the renderer: float boxes in, heatmap out, one launch.
 * :class:`RaggedBatch` — minimal stand-in for accvlab.batching_helpers.RaggedBatch (fields ``tensor``,
   ``sample_sizes``; /root/reference/packages/batching_helpers/accvlab/batching_helpers/data_format/ragged_batch.py:109-171).
+* :func:`combine_data`, :func:`pack_radius_center` — per-sample tensor lists -> RaggedBatch in ONE launch (the
+  reference: one slice-assign kernel per sample, batching_helpers/batched_processing_py.py:275-438,
+  DH/examples/draw_heatmap_batched.py:42-50); the second applies K1 on the way.
 * :func:`shard_range` — contiguous batch slice of a rank (multi-GPU: no collective on the data path).
 """
 from __future__ import annotations
 
-from typing import Optional, Tuple
+from typing import Optional, Sequence, Tuple, Union
 
 import torch
 
@@ -23,6 +26,8 @@ __all__ = [
     "render_heatmap_batched",
     "render_heatmap_from_boxes",
     "render_heatmap_flat",
+    "combine_data",
+    "pack_radius_center",
     "shard_range",
     "launch_count",
     "fill_probe",
@@ -118,6 +123,58 @@ def render_heatmap_flat(centers: torch.Tensor, radii: torch.Tensor, heatmap_idxe
         out = torch.empty((num_heatmaps, height, width), dtype=torch.float32, device=centers.device)
     _ext.render_heatmap_flat(out, centers, radii, heatmap_idxes, diameter_to_sigma_factor, k_scale, True)
     return out
+
+
+def _flatten(data) -> list:
+    """Depth-first flattening of a (nested) sequence of tensors (batched_processing_py.py:373-397)."""
+    if isinstance(data, torch.Tensor):
+        return [data]
+    if isinstance(data, Sequence) and not isinstance(data, str):
+        out = []
+        for el in data:
+            out += _flatten(el)
+        return out
+    raise AssertionError(f"The data to combine must be a tensor or a (nested) sequence of tensors. Got {type(data)}.")
+
+
+def combine_data(data_list: Sequence[Union[Sequence, torch.Tensor]], other_with_same_sample_sizes: Optional[RaggedBatch] = None,
+                 device: Optional[Union[torch.device, str]] = None, flatten_batch_dims: bool = True,
+                 max_sample_size: Optional[int] = None) -> RaggedBatch:
+    """``accvlab.batching_helpers.combine_data`` for CUDA inputs (batched_processing_py.py:275-438, flattening mode):
+    a (nested) sequence of per-sample tensors ``[n_i, *data]`` -> ``RaggedBatch`` with ``tensor [B, max n_i, *data]``
+    (zero padded) and int64 ``sample_sizes``. One kernel launch + one small H2D copy instead of one slice-assign per
+    sample. ``max_sample_size`` (extension) pads to a fixed length. There is no CPU path: every element must live on
+    the target CUDA device."""
+    assert isinstance(data_list, Sequence), "`data_list` must be a sequence"
+    assert len(data_list) > 0, "`data_list` must not be empty"
+    if not flatten_batch_dims:
+        raise NotImplementedError("only flatten_batch_dims=True (one batch dimension) feeds draw_heatmap")
+    flat = _flatten(data_list)
+    if device is not None:
+        dev = torch.device(device)
+        if dev.type == "cuda" and dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        for el in flat:
+            if el.device != dev:
+                raise RuntimeError(f"combine_data: element on {el.device}, expected {dev} (no CPU path, no implicit copies)")
+    tensor, sizes = _ext.combine_data([el.contiguous() for el in flat], -1 if max_sample_size is None else int(max_sample_size))
+    if other_with_same_sample_sizes is not None:
+        assert len(flat) == other_with_same_sample_sizes.sample_sizes.shape[0], \
+            "Number of samples does not match `other_with_same_sample_sizes`"
+        assert tensor.shape[1] == other_with_same_sample_sizes.tensor.shape[1], \
+            "Needed mask dimension does not match `other_with_same_sample_sizes`"
+        return RaggedBatch(tensor, mask=other_with_same_sample_sizes._mask, sample_sizes=other_with_same_sample_sizes.sample_sizes)
+    return RaggedBatch(tensor, sample_sizes=sizes)
+
+
+def pack_radius_center(centers_list: Sequence[torch.Tensor], bboxes_list: Sequence[torch.Tensor], out_size_factor: float,
+                       max_sample_size: Optional[int] = None) -> Tuple[RaggedBatch, RaggedBatch]:
+    """Per-sample float centres ``[n_i,2]`` and boxes ``[n_i,4]`` -> (``centers`` int32 ``[B,T,2]``, ``radii`` int32
+    ``[B,T]``) RaggedBatches sharing one int64 ``sample_sizes``: combine_data + get_centers_and_radii
+    (DH/tests/_test_helpers.py:20-28) in one launch, ready for ``draw_heatmap_batched``."""
+    c, r, sizes = _ext.pack_radius_center([t.contiguous() for t in centers_list], [t.contiguous() for t in bboxes_list],
+                                          float(out_size_factor), -1 if max_sample_size is None else int(max_sample_size))
+    return RaggedBatch(c, sample_sizes=sizes), RaggedBatch(r, sample_sizes=sizes)
 
 
 def shard_range(batch_size: int, rank: int, world_size: int) -> Tuple[int, int]:

@@ -25,6 +25,7 @@
 #include <atomic>
 
 #include "dh_b200.h"
+#include "dh_k1.cuh"
 
 #define DH_STR2(x) #x
 #define DH_STR(x) DH_STR2(x)
@@ -70,16 +71,7 @@ struct RenderParams {
 };
 
 // ------------------------------------------------------------------------------------------------
-// K1 arithmetic (tests/_test_helpers.py:20-28), shared by the stand-alone kernel and SRC_BOXES.
-__device__ __forceinline__ void radius_center_one(float cx, float cy, float x1, float y1, float x2, float y2,
-                                                  float osf, int& xi, int& yi, int& r) {
-    const float m = fminf(fminf(__fsub_rn(cx, x1), __fsub_rn(cy, y1)), fminf(__fsub_rn(x2, cx), __fsub_rn(y2, cy)));
-    r = (int)ceilf(__fdiv_rn(m, osf));
-    if (r < 1) r = 1;
-    xi = (int)__fdiv_rn(cx, osf);
-    yi = (int)__fdiv_rn(cy, osf);
-}
-
+// K1 arithmetic: dh_k1.cuh (shared with dh_pack.cu)
 __global__ void __launch_bounds__(256) radius_center_kernel(const float* __restrict__ centers,
                                                             const float* __restrict__ bboxes, float osf, long long n,
                                                             int32_t* __restrict__ centers_out,

@@ -1,0 +1,118 @@
+// dh_pack.cu — list-of-tensors -> RaggedBatch packing, optionally fused with K1.
+//
+// Replaces the step BEFORE the renderer in the reference's callers: a Python loop of one slice-assign kernel per
+// sample and per array into a torch.zeros tensor
+//   /root/reference/packages/batching_helpers/accvlab/batching_helpers/batched_processing_py.py:411-423 (combine_data)
+//   /root/reference/packages/draw_heatmap/examples/draw_heatmap_batched.py:42-50
+// by ONE launch per array: a device table of B source pointers + B sizes, every destination element written exactly
+// once (payload or the zero padding: the torch.zeros pass is fused in), coalesced.
+// dh_pack_radius_center additionally applies K1 (dh_k1.cuh) on the way, so per-sample float centre / box lists become
+// the int32 centres + radii RaggedBatch tensors draw_heatmap_batched takes, in one launch.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dh_b200.h"
+#include "dh_k1.cuh"
+
+namespace dh {
+
+extern void count_launches(uint64_t n);  // dh_kernels.cu
+
+__device__ __forceinline__ long long clamp_size(const int64_t* __restrict__ sizes, long long b, long long T) {
+    long long n = sizes[b];
+    return n < 0 ? 0 : (n > T ? T : n);
+}
+
+// dst [B, T*R] elements of type E; sample b: the first min(sizes[b],T)*R elements from src[b], zeros after.
+// grid.x covers one sample's T*R elements, grid.y strides over samples.
+template <typename E>
+__global__ void __launch_bounds__(256) pack_kernel(E* __restrict__ dst, const void* const* __restrict__ src,
+                                                   const int64_t* __restrict__ sizes, long long B, long long T,
+                                                   long long R) {
+    const long long per = T * R;
+    for (long long b = blockIdx.y; b < B; b += gridDim.y) {
+        const long long n = clamp_size(sizes, b, T) * R;
+        const E* __restrict__ s = n > 0 ? static_cast<const E*>(src[b]) : nullptr;
+        E* __restrict__ d = dst + b * per;
+        for (long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x; j < per; j += (long long)gridDim.x * blockDim.x)
+            d[j] = j < n ? s[j] : E{};
+    }
+}
+
+struct alignas(16) B16 {
+    unsigned x = 0, y = 0, z = 0, w = 0;
+};
+
+// K1 fused: per-sample float centres [n,2] and boxes [n,4] -> int centres [B,T,2], radii [B,T]; padding = 0.
+__global__ void __launch_bounds__(256) pack_k1_kernel(const float* const* __restrict__ csrc, const float* const* __restrict__ bsrc,
+                                                      const int64_t* __restrict__ sizes, float osf, long long B, long long T,
+                                                      int32_t* __restrict__ centers_out, int32_t* __restrict__ radii_out) {
+    for (long long b = blockIdx.y; b < B; b += gridDim.y) {
+        const long long n = clamp_size(sizes, b, T);
+        const float2* __restrict__ c = n > 0 ? reinterpret_cast<const float2*>(csrc[b]) : nullptr;
+        const float4* __restrict__ bx = n > 0 ? reinterpret_cast<const float4*>(bsrc[b]) : nullptr;
+        int2* __restrict__ co = reinterpret_cast<int2*>(centers_out) + b * T;
+        int32_t* __restrict__ ro = radii_out + b * T;
+        for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < T; t += (long long)gridDim.x * blockDim.x) {
+            int xi = 0, yi = 0, r = 0;
+            if (t < n) {
+                const float2 cc = c[t];
+                const float4 bb = bx[t];
+                radius_center_one(cc.x, cc.y, bb.x, bb.y, bb.z, bb.w, osf, xi, yi, r);
+            }
+            co[t] = make_int2(xi, yi);
+            ro[t] = r;
+        }
+    }
+}
+
+static dim3 pack_grid(long long per, long long B) {
+    long long gx = (per + 255) / 256;
+    if (gx < 1) gx = 1;
+    if (gx > 4096) gx = 4096;
+    return dim3((unsigned)gx, (unsigned)(B < 65535 ? B : 65535), 1);
+}
+
+}  // namespace dh
+
+extern "C" {
+
+int dh_pack_ragged(void* stream, void* dst, const void* const* src_ptrs, const int64_t* sizes, int64_t B, int64_t T,
+                   int64_t row_elems, int elem_bytes) {
+    if (B < 0 || T < 0 || row_elems < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (elem_bytes != 1 && elem_bytes != 2 && elem_bytes != 4 && elem_bytes != 8 && elem_bytes != 16)
+        return DH_ERR_INVALID_ARGUMENT;
+    if (B == 0 || T == 0 || row_elems == 0) return DH_OK;
+    if (!dst || !src_ptrs || !sizes) return DH_ERR_INVALID_ARGUMENT;
+    if (reinterpret_cast<uintptr_t>(dst) % (uintptr_t)elem_bytes) return DH_ERR_INVALID_ARGUMENT;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) return DH_ERR_NO_DEVICE;
+    const dim3 g = dh::pack_grid(T * row_elems, B);
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (elem_bytes) {
+        case 1: dh::pack_kernel<uint8_t><<<g, 256, 0, s>>>((uint8_t*)dst, src_ptrs, sizes, B, T, row_elems); break;
+        case 2: dh::pack_kernel<uint16_t><<<g, 256, 0, s>>>((uint16_t*)dst, src_ptrs, sizes, B, T, row_elems); break;
+        case 4: dh::pack_kernel<uint32_t><<<g, 256, 0, s>>>((uint32_t*)dst, src_ptrs, sizes, B, T, row_elems); break;
+        case 8: dh::pack_kernel<uint64_t><<<g, 256, 0, s>>>((uint64_t*)dst, src_ptrs, sizes, B, T, row_elems); break;
+        default: dh::pack_kernel<dh::B16><<<g, 256, 0, s>>>((dh::B16*)dst, src_ptrs, sizes, B, T, row_elems); break;
+    }
+    dh::count_launches(1);
+    return (int)cudaGetLastError();
+}
+
+int dh_pack_radius_center(void* stream, const float* const* centers_ptrs, const float* const* bboxes_ptrs,
+                          const int64_t* sizes, float out_size_factor, int64_t B, int64_t T, int32_t* centers_out,
+                          int32_t* radii_out) {
+    if (B < 0 || T < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (B == 0 || T == 0) return DH_OK;
+    if (!centers_ptrs || !bboxes_ptrs || !sizes || !centers_out || !radii_out) return DH_ERR_INVALID_ARGUMENT;
+    if (reinterpret_cast<uintptr_t>(centers_out) & 7u) return DH_ERR_INVALID_ARGUMENT;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) return DH_ERR_NO_DEVICE;
+    dh::pack_k1_kernel<<<dh::pack_grid(T, B), 256, 0, (cudaStream_t)stream>>>(centers_ptrs, bboxes_ptrs, sizes,
+                                                                             out_size_factor, B, T, centers_out, radii_out);
+    dh::count_launches(1);
+    return (int)cudaGetLastError();
+}
+
+}  // extern "C"

@@ -10,7 +10,9 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/extension.h>
 
+#include <algorithm>
 #include <tuple>
+#include <vector>
 
 #include "dh_b200.h"
 
@@ -300,6 +302,111 @@ void render_heatmap_from_boxes_host(const c10::optional<at::Tensor>& heatmap_hos
                  "render_heatmap_from_boxes_host");
 }
 
+// ---- N1: list of per-sample tensors -> padded RaggedBatch tensor (+ sample sizes), one launch -----------------
+// Host side of dh_pack_ragged / dh_pack_radius_center: the B source pointers and B sizes go into ONE pinned host
+// table that crosses PCIe in one asynchronous copy (stream-ordered; the caching host allocator keeps the block alive
+// until the copy has run). Replaces the per-sample slice-assign loop of combine_data
+// (batching_helpers/batched_processing_py.py:411-423) and of DH/examples/draw_heatmap_batched.py:42-50.
+struct PackTable {
+    at::Tensor dev;  // int64 [n_arrays*B + B]: pointer columns, then sizes
+    int64_t B = 0, T = 0;
+};
+
+PackTable make_pack_table(const std::vector<const std::vector<at::Tensor>*>& lists, int64_t max_sample_size) {
+    const auto& first = *lists[0];
+    const int64_t B = (int64_t)first.size();
+    TORCH_CHECK(B > 0, "`data_list` must not be empty");
+    const int64_t na = (int64_t)lists.size();
+    at::Tensor host = at::empty({(na + 1) * B}, at::TensorOptions().dtype(at::kLong).pinned_memory(true));
+    int64_t* h = host.data_ptr<int64_t>();
+    int64_t T = 0;
+    const at::Device device = first[0].device();
+    for (int64_t i = 0; i < B; ++i) {
+        const at::Tensor& el = first[i];
+        const int64_t n = el.dim() == 0 ? 0 : std::min<int64_t>(el.size(0), el.numel());
+        for (int64_t a = 0; a < na; ++a) {
+            const at::Tensor& t = (*lists[a])[i];
+            TORCH_CHECK(t.is_cuda() && t.device() == device, "all list elements must be CUDA tensors on one device");
+            TORCH_CHECK(t.is_contiguous(), "list elements must be contiguous");
+            const int64_t nt = t.dim() == 0 ? 0 : std::min<int64_t>(t.size(0), t.numel());
+            TORCH_CHECK(nt == n, "lists disagree on the size of sample ", i);
+            h[a * B + i] = (int64_t) reinterpret_cast<uintptr_t>(t.data_ptr());
+        }
+        h[na * B + i] = n;
+        T = std::max(T, n);
+    }
+    if (max_sample_size >= 0) {
+        TORCH_CHECK(max_sample_size >= T, "max_sample_size (", max_sample_size, ") is smaller than the largest sample (", T, ")");
+        T = max_sample_size;
+    }
+    PackTable r;
+    r.dev = host.to(device, /*non_blocking=*/true);
+    r.B = B;
+    r.T = T;
+    return r;
+}
+
+std::tuple<at::Tensor, at::Tensor> combine_data(const std::vector<at::Tensor>& data_list, int64_t max_sample_size) {
+    TORCH_CHECK(!data_list.empty(), "`data_list` must not be empty");
+    const at::Tensor* sample = nullptr;  // first non-empty element defines dtype and trailing dims
+    for (const auto& t : data_list)
+        if (t.numel() > 0) {
+            sample = &t;
+            break;
+        }
+    if (!sample) sample = &data_list[0];
+    std::vector<int64_t> trailing;
+    for (int64_t d = 1; d < sample->dim(); ++d) trailing.push_back(sample->size(d));
+    int64_t row = 1;
+    for (auto v : trailing) row *= v;
+    for (const auto& t : data_list) {
+        TORCH_CHECK(t.scalar_type() == sample->scalar_type(), "all list elements must have the same dtype");
+        if (t.numel() > 0) {
+            TORCH_CHECK(t.dim() == sample->dim(), "all non-empty list elements must have the same number of dimensions");
+            for (int64_t d = 1; d < t.dim(); ++d)
+                TORCH_CHECK(t.size(d) == sample->size(d), "list elements must match in every dimension but the first");
+        }
+    }
+    c10::cuda::CUDAGuard guard(sample->device());
+    PackTable tab = make_pack_table({&data_list}, max_sample_size);
+    std::vector<int64_t> shape = {tab.B, tab.T};
+    shape.insert(shape.end(), trailing.begin(), trailing.end());
+    at::Tensor out = at::empty(shape, sample->options());
+    const int64_t* d = tab.dev.data_ptr<int64_t>();
+    check_status(dh_pack_ragged(at::cuda::getCurrentCUDAStream().stream(), out.data_ptr(),
+                                reinterpret_cast<const void* const*>(d), d + tab.B, tab.B, tab.T, row,
+                                (int)sample->element_size()),
+                 "combine_data");
+    return {out, tab.dev.slice(0, tab.B, 2 * tab.B)};
+}
+
+std::tuple<at::Tensor, at::Tensor, at::Tensor> pack_radius_center(const std::vector<at::Tensor>& centers_list,
+                                                                  const std::vector<at::Tensor>& bboxes_list,
+                                                                  double out_size_factor, int64_t max_sample_size) {
+    TORCH_CHECK(!centers_list.empty(), "`centers_list` must not be empty");
+    TORCH_CHECK(centers_list.size() == bboxes_list.size(), "centers_list and bboxes_list must have the same length");
+    for (size_t i = 0; i < centers_list.size(); ++i) {
+        const at::Tensor &c = centers_list[i], &b = bboxes_list[i];
+        TORCH_CHECK(c.scalar_type() == at::kFloat && b.scalar_type() == at::kFloat, "centres and boxes must be float32");
+        TORCH_CHECK(c.numel() == 0 || (c.dim() == 2 && c.size(1) == 2), "centres must be of shape [n, 2]");
+        TORCH_CHECK(b.numel() == 0 || (b.dim() == 2 && b.size(1) == 4), "bboxes must be of shape [n, 4]");
+        TORCH_CHECK(reinterpret_cast<uintptr_t>(c.data_ptr()) % 8 == 0 && reinterpret_cast<uintptr_t>(b.data_ptr()) % 16 == 0,
+                    "centres / boxes must be aligned to their row size (8 / 16 bytes)");
+    }
+    c10::cuda::CUDAGuard guard(centers_list[0].device());
+    PackTable tab = make_pack_table({&centers_list, &bboxes_list}, max_sample_size);
+    auto opt = centers_list[0].options().dtype(at::kInt);
+    at::Tensor centers_out = at::empty({tab.B, tab.T, 2}, opt), radii_out = at::empty({tab.B, tab.T}, opt);
+    const int64_t* d = tab.dev.data_ptr<int64_t>();
+    check_status(dh_pack_radius_center(at::cuda::getCurrentCUDAStream().stream(),
+                                       reinterpret_cast<const float* const*>(d),
+                                       reinterpret_cast<const float* const*>(d + tab.B), d + 2 * tab.B,
+                                       (float)out_size_factor, tab.B, tab.T, centers_out.data_ptr<int>(),
+                                       radii_out.data_ptr<int>()),
+                 "pack_radius_center");
+    return {centers_out, radii_out, tab.dev.slice(0, 2 * tab.B, 3 * tab.B)};
+}
+
 void fill_probe(at::Tensor& t) {
     CHECK_INPUT(t);
     c10::cuda::CUDAGuard guard(t.device());
@@ -351,6 +458,13 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           pybind11::arg("nums_targets"), pybind11::arg("labels"), pybind11::arg("num_classes"), pybind11::arg("height"),
           pybind11::arg("width"), pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f,
           pybind11::arg("scratch"), pybind11::arg("chunk_samples") = 0);
+    m.def("combine_data", &combine_data,
+          "List of per-sample CUDA tensors [n_i, *data] -> (zero-padded tensor [B, T, *data], int64 sample sizes [B]); one launch.",
+          pybind11::arg("data_list"), pybind11::arg("max_sample_size") = -1);
+    m.def("pack_radius_center", &pack_radius_center,
+          "Per-sample float centres [n_i,2] / boxes [n_i,4] -> (int32 centres [B,T,2], int32 radii [B,T], int64 sizes [B]), K1 fused.",
+          pybind11::arg("centers_list"), pybind11::arg("bboxes_list"), pybind11::arg("out_size_factor"),
+          pybind11::arg("max_sample_size") = -1);
     m.def("launch_count", []() { return dh_launch_count(); }, "Kernels launched by this library in this process.");
     m.def("build_info", []() { return std::string(dh_build_info()); });
 }

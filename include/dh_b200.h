@@ -181,6 +181,23 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream, float* heatmap_host, f
                                             float k_scale, void* device_scratch, size_t device_scratch_bytes,
                                             int64_t chunk_samples);
 
+/* ---- N1: list of per-sample arrays -> RaggedBatch layout (the step before the renderer) ----------------
+ * Replaces the per-sample slice-assign loop of combine_data
+ * (/root/reference/packages/batching_helpers/accvlab/batching_helpers/batched_processing_py.py:411-423) and of
+ * /root/reference/packages/draw_heatmap/examples/draw_heatmap_batched.py:42-50 by ONE launch.
+ * dst [B, T, row_elems] elements of `elem_bytes` (1,2,4,8,16) bytes; sample b takes its first
+ * n_b = clamp(sizes[b], 0, T) rows from src_ptrs[b] (row-major contiguous, aligned to elem_bytes) and ZEROS after
+ * (the reference starts from torch.zeros). `src_ptrs` (B device pointers) and `sizes` (int64 [B]) are DEVICE
+ * arrays; src_ptrs[b] is not dereferenced when n_b == 0. Every destination element is written exactly once. */
+int dh_pack_ragged(void* stream, void* dst, const void* const* src_ptrs, const int64_t* sizes, int64_t batch_size,
+                   int64_t max_sample_size, int64_t row_elems, int elem_bytes);
+
+/* Same with K1 fused (dh_radius_center arithmetic): per-sample float centres [n_b,2] (8-byte aligned) and boxes
+ * [n_b,4] (16-byte aligned) -> centers_out int32 [B,T,2] (8-byte aligned), radii_out int32 [B,T]; padded slots = 0. */
+int dh_pack_radius_center(void* stream, const float* const* centers_ptrs, const float* const* bboxes_ptrs,
+                          const int64_t* sizes, float out_size_factor, int64_t batch_size, int64_t max_sample_size,
+                          int32_t* centers_out, int32_t* radii_out);
+
 /* ---- measurement helper ---------------------------------------------------------------
  * Pure 128-bit-store fill of `bytes` bytes (multiple of 16, 16-byte aligned) with zeros using the same
  * store path and grid shape as the FRESH renderer: the write-only ceiling the renderer is compared to. */

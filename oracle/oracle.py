@@ -216,3 +216,31 @@ def digest_numpy(values, index_base=0):
         idx = np.nonzero(v > 0)[0].astype(np.uint64) + np.uint64(index_base)
         s_hash = _mix_index(idx).sum(dtype=np.uint64) if idx.size else np.uint64(0)
     return np.array([s_bits, s_hash, np.uint64(idx.size)], dtype=np.uint64).view(np.int64)
+
+
+# ---- N1: list -> RaggedBatch packing, numpy restatement ---------------------------------------------------
+def combine_data_numpy(samples, max_sample_size=None):
+    """combine_data, flattening mode (/root/reference/packages/batching_helpers/accvlab/batching_helpers/
+    batched_processing_py.py:398-426): zeros [B, max n_i, *data], sample i's n_i = min(shape[0], size) rows copied to
+    the front; dtype and trailing dims from the first non-empty sample; int64 sample sizes."""
+    samples = [np.asarray(s) for s in samples]
+    sizes = np.array([min(s.shape[0], s.size) if s.ndim else 0 for s in samples], dtype=np.int64)
+    ne = [s for s in samples if s.size > 0]
+    sample = ne[0] if ne else samples[0]
+    T = int(sizes.max()) if max_sample_size is None else int(max_sample_size)
+    out = np.zeros((len(samples), T) + tuple(sample.shape[1:]), dtype=sample.dtype)
+    for i, s in enumerate(samples):
+        if sizes[i] > 0:
+            out[i, : sizes[i]] = s
+    return out, sizes
+
+
+def pack_radius_center_numpy(centers_list, bboxes_list, osf, max_sample_size=None):
+    """combine_data + get_centers_and_radii (DH/tests/_test_helpers.py:20-28) on the valid slots; padded slots = 0."""
+    c, sizes = combine_data_numpy([np.asarray(a, np.float32).reshape(-1, 2) for a in centers_list], max_sample_size)
+    b, _ = combine_data_numpy([np.asarray(a, np.float32).reshape(-1, 4) for a in bboxes_list], max_sample_size)
+    ci, ri = radius_center(c, b, osf)
+    pad = np.arange(c.shape[1])[None, :] >= sizes[:, None]
+    ci[pad] = 0
+    ri[pad] = 0
+    return ci, ri, sizes

@@ -42,6 +42,8 @@ SIGNATURES = {
     "dh_host_scratch_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _i, _i64, _i]),
     "dh_draw_heatmap_batched_from_boxes_host": (_i, [_p, _p, _p, _p, _p, _p, _f, _p, _p, _i64, _i64, _i64, _i64, _i64,
                                                      _f, _f, _p, _sz, _i64]),
+    "dh_pack_ragged": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i]),
+    "dh_pack_radius_center": (_i, [_p, _p, _p, _p, _f, _i64, _i64, _p, _p]),
     "dh_fill_probe": (_i, [_p, _p, _sz]),
     "dh_expf_probe": (_i, [_p, ctypes.c_uint32, _i64, _p]),
 }
