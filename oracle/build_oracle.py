@@ -11,6 +11,12 @@ build_reference_gpu() nvcc/g++ on the UNMODIFIED reference sources, compiled fro
                  (--ftz=false) for `dh_ref_ieee`; arch fixed to sm_100a (the reference auto-detects the GPU).
         The reference's own setup.py / build system is NOT run.
 
+build_reference_dali() g++ on the UNMODIFIED reference DALI operator source
+                      /root/reference/packages/dali_pipeline_framework/ext_impl/DrawGaussians.cc (+ .h), compiled from
+                      where it lies against oracle/dali_stub (a minimal stand-in for the DALI headers it includes:
+                      DALI itself is not installed) plus oracle/dg_ref_driver.cc       -> oracle/_ref/libdg_ref.so
+                      The reference's CMake build is NOT run.
+
 oracle/_ref/ is git-ignored but travels to the GPU box; /root/reference does not exist there, so
 build_reference_gpu() is a no-op when the sources are absent.
 """
@@ -84,7 +90,25 @@ def build_reference_gpu(force: bool = False) -> dict:
     return {k: (v if os.path.exists(v) else None) for k, v in paths.items()}
 
 
+REF_DPF = "/root/reference/packages/dali_pipeline_framework/ext_impl"
+
+
+def build_reference_dali(force: bool = False):
+    """Compile the reference's draw_gaussians operator source against the DALI stub. Returns the path or None."""
+    out = os.path.join(REF_OUT, "libdg_ref.so")
+    cc, hh = os.path.join(REF_DPF, "DrawGaussians.cc"), os.path.join(REF_DPF, "DrawGaussians.h")
+    drv = os.path.join(HERE, "dg_ref_driver.cc")
+    if not (os.path.exists(cc) and os.path.exists(hh)):
+        return out if os.path.exists(out) else None
+    if force or not _newer(out, [cc, hh, drv]):
+        os.makedirs(REF_OUT, exist_ok=True)
+        _run(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-fvisibility=hidden",
+              f"-I{os.path.join(HERE, 'dali_stub')}", f"-I{REF_DPF}", drv, cc, "-o", out])
+    return out
+
+
 if __name__ == "__main__":
     build_c_oracle(force="--force" in sys.argv)
     if "--ref" in sys.argv:
         print(build_reference_gpu(force="--force" in sys.argv))
+        print(build_reference_dali(force="--force" in sys.argv))

@@ -39,6 +39,8 @@ def lib() -> ctypes.CDLL:
         L.dho_refcpu_draw_batched.argtypes = [c_p, c_p, c_p, c_p, c_p] + [c_i64] * 5 + [ctypes.c_double, c_f,
                                                                                        ctypes.c_int, ctypes.c_int]
         L.dho_refcpu_draw_batched.restype = None
+        L.dho_draw_gaussians.argtypes = [c_p] * 7 + [c_i64] * 6 + [c_f]
+        L.dho_draw_gaussians.restype = None
         _LIB = L
     return _LIB
 
@@ -244,3 +246,22 @@ def pack_radius_center_numpy(centers_list, bboxes_list, osf, max_sample_size=Non
     ci[pad] = 0
     ri[pad] = 0
     return ci, ri, sizes
+
+
+# ---- N2: DALI draw_gaussians semantics (dh_oracle.c: dho_draw_gaussians) -----------------------------------
+def draw_gaussians(heat, centers, radii, sizes, k_for_classes, radius_to_sigma_factor, slice_ids=None, active=None):
+    """In place on heat f32 [B,C,H,W] (or [B,H,W] -> C=1). centers i32 [B,T,2], radii f32 [B,T], slice_ids i32 [B,T],
+    active bool [B,T], sizes [B]. Restates DrawGaussians.cc:31-75,88-157 (see dh_oracle.c)."""
+    assert heat.dtype == np.float32 and heat.flags.c_contiguous
+    shape4 = heat.shape if heat.ndim == 4 else (heat.shape[0], 1) + heat.shape[1:]
+    B, C, H, W = shape4
+    centers = _c(centers, np.int32)
+    radii = _c(radii, np.float32)
+    T = radii.shape[1] if radii.ndim == 2 else 0
+    sizes = _c(sizes, np.int64)
+    k = _c(k_for_classes, np.float32).reshape(-1)
+    sl = None if slice_ids is None else _c(slice_ids, np.int32)
+    ac = None if active is None else _c(np.asarray(active).astype(np.uint8), np.uint8)
+    lib().dho_draw_gaussians(_ptr(heat), _ptr(centers), _ptr(radii), _ptr(sl), _ptr(ac), _ptr(sizes), _ptr(k), k.size,
+                             B, T, C, H, W, float(radius_to_sigma_factor))
+    return heat
