@@ -10,6 +10,8 @@
 * :func:`combine_data`, :func:`pack_radius_center` — per-sample tensor lists -> RaggedBatch in ONE launch (the
   reference: one slice-assign kernel per sample, batching_helpers/batched_processing_py.py:275-438,
   DH/examples/draw_heatmap_batched.py:42-50); the second applies K1 on the way.
+* :func:`draw_gaussians` — the DALI ``draw_gaussians`` operator semantics (CPU-only in the reference:
+  dali_pipeline_framework/ext_impl/DrawGaussians.cc:31-157) as a GPU op on RaggedBatch inputs.
 * :func:`shard_range` — contiguous batch slice of a rank (multi-GPU: no collective on the data path).
 """
 from __future__ import annotations
@@ -26,6 +28,7 @@ __all__ = [
     "render_heatmap_batched",
     "render_heatmap_from_boxes",
     "render_heatmap_flat",
+    "draw_gaussians",
     "combine_data",
     "pack_radius_center",
     "shard_range",
@@ -123,6 +126,35 @@ def render_heatmap_flat(centers: torch.Tensor, radii: torch.Tensor, heatmap_idxe
         out = torch.empty((num_heatmaps, height, width), dtype=torch.float32, device=centers.device)
     _ext.render_heatmap_flat(out, centers, radii, heatmap_idxes, diameter_to_sigma_factor, k_scale, True)
     return out
+
+
+def draw_gaussians(heatmap: Optional[torch.Tensor], active, slice_ids, centers, radii, k_for_classes,
+                   radius_to_sigma_factor: float, out: Optional[torch.Tensor] = None,
+                   shape: Optional[Tuple[int, ...]] = None) -> torch.Tensor:
+    """GPU version of the reference's DALI operator ``draw_gaussians(heatmap, active, slice_ids, centers, radii,
+    k_for_classes=..., radius_to_sigma_factor=...)`` (ext_impl/DrawGaussians.cc:88-157; Python call site
+    processing_steps/bounding_box_to_heatmap_converter.py:321-399): returns ``max(heatmap, per-class Gaussians)``.
+
+    Inputs are in the RaggedBatch layout instead of DALI's per-sample lists: ``centers`` int32 ``[B,T,2]``, ``radii``
+    float32 ``[B,T]``, ``slice_ids`` int32 ``[B,T]`` (or ``None``: class 0), ``active`` bool ``[B,T]`` (or ``None``),
+    each a ``RaggedBatch`` (``sample_sizes`` taken from ``radii``) or a plain tensor meaning "all T slots valid".
+    ``heatmap`` float32 ``[B,C,H,W]`` / ``[B,H,W]``; ``None`` renders a fresh heatmap of ``shape`` (zero-init fused).
+    ``out`` may be ``heatmap`` itself (in place); default: a new tensor, like the operator."""
+    r_t, sizes = _tensor_and_sizes(radii)
+    c_t, _ = _tensor_and_sizes(centers)
+    a_t = None if active is None else _tensor_and_sizes(active)[0]
+    s_t = None if slice_ids is None else _tensor_and_sizes(slice_ids)[0]
+    if sizes is None:
+        sizes = torch.full((r_t.shape[0],), r_t.shape[1], dtype=torch.int64, device=r_t.device)
+    if not isinstance(k_for_classes, torch.Tensor):
+        k_for_classes = torch.tensor(list(k_for_classes), dtype=torch.float32, device=r_t.device)
+    if out is None:
+        if heatmap is None:
+            assert shape is not None, "`shape` is needed when no input heatmap is given"
+            out = torch.empty(tuple(shape), dtype=torch.float32, device=r_t.device)
+        else:
+            out = torch.empty_like(heatmap)
+    return _ext.draw_gaussians(heatmap, out, a_t, s_t, c_t, r_t, sizes, k_for_classes, float(radius_to_sigma_factor))
 
 
 def _flatten(data) -> list:

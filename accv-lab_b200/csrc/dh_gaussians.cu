@@ -1,0 +1,283 @@
+// dh_gaussians.cu — N2: the DALI `draw_gaussians` operator semantics on the GPU.
+//
+// The reference implements this operator for the CPU only
+//   /root/reference/packages/dali_pipeline_framework/ext_impl/DrawGaussians.cc:31-75  (draw_gaussian)
+//   .../DrawGaussians.cc:88-157 (RunImpl: out = in; every ACTIVE object -> plane slice_id with k_for_classes[slice_id])
+// one thread-pool task per sample, serial loop over objects and window pixels. Differences to the draw_heatmap
+// kernel arithmetic: FLOAT radius, sigma = radius * factor, window [floor(c - r), ceil(c + r)]
+// (inclusive, can be asymmetric after fp32 rounding), per-class peak k, an `active` flag per object, and
+// max(pixel, val) = (pixel < val) ? val : pixel.
+//
+// Here: output-partitioned like the main renderer. One CTA per unit = a band of whole rows of one (sample, class)
+// plane (<= 4096 pixels). Per unit: the sample's T slots are scanned once (active / class / size filter, window
+// arithmetic exactly as the reference: floorf/ceilf of one fp32 add, clip, cull against the band), compacted with
+// warp ballot + popc prefix into a shared-memory list; every thread then owns 4 consecutive pixels x up to 4 items
+// in registers and keeps, per pixel, min_o t_o with t_o = (float)(dy^2+dx^2) * inv_o (max_o for k < 0): ONE expf per
+// touched pixel (expf is monotone, tests/test_gpu_properties.py), no atomics; the band is written once with 128-bit
+// stores (input copied / zero-init fused for untouched pixels; in-place calls write touched groups only).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dh_b200.h"
+
+namespace dh {
+
+extern void count_launches(uint64_t n);  // dh_kernels.cu
+
+constexpr int kGsThreads = 256;
+constexpr int kGsItems = 4;      // register-resident items (PX pixels each) per thread and pass
+constexpr int kGsListCap = 512;  // objects per shared-memory list chunk
+constexpr float kGsMaxRadius = 2048.0f;
+
+struct __align__(16) GObj {
+    int x0, x1, y0, y1;  // clipped window, inclusive
+    float cx, cy, inv;   // centre (exact ints as floats), 1 / (2 sigma^2)
+    int pad;
+};
+
+struct GsParams {
+    const float* in;  // may be null (FRESH) or == out (in place)
+    float* out;
+    const int32_t* centers;
+    const float* radii;
+    const int32_t* slice_ids;  // may be null -> class 0
+    const uint8_t* active;     // may be null -> all active
+    const void* sizes;
+    int sizes_i64;
+    const float* k_for_classes;
+    int num_k;
+    long long num_planes, total_units;
+    int C, T, H, W, band_rows, bands_per_plane;
+    float factor;
+    dh_status* status;
+};
+
+// Slot -> list entry for plane class `cls`, culled against rows [by0, by1]. Window arithmetic of DrawGaussians.cc:34-51.
+__device__ __forceinline__ bool gs_make(const GsParams& p, long long i, int cls, int by0, int by1, bool count, GObj& o) {
+    if (p.active != nullptr && p.active[i] == 0) return false;
+    const float r = p.radii[i];
+    if (!(fabsf(r) <= kGsMaxRadius)) {  // NaN or huge; counted once per object (by the sample's first unit)
+        if (count && p.status) atomicAdd(&p.status->skipped_radius, 1u);
+        return false;
+    }
+    const int c = p.slice_ids != nullptr ? p.slice_ids[i] : 0;
+    if (c != cls) {
+        if (count && p.status && (c < 0 || c >= p.C || c >= p.num_k)) atomicAdd(&p.status->skipped_label, 1u);
+        return false;
+    }
+    const int2 cc = *reinterpret_cast<const int2*>(p.centers + 2 * i);
+    const float fx = (float)cc.x, fy = (float)cc.y;
+    // |centre| beyond the map by more than the largest window: nothing to draw (also keeps float -> int casts defined)
+    if (fabsf(fx) > 16777216.0f || fabsf(fy) > 16777216.0f) return false;
+    const int min_x = (int)floorf(__fsub_rn(fx, r)), max_x = (int)ceilf(__fadd_rn(fx, r));
+    const int min_y = (int)floorf(__fsub_rn(fy, r)), max_y = (int)ceilf(__fadd_rn(fy, r));
+    if ((max_x < 0 || min_x >= p.W) || (max_y < 0 || min_y >= p.H)) return false;
+    o.x0 = min(max(0, min_x), p.W - 1);
+    o.x1 = min(max(0, max_x), p.W - 1);
+    o.y0 = min(max(0, min_y), p.H - 1);
+    o.y1 = min(max(0, max_y), p.H - 1);
+    if (o.x0 > o.x1 || o.y0 > o.y1) return false;  // negative radius: empty loops in the reference
+    if (o.y1 < by0 || o.y0 > by1) return false;
+    const float sigma = __fmul_rn(r, p.factor);
+    o.inv = __fdiv_rn(1.0f, __fmul_rn(__fmul_rn(2.0f, sigma), sigma));
+    o.cx = fx;
+    o.cy = fy;
+    o.pad = 0;
+    return true;
+}
+
+template <int PX, bool INPLACE>
+__global__ void __launch_bounds__(kGsThreads) gaussians_kernel(const GsParams p) {
+    __shared__ GObj s_list[kGsListCap];
+    __shared__ int s_cnt;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int wunits = p.W / PX;
+    const long long plane_elems = (long long)p.H * p.W;
+    const float INF = __int_as_float(0x7f800000);
+
+    for (long long u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+        const long long plane = u / p.bands_per_plane;
+        const int band = (int)(u - plane * p.bands_per_plane);
+        const int by0 = band * p.band_rows, by1 = min(by0 + p.band_rows, p.H) - 1;  // inclusive
+        const long long sample = plane / p.C;
+        const int cls = (int)(plane - sample * p.C);
+        long long ns = p.sizes_i64 ? reinterpret_cast<const long long*>(p.sizes)[sample]
+                                   : (long long)reinterpret_cast<const int*>(p.sizes)[sample];
+        ns = ns < 0 ? 0 : (ns > p.T ? p.T : ns);
+        const int n = (int)ns;
+        const bool class_ok = cls < p.num_k;
+        const float k = class_ok ? p.k_for_classes[cls] : 0.0f;
+        const bool kneg = k < 0.0f;
+        const bool count = (band == 0 && cls == 0);
+        const long long src = sample * p.T;
+        const float* const in_plane = p.in ? p.in + plane * plane_elems : nullptr;
+        float* const out_plane = p.out + plane * plane_elems;
+        const int nitems = (by1 - by0 + 1) * wunits;
+        const bool single = n <= kGsListCap;
+
+        auto build = [&](int c0, bool do_count) {  // list of slots [c0, c0 + cap) (block-wide; ends with a barrier)
+            __syncthreads();
+            if (tid == 0) s_cnt = 0;
+            __syncthreads();
+            const int c1 = min(n, c0 + kGsListCap);
+            for (int base = c0; base < c1; base += kGsThreads) {
+                const int t = base + tid;
+                GObj o;
+                const bool pred = (t < c1) && class_ok && gs_make(p, src + t, cls, by0, by1, do_count, o);
+                const unsigned bal = __ballot_sync(0xffffffffu, pred);
+                if (bal) {
+                    int pos = 0;
+                    if (lane == 0) pos = atomicAdd(&s_cnt, __popc(bal));
+                    pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(bal & ((1u << lane) - 1u));
+                    if (pred) s_list[pos] = o;
+                }
+            }
+            __syncthreads();
+            return s_cnt;
+        };
+
+        int cnt = single ? build(0, count) : 0;
+        if (single && cnt == 0) {  // nothing lands in this band
+            if constexpr (!INPLACE) {
+                for (int it = tid; it < nitems; it += kGsThreads) {
+                    const int row = by0 + it / wunits, col = (it % wunits) * PX;
+                    const long long idx = (long long)row * p.W + col;
+                    if constexpr (PX == 4) {
+                        const float4 v = in_plane ? *reinterpret_cast<const float4*>(in_plane + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        *reinterpret_cast<float4*>(out_plane + idx) = v;
+                    } else {
+                        out_plane[idx] = in_plane ? in_plane[idx] : 0.0f;
+                    }
+                }
+            }
+            continue;
+        }
+
+        for (int item0 = 0; item0 < nitems; item0 += kGsThreads * kGsItems) {
+            float best[kGsItems][PX];
+            unsigned touched = 0u;  // bit (q*PX + j)
+            int rows[kGsItems], cols[kGsItems];
+#pragma unroll
+            for (int q = 0; q < kGsItems; ++q) {
+                const int it = item0 + q * kGsThreads + tid;
+                const bool valid = it < nitems;
+                rows[q] = valid ? by0 + it / wunits : -1 - (1 << 30);  // invalid items fail every row test
+                cols[q] = valid ? (it % wunits) * PX : 0;
+#pragma unroll
+                for (int j = 0; j < PX; ++j) best[q][j] = INF;
+            }
+            for (int c0 = 0; c0 < (single ? 1 : n); c0 += kGsListCap) {
+                if (!single) cnt = build(c0, count && item0 == 0);
+                for (int e = 0; e < cnt; ++e) {
+                    const GObj o = s_list[e];  // broadcast
+#pragma unroll
+                    for (int q = 0; q < kGsItems; ++q) {
+                        if (rows[q] < o.y0 || rows[q] > o.y1) continue;
+                        if (cols[q] > o.x1 || cols[q] + (PX - 1) < o.x0) continue;
+                        const float fdy = (float)rows[q] - o.cy;
+                        const float fy2 = __fmul_rn(fdy, fdy);
+#pragma unroll
+                        for (int j = 0; j < PX; ++j) {
+                            const int x = cols[q] + j;
+                            const float fdx = (float)x - o.cx;
+                            // (float)(dy^2 + dx^2): both squares are exact (< 2^24), the sum rounds once like the int -> float cast
+                            float t = __fmul_rn(__fadd_rn(fy2, __fmul_rn(fdx, fdx)), o.inv);
+                            t = kneg ? -t : t;
+                            if (x >= o.x0 && x <= o.x1 && t == t) {  // NaN (0 * inf) never wins the reference's max
+                                best[q][j] = fminf(best[q][j], t);
+                                touched |= 1u << (q * PX + j);
+                            }
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < kGsItems; ++q) {
+                if (rows[q] < 0) continue;
+                const unsigned tq = (touched >> (q * PX)) & ((1u << PX) - 1u);
+                if (INPLACE && tq == 0u) continue;
+                const long long idx = (long long)rows[q] * p.W + cols[q];
+                float v[PX];
+                if constexpr (PX == 4) {
+                    const float4 a = in_plane ? *reinterpret_cast<const float4*>(in_plane + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+                } else {
+                    v[0] = in_plane ? in_plane[idx] : 0.0f;
+                }
+#pragma unroll
+                for (int j = 0; j < PX; ++j) {
+                    if (tq & (1u << j)) {
+                        const float t = kneg ? -best[q][j] : best[q][j];
+                        const float val = __fmul_rn(k, expf(-t));
+                        v[j] = (v[j] < val) ? val : v[j];  // std::max(pixel, val)
+                    }
+                }
+                if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
+                else out_plane[idx] = v[0];
+            }
+        }
+    }
+}
+
+}  // namespace dh
+
+extern "C" int dh_draw_gaussians(void* stream, const float* heatmap_in, float* heatmap_out, const int32_t* centers,
+                                 const float* radii, const int32_t* slice_ids, const uint8_t* active,
+                                 const void* nums_targets, int nums_dtype, const float* k_for_classes, int64_t num_k,
+                                 int64_t B, int64_t T, int64_t C, int64_t H, int64_t W, float radius_to_sigma_factor,
+                                 dh_status* status) {
+    if (B < 0 || T < 0 || C < 0 || num_k < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
+    if (H < 1 || W < 1) return DH_ERR_INVALID_ARGUMENT;
+    if (W > (1ll << 23) || H > (1ll << 23) || H * W >= (1ll << 31) || T > INT32_MAX || C > INT32_MAX)
+        return DH_ERR_UNSUPPORTED_SHAPE;
+    if (B == 0 || C == 0) return DH_OK;
+    if (!heatmap_out || !nums_targets || (num_k > 0 && !k_for_classes)) return DH_ERR_INVALID_ARGUMENT;
+    if (T > 0 && (!centers || !radii)) return DH_ERR_INVALID_ARGUMENT;
+    if (reinterpret_cast<uintptr_t>(centers) & 7u) return DH_ERR_INVALID_ARGUMENT;
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return DH_ERR_NO_DEVICE;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return DH_ERR_NO_DEVICE;
+    const bool inplace = heatmap_in == heatmap_out;
+    if (inplace && T == 0) return DH_OK;
+    dh::GsParams p{};
+    p.in = heatmap_in;
+    p.out = heatmap_out;
+    p.centers = centers;
+    p.radii = radii;
+    p.slice_ids = slice_ids;
+    p.active = active;
+    p.sizes = nums_targets;
+    p.sizes_i64 = nums_dtype == DH_SIZES_I64;
+    p.k_for_classes = k_for_classes;
+    p.num_k = (int)(num_k > INT32_MAX ? INT32_MAX : num_k);
+    p.num_planes = B * C;
+    p.C = (int)C;
+    p.T = (int)T;
+    p.H = (int)H;
+    p.W = (int)W;
+    p.factor = radius_to_sigma_factor;
+    p.status = status;
+    const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heatmap_out) & 15u) == 0) &&
+                     (heatmap_in == nullptr || (reinterpret_cast<uintptr_t>(heatmap_in) & 15u) == 0);
+    const long long band_px = (long long)dh::kGsThreads * dh::kGsItems * (vec ? 4 : 1);
+    long long rows = band_px / W;
+    if (rows < 1) rows = 1;
+    if (rows > H) rows = H;
+    // small problems: more, shorter bands so that every SM gets work
+    while (rows > 1 && p.num_planes * ((H + rows - 1) / rows) < 2ll * sms) rows = (rows + 1) / 2;
+    p.band_rows = (int)rows;
+    p.bands_per_plane = (int)((H + rows - 1) / rows);
+    p.total_units = p.num_planes * p.bands_per_plane;
+    const long long g = p.total_units < 0x7fffffffll ? p.total_units : 0x7fffffffll;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (vec) {
+        if (inplace) dh::gaussians_kernel<4, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else dh::gaussians_kernel<4, false><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+    } else {
+        if (inplace) dh::gaussians_kernel<1, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else dh::gaussians_kernel<1, false><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+    }
+    dh::count_launches(1);
+    return (int)cudaGetLastError();
+}

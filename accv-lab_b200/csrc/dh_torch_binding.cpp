@@ -407,6 +407,71 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> pack_radius_center(const std::vec
     return {centers_out, radii_out, tab.dev.slice(0, 2 * tab.B, 3 * tab.B)};
 }
 
+// ---- N2: DALI draw_gaussians semantics (DrawGaussians.cc:88-157), RaggedBatch layout ---------------------------
+at::Tensor draw_gaussians(const c10::optional<at::Tensor>& heatmap_in, at::Tensor& heatmap_out,
+                          const c10::optional<at::Tensor>& active, const c10::optional<at::Tensor>& slice_ids,
+                          const at::Tensor& centers, const at::Tensor& radii, const at::Tensor& nums_targets,
+                          const at::Tensor& k_for_classes, double radius_to_sigma_factor) {
+    CHECK_INPUT(heatmap_out);
+    CHECK_INPUT(centers);
+    CHECK_INPUT(radii);
+    CHECK_INPUT(nums_targets);
+    CHECK_INPUT(k_for_classes);
+    CHECK_DTYPE(heatmap_out, at::kFloat);
+    CHECK_DTYPE(centers, at::kInt);
+    CHECK_DTYPE(radii, at::kFloat);
+    CHECK_DTYPE(k_for_classes, at::kFloat);
+    TORCH_CHECK(heatmap_out.dim() == 3 || heatmap_out.dim() == 4, "Heatmap has to have 2 or 3 dimensions per sample");
+    const int64_t B = heatmap_out.size(0), C = heatmap_out.dim() == 4 ? heatmap_out.size(1) : 1;
+    const int64_t H = heatmap_out.size(-2), W = heatmap_out.size(-1);
+    TORCH_CHECK(radii.dim() == 2 && radii.size(0) == B, "radii must be of shape [batch_size, max_num_targets]");
+    const int64_t T = radii.size(1);
+    TORCH_CHECK(centers.dim() == 3 && centers.size(0) == B && centers.size(1) == T && centers.size(2) == 2,
+                "centers must be of shape [batch_size, max_num_targets, 2]");
+    TORCH_CHECK(nums_targets.dim() == 1 && nums_targets.size(0) == B, "nums_targets must be of shape [batch_size]");
+    TORCH_CHECK(k_for_classes.dim() == 1, "k_for_classes must be 1-D");
+    CHECK_SAME_DEVICE(centers, heatmap_out);
+    CHECK_SAME_DEVICE(radii, heatmap_out);
+    CHECK_SAME_DEVICE(nums_targets, heatmap_out);
+    CHECK_SAME_DEVICE(k_for_classes, heatmap_out);
+    const float* in_ptr = nullptr;
+    if (heatmap_in.has_value()) {
+        const at::Tensor& hin = *heatmap_in;
+        CHECK_INPUT(hin);
+        CHECK_DTYPE(hin, at::kFloat);
+        CHECK_SAME_DEVICE(hin, heatmap_out);
+        TORCH_CHECK(hin.sizes() == heatmap_out.sizes(), "heatmap_in and heatmap_out must have the same shape");
+        in_ptr = hin.data_ptr<float>();
+    }
+    const uint8_t* act_ptr = nullptr;
+    if (active.has_value()) {
+        const at::Tensor& a = *active;
+        CHECK_INPUT(a);
+        TORCH_CHECK(a.scalar_type() == at::kBool || a.scalar_type() == at::kByte, "active has to be of type BOOL");
+        TORCH_CHECK(a.dim() == 2 && a.size(0) == B && a.size(1) == T, "active must be of shape [batch_size, max_num_targets]");
+        CHECK_SAME_DEVICE(a, heatmap_out);
+        act_ptr = static_cast<const uint8_t*>(a.data_ptr());
+    }
+    const int32_t* sl_ptr = nullptr;
+    if (slice_ids.has_value()) {
+        const at::Tensor& sl = *slice_ids;
+        CHECK_INPUT(sl);
+        CHECK_DTYPE(sl, at::kInt);
+        TORCH_CHECK(sl.dim() == 2 && sl.size(0) == B && sl.size(1) == T, "class_ids must be of shape [batch_size, max_num_targets]");
+        CHECK_SAME_DEVICE(sl, heatmap_out);
+        sl_ptr = sl.data_ptr<int>();
+    }
+    int tag = 0;
+    const void* sizes = sizes_ptr(nums_targets, tag);
+    c10::cuda::CUDAGuard guard(heatmap_out.device());
+    check_status(dh_draw_gaussians(at::cuda::getCurrentCUDAStream().stream(), in_ptr, heatmap_out.data_ptr<float>(),
+                                   centers.data_ptr<int>(), radii.data_ptr<float>(), sl_ptr, act_ptr, sizes, tag,
+                                   k_for_classes.data_ptr<float>(), k_for_classes.numel(), B, T, C, H, W,
+                                   (float)radius_to_sigma_factor, nullptr),
+                 "draw_gaussians");
+    return heatmap_out;
+}
+
 void fill_probe(at::Tensor& t) {
     CHECK_INPUT(t);
     c10::cuda::CUDAGuard guard(t.device());
@@ -458,6 +523,11 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           pybind11::arg("nums_targets"), pybind11::arg("labels"), pybind11::arg("num_classes"), pybind11::arg("height"),
           pybind11::arg("width"), pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f,
           pybind11::arg("scratch"), pybind11::arg("chunk_samples") = 0);
+    m.def("draw_gaussians", &draw_gaussians,
+          "DALI draw_gaussians semantics (float radii, per-class k, active flags) on RaggedBatch-layout inputs; one launch.",
+          pybind11::arg("heatmap_in"), pybind11::arg("heatmap_out"), pybind11::arg("active"), pybind11::arg("slice_ids"),
+          pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"), pybind11::arg("k_for_classes"),
+          pybind11::arg("radius_to_sigma_factor"));
     m.def("combine_data", &combine_data,
           "List of per-sample CUDA tensors [n_i, *data] -> (zero-padded tensor [B, T, *data], int64 sample sizes [B]); one launch.",
           pybind11::arg("data_list"), pybind11::arg("max_sample_size") = -1);

@@ -198,6 +198,27 @@ int dh_pack_radius_center(void* stream, const float* const* centers_ptrs, const 
                           const int64_t* sizes, float out_size_factor, int64_t batch_size, int64_t max_sample_size,
                           int32_t* centers_out, int32_t* radii_out);
 
+/* ---- N2: DALI `draw_gaussians` operator semantics (second renderer mode) --------------------------------
+ * GPU counterpart of the reference's CPU-only DALI operator
+ * (/root/reference/packages/dali_pipeline_framework/ext_impl/DrawGaussians.cc:31-75 draw_gaussian, :88-157 RunImpl):
+ *   out = in; for every slot t < nums_targets[b] with active[b,t]: plane = slice_ids[b,t], k = k_for_classes[plane],
+ *   window cols [floor((float)cx - r), ceil((float)cx + r)] x rows likewise (skipped when wholly outside, clipped),
+ *   sigma = r * radius_to_sigma_factor, val = k * expf(-(float)(dy^2 + dx^2) / (2 sigma^2)), pixel = max(pixel, val).
+ * Layout: RaggedBatch instead of DALI's per-sample tensor lists — centers int32 [B,T,2] (x,y; 8-byte aligned),
+ * radii float32 [B,T], slice_ids int32 [B,T] (NULL -> 0), active uint8/bool [B,T] (NULL -> all active),
+ * nums_targets [B] (tag nums_dtype), k_for_classes float32 [num_k] DEVICE array, heatmaps float32 [B,C,H,W]
+ * ([B,H,W]: pass C = 1). heatmap_in == NULL: FRESH (out = max(0, ...), every pixel written once, nothing read);
+ * heatmap_in == heatmap_out: in place (touched pixels only); otherwise out-of-place like the operator.
+ * Deliberate differences: a slice_id outside [0, min(C, num_k)) skips the object and counts it in
+ * dh_status.skipped_label (the reference fails the batch, or writes out of bounds when slice_id >= C); radii that are
+ * NaN or |r| > 2048 are skipped and counted in skipped_radius (the reference's int32 squares overflow / its
+ * float -> int casts are undefined there). One launch. */
+int dh_draw_gaussians(void* stream, const float* heatmap_in, float* heatmap_out, const int32_t* centers,
+                      const float* radii, const int32_t* slice_ids, const uint8_t* active, const void* nums_targets,
+                      int nums_dtype, const float* k_for_classes, int64_t num_k, int64_t batch_size,
+                      int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
+                      float radius_to_sigma_factor, dh_status* status);
+
 /* ---- measurement helper ---------------------------------------------------------------
  * Pure 128-bit-store fill of `bytes` bytes (multiple of 16, 16-byte aligned) with zeros using the same
  * store path and grid shape as the FRESH renderer: the write-only ceiling the renderer is compared to. */

@@ -48,3 +48,107 @@ def test_oracle_known_answers(oracle):
     oracle.draw_gaussians(heat2, centers, radii, np.array([1]), [0.8, 1.0], 1.0 / 3.0, np.array([[0, 1]], np.int32),
                           np.array([[False, True]]))
     assert not heat2.any()
+
+
+# ---------------------------------------------------------------------------------------------- GPU
+def _ulp(a, b):
+    ai, bi = a.view(np.int32).astype(np.int64), b.view(np.int32).astype(np.int64)
+    return int(np.abs(ai - bi).max()) if a.size else 0
+
+
+def _check(got, want, name):
+    assert np.array_equal(got > 0, want > 0), f"{name}: touched mask differs"
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    err = float(np.nanmax(np.abs(got - want))) if got.size else 0.0
+    assert err <= 1e-6, f"{name}: max abs err {err}"
+    # a denormal can land one step across a power of two: compare ulps on normal values only
+    big = np.abs(want) > 1e-30
+    assert _ulp(got[big], want[big]) <= 2, f"{name}: more than 2 ulp"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CASES)
+def test_gpu_matches_reference_operator_goldens(cabi, cuda_dev, name):
+    import torch
+    from accvlab.draw_heatmap import b200
+
+    c = _case(np.load(GOLD), name)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda_dev)
+    rb = lambda a: b200.RaggedBatch(dev(a), sample_sizes=dev(c["sizes"]))
+    hin = dev(c["heat_in"])
+    l0 = b200.launch_count()
+    out = b200.draw_gaussians(hin, rb(c["active"]), rb(c["slice_ids"]), rb(c["centers"]), rb(c["radii"]), dev(c["k"]),
+                              float(c["factor"]))
+    assert b200.launch_count() - l0 == 1
+    assert out.data_ptr() != hin.data_ptr() and np.array_equal(hin.cpu().numpy(), c["heat_in"])  # out of place, input intact
+    _check(out.cpu().numpy(), c["heat_out"], name)
+    # in place gives the same bits
+    h2 = hin.clone()
+    b200.draw_gaussians(h2, rb(c["active"]), rb(c["slice_ids"]), rb(c["centers"]), rb(c["radii"]), dev(c["k"]),
+                        float(c["factor"]), out=h2)
+    assert torch.equal(h2, out)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W,T,C", [(33, 47, 40, 3), (8, 4100, 30, 1), (232, 400, 100, 10), (64, 64, 700, 2)])
+def test_gpu_vs_oracle_shapes(cabi, cuda_dev, oracle, H, W, T, C):
+    """Scalar path (W % 4 != 0), rows wider than one pass, a BASELINE-sized map, and T beyond one list chunk (700 > 512);
+    fresh (no input) and accumulate into a non-zero input."""
+    import torch
+
+    rng = np.random.default_rng(H * 1000 + W)
+    B = 5
+    sizes = rng.integers(0, T + 1, B).astype(np.int64)
+    sizes[1] = T
+    centers = np.stack([rng.integers(-8, W + 8, (B, T)), rng.integers(-8, H + 8, (B, T))], 2).astype(np.int32)
+    radii = (0.3 + rng.random((B, T)) * 12.0).astype(np.float32)
+    radii[rng.random((B, T)) < 0.2] = np.float32(3.0)
+    slice_ids = rng.integers(0, C, (B, T)).astype(np.int32)
+    active = rng.random((B, T)) < 0.8
+    k = (0.5 + rng.random(C) * 0.5).astype(np.float32)
+    factor = 0.3
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda_dev)
+    d = dict(c=dev(centers), r=dev(radii), s=dev(slice_ids), a=dev(active), n=dev(sizes), k=dev(k))
+
+    def run(hin, out):
+        rc = cabi.dh_draw_gaussians(_cabi.stream_ptr(), _cabi.ptr(hin), _cabi.ptr(out), _cabi.ptr(d["c"]), _cabi.ptr(d["r"]),
+                                    _cabi.ptr(d["s"]), _cabi.ptr(d["a"]), _cabi.ptr(d["n"]), _cabi.DH_SIZES_I64,
+                                    _cabi.ptr(d["k"]), C, B, T, C, H, W, factor, None)
+        _cabi.check(cabi, rc, "dh_draw_gaussians")
+        torch.cuda.synchronize()
+
+    want = np.zeros((B, C, H, W), np.float32)
+    oracle.draw_gaussians(want, centers, radii, sizes, k, factor, slice_ids, active)
+    out = torch.full((B, C, H, W), 9.0, device=cuda_dev)
+    run(None, out)  # fresh
+    _check(out.cpu().numpy(), want, "fresh")
+    bg = (rng.random((B, C, H, W), dtype=np.float32) * 0.6 * (rng.random((B, C, H, W)) < 0.3)).astype(np.float32)
+    want2 = bg.copy()
+    oracle.draw_gaussians(want2, centers, radii, sizes, k, factor, slice_ids, active)
+    out2 = torch.empty((B, C, H, W), device=cuda_dev)
+    run(dev(bg), out2)
+    _check(out2.cpu().numpy(), want2, "accumulate")
+
+
+@pytest.mark.gpu
+def test_gpu_out_of_range_classes_and_radii_are_skipped_and_counted(cabi, cuda_dev, oracle):
+    import torch
+
+    B, T, C, H, W = 1, 4, 2, 16, 16
+    centers = np.array([[[4, 4], [8, 8], [12, 12], [5, 9]]], np.int32)
+    radii = np.array([[2.0, np.nan, 3.0, 1e9]], np.float32)
+    slice_ids = np.array([[0, 1, 7, 1]], np.int32)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda_dev)
+    status = torch.zeros(4, dtype=torch.int32, device=cuda_dev)
+    out = torch.empty((B, C, H, W), device=cuda_dev)
+    keep = [dev(centers), dev(radii), dev(slice_ids), dev(np.array([T], np.int64)), dev(np.array([1.0, 1.0], np.float32))]
+    rc = cabi.dh_draw_gaussians(_cabi.stream_ptr(), None, _cabi.ptr(out), _cabi.ptr(keep[0]), _cabi.ptr(keep[1]),
+                                _cabi.ptr(keep[2]), None, _cabi.ptr(keep[3]), _cabi.DH_SIZES_I64, _cabi.ptr(keep[4]), 2,
+                                B, T, C, H, W, 0.3, _cabi.ptr(status))
+    _cabi.check(cabi, rc, "dh_draw_gaussians")
+    torch.cuda.synchronize()
+    want = np.zeros((B, C, H, W), np.float32)
+    oracle.draw_gaussians(want, centers, radii, np.array([T]), [1.0, 1.0], 0.3, slice_ids, None)
+    _check(out.cpu().numpy(), want, "skips")
+    st = status.cpu().numpy()
+    assert st[0] == 1 and st[2] == 2  # one bad class; NaN and 1e9 radii
