@@ -47,13 +47,13 @@ struct GsParams {
     const float* k_for_classes;
     int num_k;
     long long num_planes, total_units;
-    int C, T, H, W, band_rows, bands_per_plane;
+    int C, T, H, W, band_rows, bands_per_plane, bands_per_unit, units_per_plane;
     float factor;
     dh_status* status;
 };
 
-// Slot -> list entry for plane class `cls`, culled against rows [by0, by1]. Window arithmetic of DrawGaussians.cc:34-51.
-__device__ __forceinline__ bool gs_make(const GsParams& p, long long i, int cls, int by0, int by1, bool count, GObj& o) {
+// Slot -> list entry for plane class `cls`, culled against the unit's rows [uy0, uy1]. Window arithmetic of DrawGaussians.cc:34-51.
+__device__ __forceinline__ bool gs_make(const GsParams& p, long long i, int cls, int uy0, int uy1, bool count, GObj& o) {
     if (p.active != nullptr && p.active[i] == 0) return false;
     const float r = p.radii[i];
     if (!(fabsf(r) <= kGsMaxRadius)) {  // NaN or huge; counted once per object (by the sample's first unit)
@@ -77,7 +77,7 @@ __device__ __forceinline__ bool gs_make(const GsParams& p, long long i, int cls,
     o.y0 = min(max(0, min_y), p.H - 1);
     o.y1 = min(max(0, max_y), p.H - 1);
     if (o.x0 > o.x1 || o.y0 > o.y1) return false;  // negative radius: empty loops in the reference
-    if (o.y1 < by0 || o.y0 > by1) return false;
+    if (o.y1 < uy0 || o.y0 > uy1) return false;
     const float sigma = __fmul_rn(r, p.factor);
     o.inv = __fdiv_rn(1.0f, __fmul_rn(__fmul_rn(2.0f, sigma), sigma));
     o.cx = fx;
@@ -87,7 +87,7 @@ __device__ __forceinline__ bool gs_make(const GsParams& p, long long i, int cls,
 }
 
 template <int PX, bool INPLACE>
-__global__ void __launch_bounds__(kGsThreads) gaussians_kernel(const GsParams p) {
+__global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(const GsParams p) {
     __shared__ GObj s_list[kGsListCap];
     __shared__ int s_cnt;
     const int tid = threadIdx.x, lane = tid & 31;
@@ -95,10 +95,12 @@ __global__ void __launch_bounds__(kGsThreads) gaussians_kernel(const GsParams p)
     const long long plane_elems = (long long)p.H * p.W;
     const float INF = __int_as_float(0x7f800000);
 
+    __shared__ unsigned s_mask;  // bands of the unit some object overlaps
     for (long long u = blockIdx.x; u < p.total_units; u += gridDim.x) {
-        const long long plane = u / p.bands_per_plane;
-        const int band = (int)(u - plane * p.bands_per_plane);
-        const int by0 = band * p.band_rows, by1 = min(by0 + p.band_rows, p.H) - 1;  // inclusive
+        const long long plane = u / p.units_per_plane;
+        const int ug = (int)(u - plane * p.units_per_plane);
+        const int ub0 = ug * p.bands_per_unit, ub1 = min(ub0 + p.bands_per_unit, p.bands_per_plane);
+        const int uy0 = ub0 * p.band_rows, uy1 = min(ub1 * p.band_rows, p.H) - 1;  // inclusive
         const long long sample = plane / p.C;
         const int cls = (int)(plane - sample * p.C);
         long long ns = p.sizes_i64 ? reinterpret_cast<const long long*>(p.sizes)[sample]
@@ -108,26 +110,37 @@ __global__ void __launch_bounds__(kGsThreads) gaussians_kernel(const GsParams p)
         const bool class_ok = cls < p.num_k;
         const float k = class_ok ? p.k_for_classes[cls] : 0.0f;
         const bool kneg = k < 0.0f;
-        const bool count = (band == 0 && cls == 0);
+        const bool count = (ug == 0 && cls == 0);
         const long long src = sample * p.T;
         const float* const in_plane = p.in ? p.in + plane * plane_elems : nullptr;
         float* const out_plane = p.out + plane * plane_elems;
-        const int nitems = (by1 - by0 + 1) * wunits;
         const bool single = n <= kGsListCap;
 
         auto build = [&](int c0, bool do_count) {  // list of slots [c0, c0 + cap) (block-wide; ends with a barrier)
             __syncthreads();
-            if (tid == 0) s_cnt = 0;
+            if (tid == 0) {
+                s_cnt = 0;
+                s_mask = 0u;
+            }
             __syncthreads();
             const int c1 = min(n, c0 + kGsListCap);
             for (int base = c0; base < c1; base += kGsThreads) {
                 const int t = base + tid;
                 GObj o;
-                const bool pred = (t < c1) && class_ok && gs_make(p, src + t, cls, by0, by1, do_count, o);
+                const bool pred = (t < c1) && class_ok && gs_make(p, src + t, cls, uy0, uy1, do_count, o);
                 const unsigned bal = __ballot_sync(0xffffffffu, pred);
                 if (bal) {
+                    unsigned bits = 0u;
+                    if (pred) {
+                        const int lo = (max(o.y0, uy0) - uy0) / p.band_rows, hi = (min(o.y1, uy1) - uy0) / p.band_rows;
+                        bits = ((2u << (hi - lo)) - 1u) << lo;
+                    }
+                    bits = __reduce_or_sync(0xffffffffu, bits);
                     int pos = 0;
-                    if (lane == 0) pos = atomicAdd(&s_cnt, __popc(bal));
+                    if (lane == 0) {
+                        pos = atomicAdd(&s_cnt, __popc(bal));
+                        atomicOr(&s_mask, bits);
+                    }
                     pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(bal & ((1u << lane) - 1u));
                     if (pred) s_list[pos] = o;
                 }
@@ -137,17 +150,21 @@ __global__ void __launch_bounds__(kGsThreads) gaussians_kernel(const GsParams p)
         };
 
         int cnt = single ? build(0, count) : 0;
-        if (single && cnt == 0) {  // nothing lands in this band
+        const unsigned mask = single ? s_mask : 0xffffffffu;
+      for (int b = ub0; b < ub1; ++b) {
+        const int by0 = b * p.band_rows, by1 = min(by0 + p.band_rows, p.H) - 1;  // inclusive
+        const int nitems = (by1 - by0 + 1) * wunits;
+        if (!((mask >> (b - ub0)) & 1u)) {  // nothing lands in this band
             if constexpr (!INPLACE) {
-                for (int it = tid; it < nitems; it += kGsThreads) {
-                    const int row = by0 + it / wunits, col = (it % wunits) * PX;
-                    const long long idx = (long long)row * p.W + col;
-                    if constexpr (PX == 4) {
-                        const float4 v = in_plane ? *reinterpret_cast<const float4*>(in_plane + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-                        *reinterpret_cast<float4*>(out_plane + idx) = v;
-                    } else {
-                        out_plane[idx] = in_plane ? in_plane[idx] : 0.0f;
-                    }
+                // whole rows: the band is one contiguous range of the plane
+                const long long base = (long long)by0 * wunits;
+                if constexpr (PX == 4) {
+                    const float4* const i4 = in_plane ? reinterpret_cast<const float4*>(in_plane) + base : nullptr;
+                    float4* const o4 = reinterpret_cast<float4*>(out_plane) + base;
+#pragma unroll 4
+                    for (int it = tid; it < nitems; it += kGsThreads) o4[it] = i4 ? i4[it] : make_float4(0.f, 0.f, 0.f, 0.f);
+                } else {
+                    for (int it = tid; it < nitems; it += kGsThreads) out_plane[base + it] = in_plane ? in_plane[base + it] : 0.0f;
                 }
             }
             continue;
@@ -167,7 +184,7 @@ __global__ void __launch_bounds__(kGsThreads) gaussians_kernel(const GsParams p)
                 for (int j = 0; j < PX; ++j) best[q][j] = INF;
             }
             for (int c0 = 0; c0 < (single ? 1 : n); c0 += kGsListCap) {
-                if (!single) cnt = build(c0, count && item0 == 0);
+                if (!single) cnt = build(c0, count && item0 == 0 && b == ub0);
                 for (int e = 0; e < cnt; ++e) {
                     const GObj o = s_list[e];  // broadcast
 #pragma unroll
@@ -216,6 +233,7 @@ __global__ void __launch_bounds__(kGsThreads) gaussians_kernel(const GsParams p)
                 else out_plane[idx] = v[0];
             }
         }
+      }  // bands of the unit
     }
 }
 
@@ -268,7 +286,17 @@ extern "C" int dh_draw_gaussians(void* stream, const float* heatmap_in, float* h
     while (rows > 1 && p.num_planes * ((H + rows - 1) / rows) < 2ll * sms) rows = (rows + 1) / 2;
     p.band_rows = (int)rows;
     p.bands_per_plane = (int)((H + rows - 1) / rows);
-    p.total_units = p.num_planes * p.bands_per_plane;
+    // unit = consecutive bands of one plane sharing one scan of the sample's slots (~128 KB of output, <= 32 bands);
+    // fewer bands per unit on small problems so that every SM still sees several units
+    long long bpu = (131072 / 4) / (rows * W);
+    if (bpu < 1) bpu = 1;
+    if (bpu > 32) bpu = 32;
+    if (bpu > p.bands_per_plane) bpu = p.bands_per_plane;
+    while (bpu > 1 && p.num_planes * ((p.bands_per_plane + bpu - 1) / bpu) < 8ll * sms) bpu = (bpu + 1) / 2;
+    p.units_per_plane = (int)((p.bands_per_plane + bpu - 1) / bpu);
+    p.bands_per_unit = (int)((p.bands_per_plane + p.units_per_plane - 1) / p.units_per_plane);
+    p.units_per_plane = (p.bands_per_plane + p.bands_per_unit - 1) / p.bands_per_unit;
+    p.total_units = p.num_planes * p.units_per_plane;
     const long long g = p.total_units < 0x7fffffffll ? p.total_units : 0x7fffffffll;
     cudaStream_t s = (cudaStream_t)stream;
     if (vec) {
