@@ -19,6 +19,7 @@
 #include <stdint.h>
 
 #include "dh_b200.h"
+#include "dh_ptx.cuh"
 
 namespace dh {
 
@@ -86,16 +87,32 @@ __device__ __forceinline__ bool gs_make(const GsParams& p, long long i, int cls,
     return true;
 }
 
-template <int PX, bool INPLACE>
+constexpr int kGsZeroBytes = 8192;  // constant zero tile of the FRESH mode
+
+// FRESH (no input heatmap, PX == 4): runs of untouched bands leave as bulk stores (SASS UBLKCP) from a zero tile, issued
+// by the lanes of warp 0 in parallel — no LSU or register traffic for the bytes nobody draws on.
+template <int PX, bool INPLACE, bool FRESH>
 __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(const GsParams p) {
     __shared__ GObj s_list[kGsListCap];
     __shared__ int s_cnt;
+    __shared__ __align__(128) float4 s_zero[FRESH ? kGsZeroBytes / 16 : 1];
+    if constexpr (FRESH) {
+        for (int i = threadIdx.x; i < kGsZeroBytes / 16; i += kGsThreads) s_zero[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        fence_proxy_async();  // visible to the bulk-copy engine (the barriers of the first list build order it)
+    }
     const int tid = threadIdx.x, lane = tid & 31;
     const int wunits = p.W / PX;
     const long long plane_elems = (long long)p.H * p.W;
     const float INF = __int_as_float(0x7f800000);
 
     __shared__ unsigned s_mask;  // bands of the unit some object overlaps
+    int drow0[kGsItems], dcol0[kGsItems];  // (row offset, column) of this thread's items in a band
+#pragma unroll
+    for (int q = 0; q < kGsItems; ++q) {
+        const int it = q * kGsThreads + tid;
+        drow0[q] = it / wunits;
+        dcol0[q] = (it - drow0[q] * wunits) * PX;
+    }
     for (long long u = blockIdx.x; u < p.total_units; u += gridDim.x) {
         const long long plane = u / p.units_per_plane;
         const int ug = (int)(u - plane * p.units_per_plane);
@@ -151,11 +168,31 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
 
         int cnt = single ? build(0, count) : 0;
         const unsigned mask = single ? s_mask : 0xffffffffu;
+        if constexpr (FRESH) {
+            if (tid < 32) {  // lane l starts the run of untouched bands that begins at band ub0 + l
+                const int nb = ub1 - ub0;
+                const unsigned z = ~mask & (nb >= 32 ? 0xffffffffu : ((1u << nb) - 1u));
+                if (((z >> tid) & 1u) && (tid == 0 || !((z >> (tid - 1)) & 1u))) {
+                    const unsigned inv = ~(z >> tid);
+                    const int run = inv ? __ffs(inv) - 1 : 32 - tid;
+                    const int r0 = (ub0 + tid) * p.band_rows, r1 = min(r0 + run * p.band_rows, p.H);
+                    char* dst = reinterpret_cast<char*>(out_plane + (long long)r0 * p.W);
+                    long long bytes = (long long)(r1 - r0) * p.W * 4;
+                    while (bytes > 0) {
+                        const unsigned c = (unsigned)(bytes < kGsZeroBytes ? bytes : kGsZeroBytes);
+                        bulk_store(dst, s_zero, c);
+                        dst += c;
+                        bytes -= c;
+                    }
+                    bulk_commit();
+                }
+            }
+        }
       for (int b = ub0; b < ub1; ++b) {
         const int by0 = b * p.band_rows, by1 = min(by0 + p.band_rows, p.H) - 1;  // inclusive
         const int nitems = (by1 - by0 + 1) * wunits;
         if (!((mask >> (b - ub0)) & 1u)) {  // nothing lands in this band
-            if constexpr (!INPLACE) {
+            if constexpr (!INPLACE && !FRESH) {
                 // whole rows: the band is one contiguous range of the plane
                 const long long base = (long long)by0 * wunits;
                 if constexpr (PX == 4) {
@@ -178,8 +215,11 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
             for (int q = 0; q < kGsItems; ++q) {
                 const int it = item0 + q * kGsThreads + tid;
                 const bool valid = it < nitems;
-                rows[q] = valid ? by0 + it / wunits : -1 - (1 << 30);  // invalid items fail every row test
-                cols[q] = valid ? (it % wunits) * PX : 0;
+                // item -> (row, col): the divisions are hoisted out of the band loop for the first (usually only) pass
+                const int dr = item0 == 0 ? drow0[q] : it / wunits;
+                const int dc = item0 == 0 ? dcol0[q] : (it % wunits) * PX;
+                rows[q] = valid ? by0 + dr : -1 - (1 << 30);  // invalid items fail every row test
+                cols[q] = valid ? dc : 0;
 #pragma unroll
                 for (int j = 0; j < PX; ++j) best[q][j] = INF;
             }
@@ -187,6 +227,7 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
                 if (!single) cnt = build(c0, count && item0 == 0 && b == ub0);
                 for (int e = 0; e < cnt; ++e) {
                     const GObj o = s_list[e];  // broadcast
+                    if (o.y1 < by0 || o.y0 > by1) continue;  // block-uniform: the object misses this band of the unit
 #pragma unroll
                     for (int q = 0; q < kGsItems; ++q) {
                         if (rows[q] < o.y0 || rows[q] > o.y1) continue;
@@ -213,7 +254,7 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
                 if (rows[q] < 0) continue;
                 const unsigned tq = (touched >> (q * PX)) & ((1u << PX) - 1u);
                 if (INPLACE && tq == 0u) continue;
-                const long long idx = (long long)rows[q] * p.W + cols[q];
+                const int idx = rows[q] * p.W + cols[q];  // H*W < 2^31
                 float v[PX];
                 if constexpr (PX == 4) {
                     const float4 a = in_plane ? *reinterpret_cast<const float4*>(in_plane + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -221,12 +262,12 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
                 } else {
                     v[0] = in_plane ? in_plane[idx] : 0.0f;
                 }
+                if (tq != 0u) {  // one expf per pixel of a touched item, unconditionally: no per-pixel divergence
 #pragma unroll
-                for (int j = 0; j < PX; ++j) {
-                    if (tq & (1u << j)) {
+                    for (int j = 0; j < PX; ++j) {
                         const float t = kneg ? -best[q][j] : best[q][j];
                         const float val = __fmul_rn(k, expf(-t));
-                        v[j] = (v[j] < val) ? val : v[j];  // std::max(pixel, val)
+                        v[j] = ((tq & (1u << j)) && v[j] < val) ? val : v[j];  // std::max(pixel, val)
                     }
                 }
                 if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
@@ -235,6 +276,7 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
         }
       }  // bands of the unit
     }
+    if constexpr (FRESH) bulk_wait_read<0>();  // the zero tile must outlive every bulk read this thread issued
 }
 
 }  // namespace dh
@@ -300,11 +342,12 @@ extern "C" int dh_draw_gaussians(void* stream, const float* heatmap_in, float* h
     const long long g = p.total_units < 0x7fffffffll ? p.total_units : 0x7fffffffll;
     cudaStream_t s = (cudaStream_t)stream;
     if (vec) {
-        if (inplace) dh::gaussians_kernel<4, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);
-        else dh::gaussians_kernel<4, false><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        if (inplace) dh::gaussians_kernel<4, true, false><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else if (heatmap_in == nullptr) dh::gaussians_kernel<4, false, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else dh::gaussians_kernel<4, false, false><<<(int)g, dh::kGsThreads, 0, s>>>(p);
     } else {
-        if (inplace) dh::gaussians_kernel<1, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);
-        else dh::gaussians_kernel<1, false><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        if (inplace) dh::gaussians_kernel<1, true, false><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else dh::gaussians_kernel<1, false, false><<<(int)g, dh::kGsThreads, 0, s>>>(p);
     }
     dh::count_launches(1);
     return (int)cudaGetLastError();

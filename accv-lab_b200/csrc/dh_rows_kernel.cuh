@@ -19,6 +19,7 @@
 //   * ACCUMULATE mode (reference semantics): only the touched spans are read-max-written with plain coalesced
 //         loads/stores; untouched pixels are neither read nor written.
 #pragma once
+#include "dh_ptx.cuh"
 
 namespace dh {
 
@@ -35,19 +36,6 @@ struct __align__(16) ObjI {
     int x, y, r;
     float w;  // 1/var (> 0)
 };
-
-// ---- PTX wrappers (sm_90+/sm_100a bulk async copy, shared::cta -> global) ------------------------------------
-__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, unsigned bytes) {
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() {
-    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // Raw slot -> (x, y, r) for the four sources; false if the slot does not belong to this plane.
 template <int SRC>

@@ -62,6 +62,66 @@ def test_cfg3_full_size_properties(cabi, cuda_dev):
     assert bool((fresh.reshape(-1, cfg.H, cfg.W)[pl, y[inside], x[inside]] == np.float32(0.8)).all())
 
 
+def _window_cover_count(co, ro, s, lab, C, H, W, dev, chunk=256):
+    """Number of pixels covered by the union of the clipped (2r+1)^2 windows, computed independently of the renderer
+    with torch ops (2-D difference image per plane, integrated), in sample chunks to bound memory."""
+    B, T = ro.shape
+    total = 0
+    for b0 in range(0, B, chunk):
+        b1 = min(B, b0 + chunk)
+        nb = b1 - b0
+        valid = torch.arange(T, device=dev)[None, :] < s[b0:b1, None]
+        x, y, r = co[b0:b1, :, 0].long(), co[b0:b1, :, 1].long(), ro[b0:b1].long()
+        x0, x1 = (x - r).clamp(0, W), (x + r + 1).clamp(0, W)
+        y0, y1 = (y - r).clamp(0, H), (y + r + 1).clamp(0, H)
+        valid &= (x0 < x1) & (y0 < y1)
+        plane = (torch.arange(nb, device=dev)[:, None] * C + lab[b0:b1].long())[valid]
+        diff = torch.zeros((nb * C, H + 1, W + 1), device=dev, dtype=torch.int32)
+        one = torch.ones_like(plane, dtype=torch.int32)
+        diff.index_put_((plane, y0[valid], x0[valid]), one, accumulate=True)
+        diff.index_put_((plane, y1[valid], x1[valid]), one, accumulate=True)
+        diff.index_put_((plane, y0[valid], x1[valid]), -one, accumulate=True)
+        diff.index_put_((plane, y1[valid], x0[valid]), -one, accumulate=True)
+        total += int((diff.cumsum(1, dtype=torch.int32).cumsum(2, dtype=torch.int32)[:, :H, :W] > 0).sum())
+        del diff
+    return total
+
+
+@pytest.mark.parametrize("name", ["cfg4", "cfg5"])
+def test_full_size_properties_cfg4_cfg5(cabi, cuda_dev, name):
+    """BASELINE.json's full sizes (cfg5: 30 720 planes, 11.4 GB) through size-independent properties:
+    fresh fused == zeros + accumulate (bitwise); accumulate is idempotent; the digest fused into the render launch ==
+    a separate checksum pass == the sum of the digests of 8 independently rendered shards (SURVEY.md 8(e));
+    touched-pixel count == an independent union-of-windows count; all values in [0, k]; max == k."""
+    w = workloads.make(name)
+    cfg = w.cfg
+    cf, bf, s, lab = _upload(w, cuda_dev)
+    shape = (w.B, cfg.C, cfg.H, cfg.W)
+    sample_elems = cfg.C * cfg.H * cfg.W
+    fresh = torch.full(shape, 9.0, device=cuda_dev)
+    d_fused = _cabi.draw_from_boxes_digest(cabi, fresh, cf, bf, float(cfg.osf), s, lab, 6.0, 1.0)
+    d_pass = _cabi.checksum(cabi, fresh)
+    assert torch.equal(d_fused, d_pass)
+    co, ro = _cabi.radius_center(cabi, cf, bf, float(cfg.osf))
+    acc = torch.zeros(shape, device=cuda_dev)
+    _cabi.draw_batched(cabi, acc, co, ro, s, lab, 6.0, 1.0)
+    assert torch.equal(fresh, acc)
+    _cabi.draw_batched(cabi, acc, co, ro, s, lab, 6.0, 1.0)  # idempotent
+    assert torch.equal(fresh, acc)
+    del acc
+    d = torch.zeros(3, dtype=torch.int64, device=cuda_dev)
+    for g in range(8):
+        lo, hi = workloads.shard_range(w.B, g, 8)
+        part = torch.empty((hi - lo, cfg.C, cfg.H, cfg.W), device=cuda_dev)
+        _cabi.draw_from_boxes(cabi, part, cf[lo:hi].contiguous(), bf[lo:hi].contiguous(), float(cfg.osf),
+                              s[lo:hi].contiguous(), lab[lo:hi].contiguous())
+        _cabi.checksum(cabi, part, lo * sample_elems, d)
+        del part
+    assert torch.equal(d, d_pass)
+    assert int(d_pass[2]) == _window_cover_count(co, ro, s, lab, cfg.C, cfg.H, cfg.W, cuda_dev)
+    assert float(fresh.min()) >= 0.0 and float(fresh.max()) == 1.0
+
+
 def test_sharded_equals_unsharded_digest(cabi, cuda_dev):
     """G contiguous batch slices rendered independently give the unsharded result (digest additive)."""
     w = workloads.make("cfg5", B=96)
