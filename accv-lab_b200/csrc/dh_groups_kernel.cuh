@@ -368,10 +368,20 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
 template <int SRC>
 __device__ __forceinline__ int unit_header(const RenderParams& p, long long u, int G, UnitSrc& us, int& uy0, int& uy1,
                                            bool& count_skips) {
-    us.plane = u / p.units_per_plane;
-    const int ug = (int)(u - us.plane * p.units_per_plane);
-    uy0 = ug * p.bands_per_unit * G;
-    uy1 = min(uy0 + p.bands_per_unit * G, p.H);
+    int ug, bpu;
+    if (u < p.tier1_units) {
+        us.plane = u / p.units_per_plane;
+        ug = (int)(u - us.plane * p.units_per_plane);
+        bpu = p.bands_per_unit;
+    } else {  // tail tier: smaller units, handed out last
+        const long long u2 = u - p.tier1_units;
+        const long long pl2 = u2 / p.units_per_plane2;
+        us.plane = p.tier1_planes + pl2;
+        ug = (int)(u2 - pl2 * p.units_per_plane2);
+        bpu = p.bands_per_unit2;
+    }
+    uy0 = ug * bpu * G;
+    uy1 = min(uy0 + bpu * G, p.H);
     if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
         const long long sample = us.plane / p.C;
         us.cls = (int)(us.plane - sample * p.C);
@@ -498,6 +508,11 @@ __device__ __forceinline__ void digest_flush(Digest& dg, unsigned long long* out
 // Tried and measured slower on B200 (profiles/r01/experiments.md): claiming groups dynamically with shared-memory
 // atomics (+23 % instructions, -15 % throughput) and a producer/consumer warp pipeline over two list stages (equal at
 // best, 10-25 % slower for units under 128 KB).
+#ifdef DH_TRACE_UNITS  // profiling builds only (profiles/scripts/unit_trace.py): per-unit start / end / SM / list size
+__device__ unsigned long long* g_trace = nullptr;
+__device__ long long g_trace_units = 0;
+#endif
+
 template <bool ACCUM, int SRC, bool DIGEST>
 __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const RenderParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -535,6 +550,16 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         const int ngroups = (uy1 - uy0 + G - 1) / G;
 
         __syncthreads();  // every warp is done with the previous unit's list (and shared memory is initialised)
+#ifdef DH_TRACE_UNITS
+        if (tid == 0 && g_trace && u < g_trace_units) {
+            unsigned long long t;
+            unsigned sm;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+            asm volatile("mov.u32 %0, %smid;" : "=r"(sm));
+            g_trace[u * 4 + 0] = t;
+            g_trace[u * 4 + 2] = sm;
+        }
+#endif
         if (tid == 0) {
             s_cnt = 0;
             s_mask = 0ull;
@@ -589,6 +614,14 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
             render_group<ACCUM, SRC, DIGEST>(p, ws, plane_ptr, plane_index0, y0, min(G, uy1 - y0), W, G, kneg, lane, small, mine,
                                              s_unit, ucnt, us, dg);
         }
+#ifdef DH_TRACE_UNITS
+        if (lane == 0 && g_trace && u < g_trace_units) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+            atomicMax(&g_trace[u * 4 + 1], t);
+            if (warp == 0) g_trace[u * 4 + 3] = (unsigned long long)ucnt | ((unsigned long long)__popcll(mask) << 32);
+        }
+#endif
         // next unit: the one the block scheduler hands over (cluster launch control), else the static stride
         if (p.use_clc) {
             mbar_wait(&s_bar, clc_phase);

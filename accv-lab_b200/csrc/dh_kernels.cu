@@ -66,6 +66,9 @@ struct RenderParams {
     long long digest_base;       // element index of heat[0] in the unsharded result
     int use_clc;                 // groups_kernel: fetch further units through cluster launch control
     long long total_units;
+    // groups_kernel, tail tier: planes >= tier1_planes are cut into smaller units (handed out last)
+    long long tier1_units, tier1_planes;
+    int bands_per_unit2, units_per_plane2;
     float factor, k;
     dh_status* status;
 };
@@ -645,6 +648,8 @@ static int env_int(const char* name, int dflt) {
 static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 131072);
 static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
 static const int g_no_clc = env_int("DH_G_NOCLC", 0);
+static const int g_tail_div = env_int("DH_G_TAIL_DIV", 2);            // tail-tier units are 1/this of a full unit (1 = off)
+static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail tier = this/2 waves of full-size units
 
 // Plan of the groups kernels: row group = G whole rows (<= kGStageCap bytes), unit = up to 64 groups of one plane,
 // ~128 KB when the problem is large (amortises the per-unit list build; measured optimum on cfg5: 3 units per plane), smaller when it
@@ -673,7 +678,28 @@ static void make_groups_plan(RenderParams& p, long long max_ctas) {
     p.units_per_plane = (int)((groups_y + gpu - 1) / gpu);
     p.bands_per_unit = (groups_y + p.units_per_plane - 1) / p.units_per_plane;  // balance the last unit
     p.units_per_plane = (groups_y + p.bands_per_unit - 1) / p.bands_per_unit;
-    p.total_units = p.num_planes * p.units_per_plane;
+    // Tail tier. Units are handed out in address order and a unit with many objects takes 2-3 x the mean, so the
+    // launch used to end with a long tail of half-idle SMs (profiles/scripts/unit_trace.py: 12 of 39 us on cfg3).
+    // The planes that are handed out last (about one wave of full-size units) are cut into half-size units. Measured
+    // gain is small (cfg3 43.7 -> 42.3 us, 8-GPU slice of cfg5 221.0 -> 220.1 us): an EMPTY unit already takes 3-4 us
+    // of pure latency (sizes -> slots -> barriers -> next-unit handshake), so finer units buy little; quarter or
+    // eighth units and longer tiers were slower (profiles/r01/experiments.md).
+    p.tier1_planes = p.num_planes;
+    p.bands_per_unit2 = p.bands_per_unit;
+    p.units_per_plane2 = p.units_per_plane;
+    const int small = g_tail_div > 1 ? p.bands_per_unit / g_tail_div : 0;
+    if (small >= kGWarps && p.num_planes * p.units_per_plane > max_ctas) {
+        long long planes2 = (g_tail_waves_x2 * max_ctas / 2 + p.units_per_plane - 1) / p.units_per_plane;
+        if (planes2 > p.num_planes / 2) planes2 = p.num_planes / 2;
+        if (planes2 > 0) {
+            p.tier1_planes = p.num_planes - planes2;
+            p.units_per_plane2 = (groups_y + small - 1) / small;
+            p.bands_per_unit2 = (groups_y + p.units_per_plane2 - 1) / p.units_per_plane2;
+            p.units_per_plane2 = (groups_y + p.bands_per_unit2 - 1) / p.bands_per_unit2;
+        }
+    }
+    p.tier1_units = p.tier1_planes * p.units_per_plane;
+    p.total_units = p.tier1_units + (p.num_planes - p.tier1_planes) * p.units_per_plane2;
     p.stage_bytes = (int)((group_bytes + 127) & ~127ll);
 }
 
@@ -935,6 +961,17 @@ int dh_draw_heatmap(void* stream_, float* heatmaps, const int32_t* centers, cons
     p.csr_items = items;
     return dh::launch_render<dh::SRC_CSR>(stream, p, mode);
 }
+
+#ifdef DH_TRACE_UNITS
+// Profiling builds only (not declared in include/dh_b200.h, not in the shipped library).
+int dh_debug_set_trace(void* buf, int64_t units) {
+    unsigned long long* b = (unsigned long long*)buf;
+    long long n = units;
+    cudaError_t e = cudaMemcpyToSymbol(dh::g_trace, &b, sizeof(b));
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(dh::g_trace_units, &n, sizeof(n));
+    return (int)e;
+}
+#endif
 
 int dh_fill_probe(void* stream, void* dst, size_t bytes) {
     if (bytes == 0) return DH_OK;
