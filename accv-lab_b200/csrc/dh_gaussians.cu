@@ -352,3 +352,160 @@ extern "C" int dh_draw_gaussians(void* stream, const float* heatmap_in, float* h
     dh::count_launches(1);
     return (int)cudaGetLastError();
 }
+
+// ================================================================================================================
+// Front half of the reference's BoundingBoxToHeatmapConverter (everything between the annotation boxes and
+// draw_gaussians), one thread per RaggedBatch slot, one rounding per reference operation. Paths under
+// /root/reference/packages/dali_pipeline_framework/accvlab/dali_pipeline_framework:
+//   operators_impl/numba_operators/numba_operators.py:811-815    centre from the box
+//   operators_impl/python_operator_functions/python_operator_functions.py:140-171  scale, clip, sizes, area fraction
+//   processing_steps/bounding_box_to_heatmap_converter.py:352-355  floor -> int32 centre, sub-pixel offset
+//   python_operator_functions.py:213-251 + converter :369-371      is_active (class / size / area-fraction / is_valid)
+//   numba_operators.py:865-904 + converter :376                    radius (float64 product stored to fp32), clamp
+// The reference runs these as ~10 DALI CPU operators (python_function / numba_function) per sample.
+namespace dh {
+
+struct ConvParams {
+    const float* bboxes;
+    const float* centers;    // may be null: centre of the box
+    const int32_t* classes;  // may be null: no class check, sizes against row 0 of min_sizes
+    const uint8_t* valid;    // may be null
+    const void* sizes;
+    int sizes_i64;
+    const float* scale_xy;    // [B,2]
+    const double* min_sizes;  // [num_min_sizes,2] (h,w) or null
+    int num_min_sizes, num_classes;
+    long long B, T;
+    float w_max, h_max;  // heatmap W-1, H-1
+    double sf, min_frac;
+    float min_r, max_r;
+    float* bboxes_clipped;
+    int32_t* center_int;
+    float* center_offset;
+    float* radii;
+    uint8_t* is_active;
+    float* hw_clipped;
+    float* fraction;
+};
+
+__global__ void __launch_bounds__(256) converter_kernel(const ConvParams p) {
+    const long long total = p.B * p.T;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long b = i / p.T;
+        const long long t = i - b * p.T;
+        long long n = p.sizes_i64 ? reinterpret_cast<const long long*>(p.sizes)[b] : (long long)reinterpret_cast<const int*>(p.sizes)[b];
+        float x1 = 0.f, y1 = 0.f, x2 = 0.f, y2 = 0.f, offx = 0.f, offy = 0.f, rad = 0.f, hc = 0.f, wc = 0.f, frac = 0.f;
+        int cix = 0, ciy = 0;
+        bool act = false;
+        if (t < n) {
+            const float4 bb = reinterpret_cast<const float4*>(p.bboxes)[i];
+            float cx0, cy0;
+            if (p.centers) {
+                const float2 c = reinterpret_cast<const float2*>(p.centers)[i];
+                cx0 = c.x;
+                cy0 = c.y;
+            } else {
+                cx0 = __fdiv_rn(__fadd_rn(bb.x, bb.z), 2.0f);
+                cy0 = __fdiv_rn(__fadd_rn(bb.y, bb.w), 2.0f);
+            }
+            const float sx = p.scale_xy[2 * b], sy = p.scale_xy[2 * b + 1];
+            const float xs1 = __fmul_rn(sx, bb.x), xs2 = __fmul_rn(sx, bb.z), ys1 = __fmul_rn(sy, bb.y), ys2 = __fmul_rn(sy, bb.w);
+            x1 = fminf(fmaxf(xs1, 0.0f), p.w_max);
+            x2 = fminf(fmaxf(xs2, 0.0f), p.w_max);
+            y1 = fminf(fmaxf(ys1, 0.0f), p.h_max);
+            y2 = fminf(fmaxf(ys2, 0.0f), p.h_max);
+            hc = fabsf(__fsub_rn(y2, y1));
+            wc = fabsf(__fsub_rn(x2, x1));
+            const float ho = fabsf(__fsub_rn(ys2, ys1)), wo = fabsf(__fsub_rn(xs2, xs1));
+            frac = __fdiv_rn(__fmul_rn(hc, wc), __fmul_rn(ho, wo));  // 0/0 = NaN: never active
+            const float cx = fminf(fmaxf(__fmul_rn(sx, cx0), 0.0f), p.w_max);
+            const float cy = fminf(fmaxf(__fmul_rn(sy, cy0), 0.0f), p.h_max);
+            const float fx = floorf(cx), fy = floorf(cy);
+            cix = (int)fx;
+            ciy = (int)fy;
+            offx = __fsub_rn(cx, fx);
+            offy = __fsub_rn(cy, fy);
+            act = true;
+            int row = 0;
+            if (p.classes) {
+                const int c = p.classes[i];
+                act = c < p.num_classes;
+                row = (act && c >= 0) ? c : 0;
+            }
+            if (p.min_sizes && p.num_min_sizes > 0) {
+                row = row < p.num_min_sizes ? row : p.num_min_sizes - 1;
+                act = act && ((double)hc >= p.min_sizes[2 * row]) && ((double)wc >= p.min_sizes[2 * row + 1]);
+            }
+            act = act && ((double)frac >= p.min_frac);
+            if (p.valid) act = act && (p.valid[i] != 0);
+            const float l = fminf(x1, x2), r = fmaxf(x1, x2), tp = fminf(y1, y2), bt = fmaxf(y1, y2);
+            const float dist = fminf(fminf(__fsub_rn(cx, l), __fsub_rn(cy, tp)), fminf(__fsub_rn(r, cx), __fsub_rn(bt, cy)));
+            const double dd = fmax((double)dist, 0.0);
+            rad = __double2float_rn(__dmul_rn(dd, p.sf));
+            rad = fminf(fmaxf(p.min_r, rad), p.max_r);
+        }
+        if (p.bboxes_clipped) reinterpret_cast<float4*>(p.bboxes_clipped)[i] = make_float4(x1, y1, x2, y2);
+        reinterpret_cast<int2*>(p.center_int)[i] = make_int2(cix, ciy);
+        if (p.center_offset) reinterpret_cast<float2*>(p.center_offset)[i] = make_float2(offx, offy);
+        p.radii[i] = rad;
+        p.is_active[i] = act ? 1 : 0;
+        if (p.hw_clipped) reinterpret_cast<float2*>(p.hw_clipped)[i] = make_float2(hc, wc);
+        if (p.fraction) p.fraction[i] = frac;
+    }
+}
+
+}  // namespace dh
+
+extern "C" int dh_boxes_to_gaussian_params(void* stream, const float* bboxes, const float* centers, const int32_t* classes,
+                                           const uint8_t* is_valid, const void* nums_targets, int nums_dtype,
+                                           const float* scale_xy, const double* min_sizes_hw, int64_t num_min_sizes,
+                                           int64_t num_classes, int64_t B, int64_t T, int64_t heatmap_h, int64_t heatmap_w,
+                                           double radius_scaling_factor, float min_radius, float max_radius,
+                                           double min_fraction_area, float* bboxes_clipped, int32_t* center_int,
+                                           float* center_offset, float* radii, uint8_t* is_active, float* hw_clipped,
+                                           float* fraction_area) {
+    if (B < 0 || T < 0 || heatmap_h < 1 || heatmap_w < 1 || num_min_sizes < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
+    if (heatmap_h > (1ll << 23) || heatmap_w > (1ll << 23) || num_min_sizes > INT32_MAX) return DH_ERR_UNSUPPORTED_SHAPE;
+    if (B == 0 || T == 0) return DH_OK;
+    if (!bboxes || !nums_targets || !scale_xy || !center_int || !radii || !is_active) return DH_ERR_INVALID_ARGUMENT;
+    if (num_min_sizes > 0 && !min_sizes_hw) return DH_ERR_INVALID_ARGUMENT;
+    if ((reinterpret_cast<uintptr_t>(bboxes) & 15u) || (reinterpret_cast<uintptr_t>(centers) & 7u) ||
+        (reinterpret_cast<uintptr_t>(center_int) & 7u) || (reinterpret_cast<uintptr_t>(bboxes_clipped) & 15u) ||
+        (reinterpret_cast<uintptr_t>(center_offset) & 7u) || (reinterpret_cast<uintptr_t>(hw_clipped) & 7u))
+        return DH_ERR_INVALID_ARGUMENT;
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return DH_ERR_NO_DEVICE;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return DH_ERR_NO_DEVICE;
+    dh::ConvParams p{};
+    p.bboxes = bboxes;
+    p.centers = centers;
+    p.classes = classes;
+    p.valid = is_valid;
+    p.sizes = nums_targets;
+    p.sizes_i64 = nums_dtype == DH_SIZES_I64;
+    p.scale_xy = scale_xy;
+    p.min_sizes = min_sizes_hw;
+    p.num_min_sizes = (int)num_min_sizes;
+    p.num_classes = (int)(num_classes > INT32_MAX ? INT32_MAX : (num_classes < INT32_MIN ? INT32_MIN : num_classes));
+    p.B = B;
+    p.T = T;
+    p.w_max = (float)(heatmap_w - 1);
+    p.h_max = (float)(heatmap_h - 1);
+    p.sf = radius_scaling_factor;
+    p.min_frac = min_fraction_area;
+    p.min_r = min_radius;
+    p.max_r = max_radius;
+    p.bboxes_clipped = bboxes_clipped;
+    p.center_int = center_int;
+    p.center_offset = center_offset;
+    p.radii = radii;
+    p.is_active = is_active;
+    p.hw_clipped = hw_clipped;
+    p.fraction = fraction_area;
+    long long blocks = (B * T + 255) / 256;
+    if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
+    dh::converter_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(p);
+    dh::count_launches(1);
+    return (int)cudaGetLastError();
+}

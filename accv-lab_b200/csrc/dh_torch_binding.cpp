@@ -472,6 +472,80 @@ at::Tensor draw_gaussians(const c10::optional<at::Tensor>& heatmap_in, at::Tenso
     return heatmap_out;
 }
 
+// ---- front half of BoundingBoxToHeatmapConverter (bounding_box_to_heatmap_converter.py:321-376) ---------------
+std::vector<at::Tensor> boxes_to_gaussian_params(const at::Tensor& bboxes, const c10::optional<at::Tensor>& centers,
+                                                 const c10::optional<at::Tensor>& classes,
+                                                 const c10::optional<at::Tensor>& is_valid, const at::Tensor& nums_targets,
+                                                 const at::Tensor& scale_xy, const c10::optional<at::Tensor>& min_sizes_hw,
+                                                 int64_t num_classes, int64_t heatmap_h, int64_t heatmap_w,
+                                                 double radius_scaling_factor, double min_radius, double max_radius,
+                                                 double min_fraction_area) {
+    CHECK_INPUT(bboxes);
+    CHECK_INPUT(nums_targets);
+    CHECK_INPUT(scale_xy);
+    CHECK_DTYPE(bboxes, at::kFloat);
+    CHECK_DTYPE(scale_xy, at::kFloat);
+    TORCH_CHECK(bboxes.dim() == 3 && bboxes.size(2) == 4, "bboxes must be of shape [batch_size, max_num_targets, 4]");
+    const int64_t B = bboxes.size(0), T = bboxes.size(1);
+    TORCH_CHECK(nums_targets.dim() == 1 && nums_targets.size(0) == B, "nums_targets must be of shape [batch_size]");
+    TORCH_CHECK(scale_xy.dim() == 2 && scale_xy.size(0) == B && scale_xy.size(1) == 2, "scale_xy must be of shape [batch_size, 2]");
+    CHECK_SAME_DEVICE(nums_targets, bboxes);
+    CHECK_SAME_DEVICE(scale_xy, bboxes);
+    const float* c_ptr = nullptr;
+    const int32_t* k_ptr = nullptr;
+    const uint8_t* v_ptr = nullptr;
+    const double* m_ptr = nullptr;
+    int64_t nm = 0;
+    if (centers.has_value()) {
+        const at::Tensor& c = *centers;
+        CHECK_INPUT(c);
+        CHECK_DTYPE(c, at::kFloat);
+        CHECK_SAME_DEVICE(c, bboxes);
+        TORCH_CHECK(c.dim() == 3 && c.size(0) == B && c.size(1) == T && c.size(2) == 2, "centers must be of shape [batch_size, max_num_targets, 2]");
+        c_ptr = c.data_ptr<float>();
+    }
+    if (classes.has_value()) {
+        const at::Tensor& k = *classes;
+        CHECK_INPUT(k);
+        CHECK_DTYPE(k, at::kInt);
+        CHECK_SAME_DEVICE(k, bboxes);
+        TORCH_CHECK(k.dim() == 2 && k.size(0) == B && k.size(1) == T, "classes must be of shape [batch_size, max_num_targets]");
+        k_ptr = k.data_ptr<int>();
+    }
+    if (is_valid.has_value()) {
+        const at::Tensor& v = *is_valid;
+        CHECK_INPUT(v);
+        TORCH_CHECK(v.scalar_type() == at::kBool || v.scalar_type() == at::kByte, "is_valid must be bool");
+        CHECK_SAME_DEVICE(v, bboxes);
+        TORCH_CHECK(v.dim() == 2 && v.size(0) == B && v.size(1) == T, "is_valid must be of shape [batch_size, max_num_targets]");
+        v_ptr = static_cast<const uint8_t*>(v.data_ptr());
+    }
+    if (min_sizes_hw.has_value()) {
+        const at::Tensor& m = *min_sizes_hw;
+        CHECK_INPUT(m);
+        CHECK_DTYPE(m, at::kDouble);
+        CHECK_SAME_DEVICE(m, bboxes);
+        TORCH_CHECK(m.dim() == 2 && m.size(1) == 2, "min_sizes_hw must be of shape [n, 2]");
+        m_ptr = m.data_ptr<double>();
+        nm = m.size(0);
+    }
+    int tag = 0;
+    const void* sizes = sizes_ptr(nums_targets, tag);
+    c10::cuda::CUDAGuard guard(bboxes.device());
+    auto f = bboxes.options();
+    at::Tensor bc = at::empty({B, T, 4}, f), ci = at::empty({B, T, 2}, f.dtype(at::kInt)), off = at::empty({B, T, 2}, f),
+               rad = at::empty({B, T}, f), act = at::empty({B, T}, f.dtype(at::kBool)), hw = at::empty({B, T, 2}, f),
+               fr = at::empty({B, T}, f);
+    check_status(dh_boxes_to_gaussian_params(at::cuda::getCurrentCUDAStream().stream(), bboxes.data_ptr<float>(), c_ptr, k_ptr,
+                                             v_ptr, sizes, tag, scale_xy.data_ptr<float>(), m_ptr, nm, num_classes, B, T,
+                                             heatmap_h, heatmap_w, radius_scaling_factor, (float)min_radius,
+                                             (float)max_radius, min_fraction_area, bc.data_ptr<float>(), ci.data_ptr<int>(),
+                                             off.data_ptr<float>(), rad.data_ptr<float>(),
+                                             static_cast<uint8_t*>(act.data_ptr()), hw.data_ptr<float>(), fr.data_ptr<float>()),
+                 "boxes_to_gaussian_params");
+    return {bc, ci, off, rad, act, hw, fr};
+}
+
 void fill_probe(at::Tensor& t) {
     CHECK_INPUT(t);
     c10::cuda::CUDAGuard guard(t.device());
@@ -528,6 +602,12 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           pybind11::arg("heatmap_in"), pybind11::arg("heatmap_out"), pybind11::arg("active"), pybind11::arg("slice_ids"),
           pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"), pybind11::arg("k_for_classes"),
           pybind11::arg("radius_to_sigma_factor"));
+    m.def("boxes_to_gaussian_params", &boxes_to_gaussian_params,
+          "Boxes -> (clipped boxes, int centres, offsets, float radii, is_active, clipped hw, area fraction): the front half of the DALI heatmap converter, one launch.",
+          pybind11::arg("bboxes"), pybind11::arg("centers"), pybind11::arg("classes"), pybind11::arg("is_valid"),
+          pybind11::arg("nums_targets"), pybind11::arg("scale_xy"), pybind11::arg("min_sizes_hw"), pybind11::arg("num_classes"),
+          pybind11::arg("heatmap_h"), pybind11::arg("heatmap_w"), pybind11::arg("radius_scaling_factor"),
+          pybind11::arg("min_radius"), pybind11::arg("max_radius"), pybind11::arg("min_fraction_area"));
     m.def("combine_data", &combine_data,
           "List of per-sample CUDA tensors [n_i, *data] -> (zero-padded tensor [B, T, *data], int64 sample sizes [B]); one launch.",
           pybind11::arg("data_list"), pybind11::arg("max_sample_size") = -1);

@@ -219,6 +219,30 @@ int dh_draw_gaussians(void* stream, const float* heatmap_in, float* heatmap_out,
                       int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
                       float radius_to_sigma_factor, dh_status* status);
 
+/* Front half of the reference's BoundingBoxToHeatmapConverter — everything between the annotation boxes and
+ * draw_gaussians, ~10 DALI CPU operators per sample in the reference — as ONE launch over the RaggedBatch slots:
+ *   centre from the box (numba_operators.py:811-815, when centers == NULL), scale by scale_xy[b] = (sx, sy) and clip to
+ *   the heatmap (python_operator_functions.py:140-171), integer centre = floor, sub-pixel offset (converter :352-355),
+ *   is_active = class < num_classes && clipped (h,w) >= min sizes && area fraction >= min_fraction_area && is_valid
+ *   (python_operator_functions.py:213-251, converter :369-371), radius = clamp(max(0, min distance of the clipped centre
+ *   to the clipped box border) * radius_scaling_factor [float64 product stored to fp32], min_radius, max_radius)
+ *   (numba_operators.py:865-904, converter :376).
+ * Inputs (device): bboxes f32 [B,T,4] (x1,y1,x2,y2 in image coordinates, corners in any order; 16-byte aligned),
+ * centers f32 [B,T,2] or NULL, classes i32 [B,T] or NULL (no class check), is_valid u8 [B,T] or NULL,
+ * nums_targets [B], scale_xy f32 [B,2] (heatmap size / image size per sample), min_sizes_hw f64 [num_min_sizes,2]
+ * (h,w): per-class table indexed by class when classes != NULL, else its row 0; num_min_sizes = 0: no size check.
+ * Outputs (device, [B,T,...], padded slots = 0): center_int i32 [.,2], radii f32, is_active u8 (inputs of
+ * dh_draw_gaussians), and optionally bboxes_clipped f32 [.,4], center_offset f32 [.,2], hw_clipped f32 [.,2] (h,w),
+ * fraction_area f32 (NULL to skip). NaN coordinates are not supported (numpy's clip propagates them). */
+int dh_boxes_to_gaussian_params(void* stream, const float* bboxes, const float* centers, const int32_t* classes,
+                                const uint8_t* is_valid, const void* nums_targets, int nums_dtype, const float* scale_xy,
+                                const double* min_sizes_hw, int64_t num_min_sizes, int64_t num_classes,
+                                int64_t batch_size, int64_t max_num_targets, int64_t heatmap_height,
+                                int64_t heatmap_width, double radius_scaling_factor, float min_radius, float max_radius,
+                                double min_fraction_area, float* bboxes_clipped, int32_t* center_int,
+                                float* center_offset, float* radii, uint8_t* is_active, float* hw_clipped,
+                                float* fraction_area);
+
 /* ---- measurement helper ---------------------------------------------------------------
  * Pure 128-bit-store fill of `bytes` bytes (multiple of 16, 16-byte aligned) with zeros using the same
  * store path and grid shape as the FRESH renderer: the write-only ceiling the renderer is compared to. */

@@ -265,3 +265,72 @@ def draw_gaussians(heat, centers, radii, sizes, k_for_classes, radius_to_sigma_f
     lib().dho_draw_gaussians(_ptr(heat), _ptr(centers), _ptr(radii), _ptr(sl), _ptr(ac), _ptr(sizes), _ptr(k), k.size,
                              B, T, C, H, W, float(radius_to_sigma_factor))
     return heat
+
+
+# ---- N2 front half: BoundingBoxToHeatmapConverter up to draw_gaussians, numpy restatement ----------------------
+def boxes_to_gaussian_params_numpy(bboxes, centers, classes, valid, sizes, scale, heatmap_hw, radius_scaling_factor,
+                                   min_radius, max_radius, min_fraction_area, num_classes=None, per_class_min_size=None,
+                                   min_object_size=None):
+    """RaggedBatch layout [B,T]. Restates, with one fp32 rounding per reference operation
+    (paths under /root/reference/packages/dali_pipeline_framework/accvlab/dali_pipeline_framework):
+      centre from box           operators_impl/numba_operators/numba_operators.py:811-815   (x1+x2)/2, (y1+y2)/2
+      scale + clip              operators_impl/python_operator_functions/python_operator_functions.py:140-171
+                                (trafo = diag(sx, sy): x' = fl(sx*x); clip to [0, W-1] / [0, H-1]; |.| sizes; area fraction)
+      floor / offset            processing_steps/bounding_box_to_heatmap_converter.py:352-355
+      is_active                 python_operator_functions.py:213-251, & is_valid (converter :369-371)
+      radius                    numba_operators.py:865-904 (corner order resolved, min distance to the border, max(0,.),
+                                float64 product with the scaling factor stored to fp32), clamp converter :376
+    centers / classes / valid may be None (centre from the box / no class check / all valid).
+    Returns dict(bboxes_clipped, center_int, center_offset, radii, is_active, hw_clipped, fraction); padded slots are 0."""
+    f32 = np.float32
+    bb = np.asarray(bboxes, f32)
+    B, T = bb.shape[:2]
+    sizes = np.asarray(sizes, np.int64)
+    scale = np.asarray(scale, f32).reshape(B, 2)
+    Hh, Wh = int(heatmap_hw[0]), int(heatmap_hw[1])
+    if centers is None:
+        cen = np.stack([(bb[..., 0] + bb[..., 2]) / f32(2.0), (bb[..., 1] + bb[..., 3]) / f32(2.0)], -1).astype(f32)
+    else:
+        cen = np.asarray(centers, f32)
+    sx, sy = scale[:, None, 0], scale[:, None, 1]
+    xs = [(sx * bb[..., 0]).astype(f32), (sx * bb[..., 2]).astype(f32)]
+    ys = [(sy * bb[..., 1]).astype(f32), (sy * bb[..., 3]).astype(f32)]
+    clipx = lambda v: np.minimum(np.maximum(v, f32(0)), f32(Wh - 1)).astype(f32)
+    clipy = lambda v: np.minimum(np.maximum(v, f32(0)), f32(Hh - 1)).astype(f32)
+    x1, x2, y1, y2 = clipx(xs[0]), clipx(xs[1]), clipy(ys[0]), clipy(ys[1])
+    h_c, w_c = np.abs(y2 - y1).astype(f32), np.abs(x2 - x1).astype(f32)
+    h_o, w_o = np.abs(ys[1] - ys[0]).astype(f32), np.abs(xs[1] - xs[0]).astype(f32)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        frac = ((h_c * w_c).astype(f32) / (h_o * w_o).astype(f32)).astype(f32)
+    cx, cy = clipx((sx * cen[..., 0]).astype(f32)), clipy((sy * cen[..., 1]).astype(f32))
+    cix, ciy = np.floor(cx).astype(np.int32), np.floor(cy).astype(np.int32)
+    offx, offy = (cx - cix.astype(f32)).astype(f32), (cy - ciy.astype(f32)).astype(f32)
+    # is_active
+    act = np.ones((B, T), bool)
+    if classes is not None:
+        cls = np.asarray(classes, np.int64)
+        act &= cls < int(num_classes)
+        if per_class_min_size is not None and len(per_class_min_size):
+            tab = np.asarray(per_class_min_size, np.float64)
+            cc = np.where(cls < int(num_classes), cls, 0)
+            cc = np.clip(cc, 0, len(tab) - 1)  # negative ids index from the end in the reference; not exercised
+            act &= (h_c.astype(np.float64) >= tab[cc, 0]) & (w_c.astype(np.float64) >= tab[cc, 1])
+    elif min_object_size is not None and len(min_object_size):
+        act &= (h_c.astype(np.float64) >= float(min_object_size[0])) & (w_c.astype(np.float64) >= float(min_object_size[1]))
+    act &= frac.astype(np.float64) >= float(min_fraction_area)
+    if valid is not None:
+        act &= np.asarray(valid, bool)
+    # radius on the CLIPPED box around the CLIPPED centre
+    l, r = np.minimum(x1, x2), np.maximum(x1, x2)
+    t, b = np.minimum(y1, y2), np.maximum(y1, y2)
+    dist = np.minimum(np.minimum((cx - l).astype(f32), (cy - t).astype(f32)), np.minimum((r - cx).astype(f32), (b - cy).astype(f32)))
+    dist = np.maximum(dist.astype(np.float64), 0.0)
+    rad = (dist * float(radius_scaling_factor)).astype(f32)
+    rad = np.minimum(np.maximum(f32(min_radius), rad), f32(max_radius)).astype(f32)
+    pad = np.arange(T)[None, :] >= sizes[:, None]
+    res = dict(bboxes_clipped=np.stack([x1, y1, x2, y2], -1).astype(f32), center_int=np.stack([cix, ciy], -1).astype(np.int32),
+               center_offset=np.stack([offx, offy], -1).astype(f32), radii=rad, is_active=act,
+               hw_clipped=np.stack([h_c, w_c], -1).astype(f32), fraction=frac)
+    for k, v in res.items():
+        v[pad] = 0
+    return res

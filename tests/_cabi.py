@@ -45,6 +45,8 @@ SIGNATURES = {
     "dh_pack_ragged": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i]),
     "dh_pack_radius_center": (_i, [_p, _p, _p, _p, _f, _i64, _i64, _p, _p]),
     "dh_draw_gaussians": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _i64, _f, _p]),
+    "dh_boxes_to_gaussian_params": (_i, [_p, _p, _p, _p, _p, _p, _i, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64,
+                                         ctypes.c_double, _f, _f, ctypes.c_double, _p, _p, _p, _p, _p, _p, _p]),
     "dh_fill_probe": (_i, [_p, _p, _sz]),
     "dh_expf_probe": (_i, [_p, ctypes.c_uint32, _i64, _p]),
 }

@@ -152,3 +152,77 @@ def test_gpu_out_of_range_classes_and_radii_are_skipped_and_counted(cabi, cuda_d
     _check(out.cpu().numpy(), want, "skips")
     st = status.cpu().numpy()
     assert st[0] == 1 and st[2] == 2  # one bad class; NaN and 1e9 radii
+
+
+# ------------------------------------------------------------------------- converter front half (boxes -> params)
+CONV_GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_converter.npz")
+CONV_CASES = ("perclass", "classes_nothresh", "noclass_minsize", "noclass_plain")
+CONV_OUT = ("bboxes_clipped", "center_int", "center_offset", "radii", "is_active", "hw_clipped", "fraction")
+
+
+def _conv_case(name):
+    g = np.load(CONV_GOLD)
+    c = {k[len(name) + 1:]: g[k] for k in g.files if k.startswith(name + "_")}
+    P = c["params"]
+    c["kw"] = dict(heatmap_hw=(int(P[0]), int(P[1])), radius_scaling_factor=float(P[2]), min_radius=float(P[3]),
+                   max_radius=float(P[4]), min_fraction_area=float(P[5]), num_classes=int(P[6]),
+                   per_class_min_size=c["per_class"] if len(c["per_class"]) else None,
+                   min_object_size=c["min_size"] if len(c["min_size"]) else None)
+    c["use_classes"], c["own_centers"], c["with_valid"] = bool(P[7]), bool(P[8]), bool(P[9])
+    return c
+
+
+def _same(a, b, name):
+    if a.dtype.kind == "f":
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32)) or np.array_equal(a, b, equal_nan=True), name
+    else:
+        assert np.array_equal(a, b), name
+
+
+@pytest.mark.parametrize("name", CONV_CASES)
+def test_oracle_converter_front_half_reproduces_reference_bit_for_bit(oracle, name):
+    c = _conv_case(name)
+    got = oracle.boxes_to_gaussian_params_numpy(c["bboxes"], c["centers"] if c["own_centers"] else None,
+                                                c["classes"] if c["use_classes"] else None,
+                                                c["valid"] if c["with_valid"] else None, c["sizes"], c["scale"], **c["kw"])
+    for k in CONV_OUT:
+        _same(got[k], c[k], f"{name}/{k}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CONV_CASES)
+def test_gpu_converter_front_half_matches_reference_bit_for_bit(cuda_dev, name):
+    """boxes -> (clipped boxes, int centre, offset, radius, is_active, hw, fraction) on the GPU == the reference's own
+    Python / numba functions (tests/golden/ref_converter.npz), every output bit-exact; then straight into draw_gaussians."""
+    import torch
+    from accvlab.draw_heatmap import b200
+
+    c = _conv_case(name)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda_dev)
+    sizes = dev(c["sizes"])
+    rb = lambda a: b200.RaggedBatch(dev(a), sample_sizes=sizes)
+    kw = c["kw"]
+    l0 = b200.launch_count()
+    got = b200.boxes_to_gaussian_params(
+        rb(c["bboxes"]), dev(c["scale"]), kw["heatmap_hw"], centers=rb(c["centers"]) if c["own_centers"] else None,
+        classes=rb(c["classes"]) if c["use_classes"] else None, is_valid=rb(c["valid"]) if c["with_valid"] else None,
+        radius_scaling_factor=kw["radius_scaling_factor"], min_radius=kw["min_radius"], max_radius=kw["max_radius"],
+        min_fraction_area=kw["min_fraction_area"], num_classes=kw["num_classes"],
+        per_class_min_object_sizes=kw["per_class_min_size"], min_object_size=kw["min_object_size"])
+    assert b200.launch_count() - l0 == 1
+    names = dict(bboxes_clipped="bboxes_clipped", center="center_int", center_offset="center_offset", radii="radii",
+                 is_active="is_active", hw_clipped="hw_clipped", fraction_area="fraction")
+    for k, gk in names.items():
+        _same(got[k].tensor.cpu().numpy(), c[gk], f"{name}/{k}")
+    # and on into the renderer: same heatmap as the oracle on the reference's parameters
+    C = kw["num_classes"] if c["use_classes"] else 1
+    H, W = kw["heatmap_hw"]
+    kcls = np.linspace(0.7, 1.0, C).astype(np.float32)
+    slice_ids = rb(np.clip(c["classes"], 0, C - 1).astype(np.int32)) if c["use_classes"] else None
+    heat = b200.draw_gaussians(None, got["is_active"], slice_ids, got["center"], got["radii"], dev(kcls), 1.0 / 3.0,
+                               shape=(len(c["sizes"]), C, H, W))
+    from oracle import oracle as orc
+    want = np.zeros(heat.shape, np.float32)
+    orc.draw_gaussians(want, c["center_int"], c["radii"], c["sizes"], kcls, 1.0 / 3.0,
+                       np.clip(c["classes"], 0, C - 1).astype(np.int32) if c["use_classes"] else None, c["is_active"])
+    _check(heat.cpu().numpy(), want, name + " render")
