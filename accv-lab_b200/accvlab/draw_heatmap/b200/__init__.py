@@ -30,6 +30,7 @@ __all__ = [
     "render_heatmap_flat",
     "draw_gaussians",
     "boxes_to_gaussian_params",
+    "gaussian_radius",
     "combine_data",
     "pack_radius_center",
     "shard_range",
@@ -183,6 +184,18 @@ def boxes_to_gaussian_params(bboxes, scale_xy: torch.Tensor, heatmap_hw: Tuple[i
                                          float(min_fraction_area))
     names = ("bboxes_clipped", "center", "center_offset", "radii", "is_active", "hw_clipped", "fraction_area")
     return {k: RaggedBatch(v, sample_sizes=sizes) for k, v in zip(names, outs)}
+
+
+def gaussian_radius(det_size: torch.Tensor, min_overlap: float = 0.5, variant: str = "cornernet", min_radius: int = 0,
+                    return_float: bool = False):
+    """CenterNet / CenterPoint ``gaussian_radius(det_size, min_overlap)`` for a float32 CUDA tensor ``[..., 2]`` of
+    (height, width) in heatmap pixels -> int32 radii ``max(min_radius, int(r))`` (what CenterPoint's target assigner
+    feeds to its ``draw_heatmap_gaussian``), ready for :func:`render_heatmap_batched` / ``draw_heatmap_batched``.
+    ``variant``: ``"cornernet"`` (CornerNet / CenterNet / CenterPoint) or ``"mmdet"`` (corrected roots). Not part of the
+    reference (its example helper uses the minimum border distance, :func:`radius_center`)."""
+    v = {"cornernet": 0, "mmdet": 1}[variant]
+    ri, rf = _ext.gaussian_radius(det_size.contiguous(), float(min_overlap), v, int(min_radius))
+    return (ri, rf) if return_float else ri
 
 
 def _flatten(data) -> list:

@@ -116,3 +116,62 @@ int dh_pack_radius_center(void* stream, const float* const* centers_ptrs, const 
 }
 
 }  // extern "C"
+
+// ================================================================================================================
+// N4: the CenterNet / CenterPoint `gaussian_radius(det_size, min_overlap)` as a K1 mode.
+// NOT in the reference (its helper uses the min border distance, dh_k1.cuh) -> PARITY UNPINNED: the
+// arithmetic restates the published algorithm (CornerNet `gaussian_radius`, kept by CenterNet utils/image.py and
+// CenterPoint det3d core/utils/center_utils.py; mmdet models/utils/gaussian_target.py is the variant with the
+// corrected roots), evaluated like upstream in float64 (Python floats), one IEEE operation per upstream operation
+// (no FMA contraction: explicit __d*_rn), then radius = max(min_radius, (int)r) as in CenterPoint's target assigner.
+namespace dh {
+
+__device__ __forceinline__ double gr_root(double a, double b, double c, bool plus) {
+    const double disc = __dsub_rn(__dmul_rn(b, b), __dmul_rn(__dmul_rn(4.0, a), c));
+    const double sq = __dsqrt_rn(disc);
+    return __ddiv_rn(plus ? __dadd_rn(b, sq) : __dsub_rn(b, sq), __dmul_rn(2.0, a));
+}
+
+__global__ void __launch_bounds__(256) gaussian_radius_kernel(const float* __restrict__ det_hw, double mo, int variant,
+                                                              int min_radius, long long n, int32_t* __restrict__ out,
+                                                              float* __restrict__ out_f) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double h = (double)det_hw[2 * i], w = (double)det_hw[2 * i + 1];
+        const double hw = __dadd_rn(h, w), wh = __dmul_rn(w, h);
+        const double om = __dsub_rn(1.0, mo);
+        double r1, r2, r3;
+        if (variant == DH_RADIUS_CORNERNET) {  // a = 1 / 4 / 4*mo, roots (b + sqrt) / 2 (no division by a)
+            const double c1 = __ddiv_rn(__dmul_rn(wh, om), __dadd_rn(1.0, mo));
+            r1 = __ddiv_rn(__dadd_rn(hw, __dsqrt_rn(__dsub_rn(__dmul_rn(hw, hw), __dmul_rn(4.0, c1)))), 2.0);
+            const double b2 = __dmul_rn(2.0, hw), c2 = __dmul_rn(om, wh);
+            r2 = __ddiv_rn(__dadd_rn(b2, __dsqrt_rn(__dsub_rn(__dmul_rn(b2, b2), __dmul_rn(16.0, c2)))), 2.0);
+            const double a3 = __dmul_rn(4.0, mo), b3 = __dmul_rn(__dmul_rn(-2.0, mo), hw), c3 = __dmul_rn(__dsub_rn(mo, 1.0), wh);
+            r3 = __ddiv_rn(__dadd_rn(b3, __dsqrt_rn(__dsub_rn(__dmul_rn(b3, b3), __dmul_rn(__dmul_rn(4.0, a3), c3)))), 2.0);
+        } else {  // mmdet: (b - sqrt) / (2a), (b - sqrt) / (2a), (b + sqrt) / (2a)
+            r1 = gr_root(1.0, hw, __ddiv_rn(__dmul_rn(wh, om), __dadd_rn(1.0, mo)), false);
+            r2 = gr_root(4.0, __dmul_rn(2.0, hw), __dmul_rn(om, wh), false);
+            r3 = gr_root(__dmul_rn(4.0, mo), __dmul_rn(__dmul_rn(-2.0, mo), hw), __dmul_rn(__dsub_rn(mo, 1.0), wh), true);
+        }
+        const double r = fmin(fmin(r1, r2), r3);
+        if (out_f) out_f[i] = (float)r;
+        int ri = (r >= 2147483647.0) ? 2147483647 : (r > -2147483648.0 ? (int)r : (-2147483647 - 1));  // int(r); NaN -> INT_MIN
+        out[i] = ri < min_radius ? min_radius : ri;
+    }
+}
+
+}  // namespace dh
+
+extern "C" int dh_gaussian_radius(void* stream, const float* det_hw, double min_overlap, int variant, int32_t min_radius,
+                                  int64_t n, int32_t* radii_out, float* radii_float_out) {
+    if (n < 0 || (variant != DH_RADIUS_CORNERNET && variant != DH_RADIUS_MMDET)) return DH_ERR_INVALID_ARGUMENT;
+    if (n == 0) return DH_OK;
+    if (!det_hw || !radii_out) return DH_ERR_INVALID_ARGUMENT;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) return DH_ERR_NO_DEVICE;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 1184) blocks = 1184;
+    dh::gaussian_radius_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(det_hw, min_overlap, variant, min_radius, n,
+                                                                             radii_out, radii_float_out);
+    dh::count_launches(1);
+    return (int)cudaGetLastError();
+}

@@ -546,6 +546,22 @@ std::vector<at::Tensor> boxes_to_gaussian_params(const at::Tensor& bboxes, const
     return {bc, ci, off, rad, act, hw, fr};
 }
 
+// ---- N4: CenterNet / CenterPoint gaussian_radius (not in the reference; parity unpinned) -------------------------
+std::tuple<at::Tensor, at::Tensor> gaussian_radius(const at::Tensor& det_hw, double min_overlap, int64_t variant,
+                                                   int64_t min_radius) {
+    CHECK_INPUT(det_hw);
+    CHECK_DTYPE(det_hw, at::kFloat);
+    TORCH_CHECK(det_hw.dim() >= 1 && det_hw.size(-1) == 2, "det_size must be of shape [..., 2] (height, width)");
+    c10::cuda::CUDAGuard guard(det_hw.device());
+    auto lead = det_hw.sizes().vec();
+    lead.pop_back();
+    at::Tensor ri = at::empty(lead, det_hw.options().dtype(at::kInt)), rf = at::empty(lead, det_hw.options());
+    check_status(dh_gaussian_radius(at::cuda::getCurrentCUDAStream().stream(), det_hw.data_ptr<float>(), min_overlap,
+                                    (int)variant, (int32_t)min_radius, ri.numel(), ri.data_ptr<int>(), rf.data_ptr<float>()),
+                 "gaussian_radius");
+    return {ri, rf};
+}
+
 void fill_probe(at::Tensor& t) {
     CHECK_INPUT(t);
     c10::cuda::CUDAGuard guard(t.device());
@@ -608,6 +624,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           pybind11::arg("nums_targets"), pybind11::arg("scale_xy"), pybind11::arg("min_sizes_hw"), pybind11::arg("num_classes"),
           pybind11::arg("heatmap_h"), pybind11::arg("heatmap_w"), pybind11::arg("radius_scaling_factor"),
           pybind11::arg("min_radius"), pybind11::arg("max_radius"), pybind11::arg("min_fraction_area"));
+    m.def("gaussian_radius", &gaussian_radius, "CenterNet/CenterPoint gaussian_radius(det_size, min_overlap) -> (int32 radii, float32 radii).",
+          pybind11::arg("det_hw"), pybind11::arg("min_overlap"), pybind11::arg("variant"), pybind11::arg("min_radius"));
     m.def("combine_data", &combine_data,
           "List of per-sample CUDA tensors [n_i, *data] -> (zero-padded tensor [B, T, *data], int64 sample sizes [B]); one launch.",
           pybind11::arg("data_list"), pybind11::arg("max_sample_size") = -1);

@@ -243,6 +243,17 @@ int dh_boxes_to_gaussian_params(void* stream, const float* bboxes, const float* 
                                 float* center_offset, float* radii, uint8_t* is_active, float* hw_clipped,
                                 float* fraction_area);
 
+/* ---- N4: CenterNet / CenterPoint gaussian_radius(det_size, min_overlap) as a K1 mode ----------------------
+ * NOT in the reference (its helper uses the minimum border distance, dh_radius_center): PARITY UNPINNED. Restates the
+ * published algorithm in float64 like upstream: DH_RADIUS_CORNERNET = CornerNet / CenterNet utils/image.py / CenterPoint
+ * center_utils.py (roots (b + sqrt(b^2 - 4ac)) / 2), DH_RADIUS_MMDET = mmdet gaussian_target.py (corrected roots
+ * (b -/+ sqrt) / (2a)); radii_out[i] = max(min_radius, (int)min(r1, r2, r3)). det_hw float32 [n,2] = (height, width)
+ * in heatmap pixels; radii_float_out (optional) receives min(r1, r2, r3) before truncation. */
+#define DH_RADIUS_CORNERNET 0
+#define DH_RADIUS_MMDET 1
+int dh_gaussian_radius(void* stream, const float* det_hw, double min_overlap, int variant, int32_t min_radius, int64_t n,
+                       int32_t* radii_out, float* radii_float_out);
+
 /* ---- measurement helper ---------------------------------------------------------------
  * Pure 128-bit-store fill of `bytes` bytes (multiple of 16, 16-byte aligned) with zeros using the same
  * store path and grid shape as the FRESH renderer: the write-only ceiling the renderer is compared to. */

@@ -334,3 +334,35 @@ def boxes_to_gaussian_params_numpy(bboxes, centers, classes, valid, sizes, scale
     for k, v in res.items():
         v[pad] = 0
     return res
+
+
+# ---- N4: CenterNet / CenterPoint gaussian_radius — PARITY UNPINNED (no implementation in /root/reference) -------
+def gaussian_radius_numpy(det_hw, min_overlap=0.5, variant="cornernet", min_radius=0):
+    """Published algorithm, float64 like upstream (Python floats). variant "cornernet": CornerNet `gaussian_radius`
+    (kept verbatim by CenterNet src/lib/utils/image.py and CenterPoint det3d/core/utils/center_utils.py):
+    r = (b + sqrt(b^2 - 4ac)) / 2; variant "mmdet": mmdet/models/utils/gaussian_target.py: (b -/+ sqrt(.)) / (2a).
+    Returns (int radii = max(min_radius, int(r)), float r). Neither package is installed here and the reference has no
+    such function, so this restatement is checked against hand-computed values only."""
+    d = np.asarray(det_hw, np.float32).astype(np.float64).reshape(-1, 2)
+    h, w = d[:, 0], d[:, 1]
+    mo = float(min_overlap)
+    with np.errstate(invalid="ignore"):
+        if variant == "cornernet":
+            c1 = w * h * (1 - mo) / (1 + mo)
+            r1 = ((h + w) + np.sqrt((h + w) * (h + w) - 4 * c1)) / 2
+            b2 = 2 * (h + w)
+            c2 = (1 - mo) * (w * h)
+            r2 = (b2 + np.sqrt(b2 * b2 - 16 * c2)) / 2
+            a3, b3, c3 = 4 * mo, -2 * mo * (h + w), (mo - 1) * (w * h)
+            r3 = (b3 + np.sqrt(b3 * b3 - 4 * a3 * c3)) / 2
+        else:
+            c1 = w * h * (1 - mo) / (1 + mo)
+            r1 = ((h + w) - np.sqrt((h + w) * (h + w) - 4 * 1.0 * c1)) / (2 * 1.0)
+            b2 = 2 * (h + w)
+            c2 = (1 - mo) * (w * h)
+            r2 = (b2 - np.sqrt(b2 * b2 - 4 * 4.0 * c2)) / (2 * 4.0)
+            a3, b3, c3 = 4 * mo, -2 * mo * (h + w), (mo - 1) * (w * h)
+            r3 = (b3 + np.sqrt(b3 * b3 - 4 * a3 * c3)) / (2 * a3)
+        r = np.minimum(np.minimum(r1, r2), r3)
+    ri = np.where(np.isnan(r), -2**31, np.clip(np.trunc(np.nan_to_num(r)), -2**31, 2**31 - 1)).astype(np.int64)
+    return np.maximum(ri, int(min_radius)).astype(np.int32), r.astype(np.float32)
