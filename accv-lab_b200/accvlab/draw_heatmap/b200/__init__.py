@@ -30,6 +30,7 @@ __all__ = [
     "render_heatmap_flat",
     "draw_gaussians",
     "boxes_to_gaussian_params",
+    "gaussian_focal_loss",
     "gaussian_radius",
     "combine_data",
     "pack_radius_center",
@@ -196,6 +197,39 @@ def gaussian_radius(det_size: torch.Tensor, min_overlap: float = 0.5, variant: s
     v = {"cornernet": 0, "mmdet": 1}[variant]
     ri, rf = _ext.gaussian_radius(det_size.contiguous(), float(min_overlap), v, int(min_radius))
     return (ri, rf) if return_float else ri
+
+
+class _GaussianFocalLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, centers, radii, sizes, labels, factor, k_scale, alpha, gamma, eps):
+        out2, grad = _ext.gaussian_focal_loss(pred.contiguous(), centers, radii, sizes, labels, factor, k_scale, alpha, gamma, eps,
+                                              pred.requires_grad)
+        if pred.requires_grad:
+            ctx.save_for_backward(grad)
+        ctx.mark_non_differentiable(out2)
+        return out2[0].to(torch.float32), out2
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_out2):
+        (grad,) = ctx.saved_tensors
+        return (grad * g_loss,) + (None,) * 9
+
+
+def gaussian_focal_loss(pred: torch.Tensor, centers, radii, diameter_to_sigma_factor: float = 6.0, k_scale: float = 1.0,
+                        labels=None, alpha: float = 2.0, gamma: float = 4.0, eps: float = 1e-12):
+    """Fused consumer of the heatmap: ``sum(GaussianFocalLoss(pred, target))`` where ``target`` is
+    the heatmap ``draw_heatmap_batched`` would draw from ``centers`` / ``radii`` (/ ``labels``) into zeros — without
+    ever writing the target to memory (formula: reference docs/intro.rst:7-26; mmdet's ``gaussian_focal_loss`` with
+    ``reduction='sum'``). Returns ``(loss_sum, num_pos)``: a differentiable float32 scalar (the gradient w.r.t. ``pred``
+    is produced by the same launch) and the number of ``target == 1`` pixels (the usual ``avg_factor``)."""
+    c_t, sizes = _tensor_and_sizes(centers)
+    r_t, _ = _tensor_and_sizes(radii)
+    l_t = None if labels is None else _tensor_and_sizes(labels)[0]
+    if sizes is None:
+        sizes = torch.full((r_t.shape[0],), r_t.shape[1], dtype=torch.int64, device=r_t.device)
+    loss, out2 = _GaussianFocalLoss.apply(pred, c_t, r_t, sizes, l_t, float(diameter_to_sigma_factor), float(k_scale),
+                                          float(alpha), float(gamma), float(eps))
+    return loss, out2[1].to(torch.int64)
 
 
 def _flatten(data) -> list:

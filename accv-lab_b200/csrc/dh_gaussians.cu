@@ -51,7 +51,33 @@ struct GsParams {
     int C, T, H, W, band_rows, bands_per_plane, bands_per_unit, units_per_plane;
     float factor;
     dh_status* status;
+    // LOSS mode (N3): draw_heatmap semantics (integer radii, sigma = (2r+1)/factor, one k) + fused Gaussian focal loss
+    const int32_t* radii_i;
+    float dh_k, alpha, gamma, eps;
+    double* partial_loss;    // [total_units]
+    long long* partial_pos;  // [total_units]
 };
+
+// LOSS mode: slot -> list entry with the draw_heatmap arithmetic (reference cuh:61-68,90-97):
+// window [x-r, x+r] x [y-r, y+r] clipped, inv = 1/(2 sigma^2) with sigma = (float)(2r+1)/factor. `slice_ids` = labels.
+__device__ __forceinline__ bool gs_make_dh(const GsParams& p, long long i, int cls, int uy0, int uy1, GObj& o) {
+    if (p.slice_ids != nullptr && p.slice_ids[i] != cls) return false;
+    const int r = p.radii_i[i];
+    if (r < 0 || r > 2048) return false;
+    const int2 cc = *reinterpret_cast<const int2*>(p.centers + 2 * i);
+    const long long X = cc.x, Y = cc.y;
+    if (Y + r < uy0 || Y - r > uy1 || X + r < 0 || X - r >= p.W || Y + r < 0 || Y - r >= p.H) return false;
+    o.x0 = (int)max(X - r, 0ll);
+    o.x1 = (int)min(X + r, (long long)p.W - 1);
+    o.y0 = (int)max(Y - r, 0ll);
+    o.y1 = (int)min(Y + r, (long long)p.H - 1);
+    const float sigma = __fdiv_rn((float)(2 * r + 1), p.factor);
+    o.inv = __fdiv_rn(1.0f, __fmul_rn(__fmul_rn(2.0f, sigma), sigma));
+    o.cx = (float)cc.x;
+    o.cy = (float)cc.y;
+    o.pad = 0;
+    return true;
+}
 
 // Slot -> list entry for plane class `cls`, culled against the unit's rows [uy0, uy1]. Window arithmetic of DrawGaussians.cc:34-51.
 __device__ __forceinline__ bool gs_make(const GsParams& p, long long i, int cls, int uy0, int uy1, bool count, GObj& o) {
@@ -91,7 +117,10 @@ constexpr int kGsZeroBytes = 8192;  // constant zero tile of the FRESH mode
 
 // FRESH (no input heatmap, PX == 4): runs of untouched bands leave as bulk stores (SASS UBLKCP) from a zero tile, issued
 // by the lanes of warp 0 in parallel — no LSU or register traffic for the bytes nobody draws on.
-template <int PX, bool INPLACE, bool FRESH>
+// LOSS (N3): nothing is drawn to memory. p.in is the prediction, the target value of every pixel is formed in registers
+// as in the FRESH renderer and consumed at once by the Gaussian focal loss (DH/docs/intro.rst:7-26); p.out (optional)
+// receives d loss / d pred; per-unit partial sums make the reduction order independent of the block scheduler.
+template <int PX, bool INPLACE, bool FRESH, bool LOSS = false>
 __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(const GsParams p) {
     __shared__ GObj s_list[kGsListCap];
     __shared__ int s_cnt;
@@ -124,13 +153,15 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
                                    : (long long)reinterpret_cast<const int*>(p.sizes)[sample];
         ns = ns < 0 ? 0 : (ns > p.T ? p.T : ns);
         const int n = (int)ns;
-        const bool class_ok = cls < p.num_k;
-        const float k = class_ok ? p.k_for_classes[cls] : 0.0f;
+        const bool class_ok = LOSS || cls < p.num_k;
+        const float k = LOSS ? p.dh_k : (class_ok ? p.k_for_classes[cls] : 0.0f);
+        double lsum = 0.0;  // LOSS: this thread's share of the unit
+        int npos = 0;
         const bool kneg = k < 0.0f;
         const bool count = (ug == 0 && cls == 0);
         const long long src = sample * p.T;
         const float* const in_plane = p.in ? p.in + plane * plane_elems : nullptr;
-        float* const out_plane = p.out + plane * plane_elems;
+        float* const out_plane = p.out ? p.out + plane * plane_elems : nullptr;
         const bool single = n <= kGsListCap;
 
         auto build = [&](int c0, bool do_count) {  // list of slots [c0, c0 + cap) (block-wide; ends with a barrier)
@@ -144,7 +175,11 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
             for (int base = c0; base < c1; base += kGsThreads) {
                 const int t = base + tid;
                 GObj o;
-                const bool pred = (t < c1) && class_ok && gs_make(p, src + t, cls, uy0, uy1, do_count, o);
+                bool pred = false;
+                if (t < c1 && class_ok) {
+                    if constexpr (LOSS) pred = gs_make_dh(p, src + t, cls, uy0, uy1, o);
+                    else pred = gs_make(p, src + t, cls, uy0, uy1, do_count, o);
+                }
                 const unsigned bal = __ballot_sync(0xffffffffu, pred);
                 if (bal) {
                     unsigned bits = 0u;
@@ -167,7 +202,7 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
         };
 
         int cnt = single ? build(0, count) : 0;
-        const unsigned mask = single ? s_mask : 0xffffffffu;
+        const unsigned mask = (single && !LOSS) ? s_mask : 0xffffffffu;  // LOSS: every pixel has a loss term
         if constexpr (FRESH) {
             if (tid < 32) {  // lane l starts the run of untouched bands that begins at band ub0 + l
                 const int nb = ub1 - ub0;
@@ -262,6 +297,45 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
                 } else {
                     v[0] = in_plane ? in_plane[idx] : 0.0f;
                 }
+                if constexpr (LOSS) {
+                    // v[] = prediction. Target of the pixel exactly as the FRESH renderer would have stored it, then
+                    //   target == 1: loss = -(1-p)^alpha log(p+eps);  else: loss = -p^alpha log(1-p+eps) (1-target)^gamma
+                    const bool std_exp = (p.alpha == 2.0f && p.gamma == 4.0f);
+                    float lq = 0.0f;
+#pragma unroll
+                    for (int j = 0; j < PX; ++j) {
+                        float tg = 0.0f;
+                        if (tq & (1u << j)) {
+                            const float val = __fmul_rn(expf(-best[q][j]), k);
+                            tg = (0.0f >= val) ? 0.0f : val;
+                        }
+                        const float pr = v[j], om = 1.0f - pr;
+                        float loss, g;
+                        if (tg == 1.0f) {
+                            const float den = pr + p.eps, lg = logf(den);
+                            const float pw = std_exp ? om * om : powf(om, p.alpha);
+                            const float pw1 = std_exp ? om : powf(om, p.alpha - 1.0f);
+                            loss = -lg * pw;
+                            g = p.alpha * pw1 * lg - pw / den;
+                            npos += 1;
+                        } else {
+                            const float den = om + p.eps, lg = logf(den);
+                            const float pa = std_exp ? pr * pr : powf(pr, p.alpha);
+                            const float pa1 = std_exp ? pr : powf(pr, p.alpha - 1.0f);
+                            const float ot = 1.0f - tg, ot2 = ot * ot;
+                            const float wgt = std_exp ? ot2 * ot2 : powf(ot, p.gamma);
+                            loss = -lg * pa * wgt;
+                            g = wgt * (pa / den - p.alpha * pa1 * lg);
+                        }
+                        lq += loss;
+                        v[j] = g;
+                    }
+                    lsum += (double)lq;
+                    if (p.out != nullptr) {
+                        if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
+                        else out_plane[idx] = v[0];
+                    }
+                } else {
                 if (tq != 0u) {  // one expf per pixel of a touched item, unconditionally: no per-pixel divergence
 #pragma unroll
                     for (int j = 0; j < PX; ++j) {
@@ -272,13 +346,93 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
                 }
                 if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
                 else out_plane[idx] = v[0];
+                }
             }
         }
       }  // bands of the unit
+        if constexpr (LOSS) {  // fixed-order reduction of the unit: lanes (xor tree) -> warps (in order) -> partial[u]
+            __shared__ double s_l[kGsThreads / 32];
+            __shared__ int s_n[kGsThreads / 32];
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) {
+                lsum += __shfl_xor_sync(0xffffffffu, lsum, d);
+                npos += __shfl_xor_sync(0xffffffffu, npos, d);
+            }
+            __syncthreads();  // previous unit's reader is done
+            if (lane == 0) {
+                s_l[tid >> 5] = lsum;
+                s_n[tid >> 5] = npos;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                double a = 0.0;
+                long long c = 0;
+#pragma unroll
+                for (int w = 0; w < kGsThreads / 32; ++w) {
+                    a += s_l[w];
+                    c += s_n[w];
+                }
+                p.partial_loss[u] = a;
+                p.partial_pos[u] = c;
+            }
+        }
     }
     if constexpr (FRESH) bulk_wait_read<0>();  // the zero tile must outlive every bulk read this thread issued
 }
 
+}  // namespace dh
+
+namespace dh {
+// Bands (<= kGsThreads*kGsItems*PX pixels of whole rows) and units (<= 32 bands, ~128 KB) of the pixel-owner kernels.
+static void gs_plan(GsParams& p, int sms, bool vec) {
+    const long long H = p.H, W = p.W;
+    const long long band_px = (long long)kGsThreads * kGsItems * (vec ? 4 : 1);
+    long long rows = band_px / W;
+    if (rows < 1) rows = 1;
+    if (rows > H) rows = H;
+    // small problems: more, shorter bands so that every SM gets work
+    while (rows > 1 && p.num_planes * ((H + rows - 1) / rows) < 2ll * sms) rows = (rows + 1) / 2;
+    p.band_rows = (int)rows;
+    p.bands_per_plane = (int)((H + rows - 1) / rows);
+    // unit = consecutive bands of one plane sharing one scan of the sample's slots (~128 KB of output, <= 32 bands);
+    // fewer bands per unit on small problems so that every SM still sees several units
+    long long bpu = (131072 / 4) / (rows * W);
+    if (bpu < 1) bpu = 1;
+    if (bpu > 32) bpu = 32;
+    if (bpu > p.bands_per_plane) bpu = p.bands_per_plane;
+    while (bpu > 1 && p.num_planes * ((p.bands_per_plane + bpu - 1) / bpu) < 8ll * sms) bpu = (bpu + 1) / 2;
+    p.units_per_plane = (int)((p.bands_per_plane + bpu - 1) / bpu);
+    p.bands_per_unit = (int)((p.bands_per_plane + p.units_per_plane - 1) / p.units_per_plane);
+    p.units_per_plane = (p.bands_per_plane + p.bands_per_unit - 1) / p.bands_per_unit;
+    p.total_units = p.num_planes * p.units_per_plane;
+}
+
+// Sum of the per-unit partials in a fixed order (one block): out2[0] = loss sum, out2[1] = number of target == 1 pixels.
+__global__ void __launch_bounds__(1024) focal_reduce_kernel(const double* __restrict__ pl, const long long* __restrict__ pp,
+                                                            long long n, double* __restrict__ out2) {
+    __shared__ double s_a[1024];
+    __shared__ long long s_c[1024];
+    double a = 0.0;
+    long long c = 0;
+    for (long long i = threadIdx.x; i < n; i += 1024) {
+        a += pl[i];
+        c += pp[i];
+    }
+    s_a[threadIdx.x] = a;
+    s_c[threadIdx.x] = c;
+    __syncthreads();
+    for (int d = 512; d > 0; d >>= 1) {
+        if ((int)threadIdx.x < d) {
+            s_a[threadIdx.x] += s_a[threadIdx.x + d];
+            s_c[threadIdx.x] += s_c[threadIdx.x + d];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        out2[0] = s_a[0];
+        out2[1] = (double)s_c[0];
+    }
+}
 }  // namespace dh
 
 extern "C" int dh_draw_gaussians(void* stream, const float* heatmap_in, float* heatmap_out, const int32_t* centers,
@@ -320,25 +474,7 @@ extern "C" int dh_draw_gaussians(void* stream, const float* heatmap_in, float* h
     p.status = status;
     const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heatmap_out) & 15u) == 0) &&
                      (heatmap_in == nullptr || (reinterpret_cast<uintptr_t>(heatmap_in) & 15u) == 0);
-    const long long band_px = (long long)dh::kGsThreads * dh::kGsItems * (vec ? 4 : 1);
-    long long rows = band_px / W;
-    if (rows < 1) rows = 1;
-    if (rows > H) rows = H;
-    // small problems: more, shorter bands so that every SM gets work
-    while (rows > 1 && p.num_planes * ((H + rows - 1) / rows) < 2ll * sms) rows = (rows + 1) / 2;
-    p.band_rows = (int)rows;
-    p.bands_per_plane = (int)((H + rows - 1) / rows);
-    // unit = consecutive bands of one plane sharing one scan of the sample's slots (~128 KB of output, <= 32 bands);
-    // fewer bands per unit on small problems so that every SM still sees several units
-    long long bpu = (131072 / 4) / (rows * W);
-    if (bpu < 1) bpu = 1;
-    if (bpu > 32) bpu = 32;
-    if (bpu > p.bands_per_plane) bpu = p.bands_per_plane;
-    while (bpu > 1 && p.num_planes * ((p.bands_per_plane + bpu - 1) / bpu) < 8ll * sms) bpu = (bpu + 1) / 2;
-    p.units_per_plane = (int)((p.bands_per_plane + bpu - 1) / bpu);
-    p.bands_per_unit = (int)((p.bands_per_plane + p.units_per_plane - 1) / p.units_per_plane);
-    p.units_per_plane = (p.bands_per_plane + p.bands_per_unit - 1) / p.bands_per_unit;
-    p.total_units = p.num_planes * p.units_per_plane;
+    dh::gs_plan(p, sms, vec);
     const long long g = p.total_units < 0x7fffffffll ? p.total_units : 0x7fffffffll;
     cudaStream_t s = (cudaStream_t)stream;
     if (vec) {
@@ -507,5 +643,86 @@ extern "C" int dh_boxes_to_gaussian_params(void* stream, const float* bboxes, co
     if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
     dh::converter_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(p);
     dh::count_launches(1);
+    return (int)cudaGetLastError();
+}
+
+// ================================================================================================================
+// N3: fused Gaussian-focal-loss consumer. The target heatmap of draw_heatmap_batched is never
+// written to HBM: every pixel's target is formed in registers (same arithmetic as the FRESH renderer) and consumed
+// by the loss of /root/reference/packages/draw_heatmap/docs/intro.rst:7-26 (the reference states the formula only;
+// it has no implementation -> PARITY UNPINNED). Traffic: 4 B/pixel read (+4 B/pixel written when the gradient is
+// requested) instead of 4 written + 4 read for the target plus the loss's own passes.
+static int focal_device(int& sms) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return DH_ERR_NO_DEVICE;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return DH_ERR_NO_DEVICE;
+    return DH_OK;
+}
+
+extern "C" size_t dh_focal_loss_workspace_bytes(int64_t B, int64_t C, int64_t H, int64_t W) {
+    if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return 16;
+    int sms = 0;
+    if (focal_device(sms) != DH_OK) sms = 148;
+    long long units = 0;
+    for (int vec = 0; vec < 2; ++vec) {
+        dh::GsParams p{};
+        p.num_planes = B * C;
+        p.H = (int)H;
+        p.W = (int)W;
+        dh::gs_plan(p, sms, vec != 0);
+        if (p.total_units > units) units = p.total_units;
+    }
+    return (size_t)units * 16 + 16;
+}
+
+extern "C" int dh_gaussian_focal_loss(void* stream, const float* pred, const int32_t* centers, const int32_t* radii,
+                                      const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t B,
+                                      int64_t T, int64_t C, int64_t H, int64_t W, float diameter_to_sigma_factor,
+                                      float k_scale, float alpha, float gamma, float eps, float* grad_pred,
+                                      double* loss_out2, void* workspace, size_t workspace_bytes) {
+    if (B < 0 || T < 0 || C < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
+    if (H < 1 || W < 1 || !(k_scale > 0.0f) || !(diameter_to_sigma_factor != 0.0f)) return DH_ERR_INVALID_ARGUMENT;
+    if (W > (1ll << 23) || H > (1ll << 23) || H * W >= (1ll << 31) || T > INT32_MAX || C > INT32_MAX)
+        return DH_ERR_UNSUPPORTED_SHAPE;
+    if (labels == nullptr) C = 1;
+    if (!loss_out2) return DH_ERR_INVALID_ARGUMENT;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (B == 0 || C == 0) return (int)cudaMemsetAsync(loss_out2, 0, 16, s);
+    if (!pred || !nums_targets || (T > 0 && (!centers || !radii))) return DH_ERR_INVALID_ARGUMENT;
+    if (reinterpret_cast<uintptr_t>(centers) & 7u) return DH_ERR_INVALID_ARGUMENT;
+    int sms = 0;
+    int st = focal_device(sms);
+    if (st != DH_OK) return st;
+    dh::GsParams p{};
+    p.in = pred;
+    p.out = grad_pred;
+    p.centers = centers;
+    p.radii_i = radii;
+    p.slice_ids = labels;
+    p.sizes = nums_targets;
+    p.sizes_i64 = nums_dtype == DH_SIZES_I64;
+    p.num_planes = B * C;
+    p.C = (int)C;
+    p.T = (int)T;
+    p.H = (int)H;
+    p.W = (int)W;
+    p.factor = diameter_to_sigma_factor;
+    p.dh_k = k_scale;
+    p.alpha = alpha;
+    p.gamma = gamma;
+    p.eps = eps;
+    const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(pred) & 15u) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(grad_pred) & 15u) == 0);
+    dh::gs_plan(p, sms, vec);
+    if (!workspace || workspace_bytes < (size_t)p.total_units * 16 + 16) return DH_ERR_WORKSPACE_TOO_SMALL;
+    if (reinterpret_cast<uintptr_t>(workspace) & 15u) return DH_ERR_INVALID_ARGUMENT;
+    p.partial_loss = (double*)workspace;
+    p.partial_pos = (long long*)((char*)workspace + (((size_t)p.total_units * 8 + 15) & ~(size_t)15));
+    const long long g = p.total_units < 0x7fffffffll ? p.total_units : 0x7fffffffll;
+    if (vec) dh::gaussians_kernel<4, false, false, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+    else dh::gaussians_kernel<1, false, false, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+    dh::focal_reduce_kernel<<<1, 1024, 0, s>>>(p.partial_loss, p.partial_pos, p.total_units, loss_out2);
+    dh::count_launches(2);
     return (int)cudaGetLastError();
 }

@@ -562,6 +562,35 @@ std::tuple<at::Tensor, at::Tensor> gaussian_radius(const at::Tensor& det_hw, dou
     return {ri, rf};
 }
 
+// ---- N3: fused Gaussian focal loss (DH/docs/intro.rst:7-26; no reference implementation) -----------------------
+std::tuple<at::Tensor, at::Tensor> gaussian_focal_loss(const at::Tensor& pred, const at::Tensor& centers,
+                                                       const at::Tensor& radii, const at::Tensor& nums_targets,
+                                                       const c10::optional<at::Tensor>& labels,
+                                                       float diameter_to_sigma_factor, float k_scale, double alpha,
+                                                       double gamma, double eps, bool want_grad) {
+    CHECK_INPUT(pred);
+    CHECK_DTYPE(pred, at::kFloat);
+    const bool classwise = labels.has_value();
+    batched_checks(pred, centers, radii, nums_targets, classwise ? &*labels : nullptr);
+    const int64_t B = pred.size(0), T = radii.size(1);
+    const int64_t C = classwise ? pred.size(1) : 1, H = pred.size(-2), W = pred.size(-1);
+    int tag = 0;
+    const void* sizes = sizes_ptr(nums_targets, tag);
+    c10::cuda::CUDAGuard guard(pred.device());
+    at::Tensor out2 = at::empty({2}, pred.options().dtype(at::kDouble));
+    at::Tensor grad = want_grad ? at::empty_like(pred) : at::Tensor();
+    const size_t wsb = dh_focal_loss_workspace_bytes(B, C, H, W);
+    at::Tensor ws = at::empty({(int64_t)wsb}, pred.options().dtype(at::kByte));
+    check_status(dh_gaussian_focal_loss(at::cuda::getCurrentCUDAStream().stream(), pred.data_ptr<float>(),
+                                        centers.data_ptr<int>(), radii.data_ptr<int>(), sizes, tag,
+                                        classwise ? labels->data_ptr<int>() : nullptr, B, T, C, H, W,
+                                        diameter_to_sigma_factor, k_scale, (float)alpha, (float)gamma, (float)eps,
+                                        want_grad ? grad.data_ptr<float>() : nullptr, out2.data_ptr<double>(),
+                                        ws.data_ptr(), wsb),
+                 "gaussian_focal_loss");
+    return {out2, grad};
+}
+
 void fill_probe(at::Tensor& t) {
     CHECK_INPUT(t);
     c10::cuda::CUDAGuard guard(t.device());
@@ -626,6 +655,12 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           pybind11::arg("min_radius"), pybind11::arg("max_radius"), pybind11::arg("min_fraction_area"));
     m.def("gaussian_radius", &gaussian_radius, "CenterNet/CenterPoint gaussian_radius(det_size, min_overlap) -> (int32 radii, float32 radii).",
           pybind11::arg("det_hw"), pybind11::arg("min_overlap"), pybind11::arg("variant"), pybind11::arg("min_radius"));
+    m.def("gaussian_focal_loss", &gaussian_focal_loss,
+          "Fused target rendering + Gaussian focal loss: (double[2] = {loss sum, #target==1}, d loss / d pred or undefined).",
+          pybind11::arg("pred"), pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"),
+          pybind11::arg("labels"), pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f,
+          pybind11::arg("alpha") = 2.0, pybind11::arg("gamma") = 4.0, pybind11::arg("eps") = 1e-12,
+          pybind11::arg("want_grad") = true);
     m.def("combine_data", &combine_data,
           "List of per-sample CUDA tensors [n_i, *data] -> (zero-padded tensor [B, T, *data], int64 sample sizes [B]); one launch.",
           pybind11::arg("data_list"), pybind11::arg("max_sample_size") = -1);

@@ -254,6 +254,24 @@ int dh_boxes_to_gaussian_params(void* stream, const float* bboxes, const float* 
 int dh_gaussian_radius(void* stream, const float* det_hw, double min_overlap, int variant, int32_t min_radius, int64_t n,
                        int32_t* radii_out, float* radii_float_out);
 
+/* ---- N3: fused Gaussian-focal-loss consumer (the step AFTER the renderer) ------------------------------
+ * loss(pred, target) of /root/reference/packages/draw_heatmap/docs/intro.rst:7-26 where `target` is the heatmap
+ * dh_draw_heatmap_batched(FRESH) would draw from the same RaggedBatch inputs — but the target is never written to
+ * HBM: each pixel's value is formed in registers and consumed at once.
+ *   target == 1 : loss = -(1 - pred)^alpha * log(pred + eps)
+ *   otherwise   : loss = -pred^alpha * log(1 - pred + eps) * (1 - target)^gamma          (eps as in mmdet, may be 0)
+ * pred float32 [B,(C),H,W] in (0,1); grad_pred (optional, same shape) receives d loss / d pred per pixel (unscaled);
+ * loss_out2 = DEVICE double[2]: { sum of the loss over all pixels, number of pixels with target == 1 } — summed in a
+ * fixed order (per-unit partials in `workspace`, then one block), so results are run-to-run identical.
+ * k_scale > 0; radii in [0, 2048] (others draw nothing). The reference documents the formula but has no implementation:
+ * PARITY UNPINNED (oracle = float64 numpy restatement, tests/test_focal_loss.py). Two launches. */
+size_t dh_focal_loss_workspace_bytes(int64_t batch_size, int64_t num_classes, int64_t height, int64_t width);
+int dh_gaussian_focal_loss(void* stream, const float* pred, const int32_t* centers, const int32_t* radii,
+                           const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t batch_size,
+                           int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
+                           float diameter_to_sigma_factor, float k_scale, float alpha, float gamma, float eps,
+                           float* grad_pred, double* loss_out2, void* workspace, size_t workspace_bytes);
+
 /* ---- measurement helper ---------------------------------------------------------------
  * Pure 128-bit-store fill of `bytes` bytes (multiple of 16, 16-byte aligned) with zeros using the same
  * store path and grid shape as the FRESH renderer: the write-only ceiling the renderer is compared to. */

@@ -366,3 +366,19 @@ def gaussian_radius_numpy(det_hw, min_overlap=0.5, variant="cornernet", min_radi
         r = np.minimum(np.minimum(r1, r2), r3)
     ri = np.where(np.isnan(r), -2**31, np.clip(np.trunc(np.nan_to_num(r)), -2**31, 2**31 - 1)).astype(np.int64)
     return np.maximum(ri, int(min_radius)).astype(np.int32), r.astype(np.float32)
+
+
+# ---- N3: Gaussian focal loss on the oracle's target — PARITY UNPINNED (formula only in the reference) -----------
+def gaussian_focal_loss_numpy(pred, target, alpha=2.0, gamma=4.0, eps=1e-12):
+    """/root/reference/packages/draw_heatmap/docs/intro.rst:7-26 (== mmdet gaussian_focal_loss, reduction 'sum'),
+    evaluated in float64 on fp32 inputs: returns (loss sum, number of target == 1 pixels, d loss / d pred as float64)."""
+    p = np.asarray(pred, np.float32).astype(np.float64)
+    t = np.asarray(target, np.float32).astype(np.float64)
+    pos = t == 1.0
+    with np.errstate(divide="ignore", invalid="ignore"):
+        lp, ln = np.log(p + eps), np.log(1 - p + eps)
+        w = (1 - t) ** gamma
+        loss = np.where(pos, -lp * (1 - p) ** alpha, -ln * p ** alpha * w)
+        grad = np.where(pos, alpha * (1 - p) ** (alpha - 1) * lp - (1 - p) ** alpha / (p + eps),
+                        w * (p ** alpha / (1 - p + eps) - alpha * p ** (alpha - 1) * ln))
+    return float(loss.sum()), int(pos.sum()), grad
