@@ -201,9 +201,9 @@ def gaussian_radius(det_size: torch.Tensor, min_overlap: float = 0.5, variant: s
 
 class _GaussianFocalLoss(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, pred, centers, radii, sizes, labels, factor, k_scale, alpha, gamma, eps):
+    def forward(ctx, pred, centers, radii, sizes, labels, factor, k_scale, alpha, gamma, eps, fast_math):
         out2, grad = _ext.gaussian_focal_loss(pred.contiguous(), centers, radii, sizes, labels, factor, k_scale, alpha, gamma, eps,
-                                              pred.requires_grad)
+                                              pred.requires_grad, fast_math)
         if pred.requires_grad:
             ctx.save_for_backward(grad)
         ctx.mark_non_differentiable(out2)
@@ -212,11 +212,11 @@ class _GaussianFocalLoss(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_loss, _g_out2):
         (grad,) = ctx.saved_tensors
-        return (grad * g_loss,) + (None,) * 9
+        return (grad * g_loss,) + (None,) * 10
 
 
 def gaussian_focal_loss(pred: torch.Tensor, centers, radii, diameter_to_sigma_factor: float = 6.0, k_scale: float = 1.0,
-                        labels=None, alpha: float = 2.0, gamma: float = 4.0, eps: float = 1e-12):
+                        labels=None, alpha: float = 2.0, gamma: float = 4.0, eps: float = 1e-12, fast_math: bool = False):
     """Fused consumer of the heatmap: ``sum(GaussianFocalLoss(pred, target))`` where ``target`` is
     the heatmap ``draw_heatmap_batched`` would draw from ``centers`` / ``radii`` (/ ``labels``) into zeros — without
     ever writing the target to memory (formula: reference docs/intro.rst:7-26; mmdet's ``gaussian_focal_loss`` with
@@ -228,7 +228,7 @@ def gaussian_focal_loss(pred: torch.Tensor, centers, radii, diameter_to_sigma_fa
     if sizes is None:
         sizes = torch.full((r_t.shape[0],), r_t.shape[1], dtype=torch.int64, device=r_t.device)
     loss, out2 = _GaussianFocalLoss.apply(pred, c_t, r_t, sizes, l_t, float(diameter_to_sigma_factor), float(k_scale),
-                                          float(alpha), float(gamma), float(eps))
+                                          float(alpha), float(gamma), float(eps), bool(fast_math))
     return loss, out2[1].to(torch.int64)
 
 

@@ -54,6 +54,7 @@ struct GsParams {
     // LOSS mode (N3): draw_heatmap semantics (integer radii, sigma = (2r+1)/factor, one k) + fused Gaussian focal loss
     const int32_t* radii_i;
     float dh_k, alpha, gamma, eps;
+    int fast;  // LOSS: MUFU-based log / division (__logf, __fdividef) instead of the IEEE-accurate routines
     double* partial_loss;    // [total_units]
     long long* partial_pos;  // [total_units]
 };
@@ -120,8 +121,14 @@ constexpr int kGsZeroBytes = 8192;  // constant zero tile of the FRESH mode
 // LOSS (N3): nothing is drawn to memory. p.in is the prediction, the target value of every pixel is formed in registers
 // as in the FRESH renderer and consumed at once by the Gaussian focal loss (DH/docs/intro.rst:7-26); p.out (optional)
 // receives d loss / d pred; per-unit partial sums make the reduction order independent of the block scheduler.
-template <int PX, bool INPLACE, bool FRESH, bool LOSS = false>
-__global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(const GsParams p) {
+// LOSS_MODE: 0 = renderer; 1 = alpha 2 / gamma 4, IEEE-accurate log and division; 2 = same through the special-function
+// unit (__logf, __fdividef); 3 = general exponents (powf). Compile-time so that each variant's code stays small: a
+// run-time switch tripled the unrolled loss body and the kernel stalled on instruction fetch (ncu: no_instruction 2.8).
+template <int PX, bool INPLACE, bool FRESH, int LOSS_MODE = 0>
+__global__ void __launch_bounds__(kGsThreads, LOSS_MODE ? 2 : (PX == 4 ? 3 : 4)) gaussians_kernel(const GsParams p) {
+    constexpr bool LOSS = LOSS_MODE != 0;
+    constexpr bool std_exp = LOSS_MODE == 1 || LOSS_MODE == 2;
+    constexpr bool FAST = LOSS_MODE == 2;
     __shared__ GObj s_list[kGsListCap];
     __shared__ int s_cnt;
     __shared__ __align__(128) float4 s_zero[FRESH ? kGsZeroBytes / 16 : 1];
@@ -258,6 +265,23 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
 #pragma unroll
                 for (int j = 0; j < PX; ++j) best[q][j] = INF;
             }
+            // input pixels of all items up front: the loads are in flight while the objects are evaluated (issued one
+            // item at a time next to their stores they serialise on the memory latency: out may alias in)
+            float vin[kGsItems][PX];
+#pragma unroll
+            for (int q = 0; q < kGsItems; ++q) {
+#pragma unroll
+                for (int j = 0; j < PX; ++j) vin[q][j] = 0.0f;
+                if (in_plane != nullptr && rows[q] >= 0) {
+                    const int idx = rows[q] * p.W + cols[q];
+                    if constexpr (PX == 4) {
+                        const float4 a = __ldg(reinterpret_cast<const float4*>(in_plane + idx));
+                        vin[q][0] = a.x; vin[q][1] = a.y; vin[q][2] = a.z; vin[q][3] = a.w;
+                    } else {
+                        vin[q][0] = __ldg(in_plane + idx);
+                    }
+                }
+            }
             for (int c0 = 0; c0 < (single ? 1 : n); c0 += kGsListCap) {
                 if (!single) cnt = build(c0, count && item0 == 0 && b == ub0);
                 for (int e = 0; e < cnt; ++e) {
@@ -291,16 +315,11 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
                 if (INPLACE && tq == 0u) continue;
                 const int idx = rows[q] * p.W + cols[q];  // H*W < 2^31
                 float v[PX];
-                if constexpr (PX == 4) {
-                    const float4 a = in_plane ? *reinterpret_cast<const float4*>(in_plane + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-                } else {
-                    v[0] = in_plane ? in_plane[idx] : 0.0f;
-                }
+#pragma unroll
+                for (int j = 0; j < PX; ++j) v[j] = vin[q][j];
                 if constexpr (LOSS) {
                     // v[] = prediction. Target of the pixel exactly as the FRESH renderer would have stored it, then
                     //   target == 1: loss = -(1-p)^alpha log(p+eps);  else: loss = -p^alpha log(1-p+eps) (1-target)^gamma
-                    const bool std_exp = (p.alpha == 2.0f && p.gamma == 4.0f);
                     float lq = 0.0f;
 #pragma unroll
                     for (int j = 0; j < PX; ++j) {
@@ -312,20 +331,20 @@ __global__ void __launch_bounds__(kGsThreads, PX == 4 ? 3 : 4) gaussians_kernel(
                         const float pr = v[j], om = 1.0f - pr;
                         float loss, g;
                         if (tg == 1.0f) {
-                            const float den = pr + p.eps, lg = logf(den);
+                            const float den = pr + p.eps, lg = FAST ? __logf(den) : logf(den);
                             const float pw = std_exp ? om * om : powf(om, p.alpha);
                             const float pw1 = std_exp ? om : powf(om, p.alpha - 1.0f);
                             loss = -lg * pw;
-                            g = p.alpha * pw1 * lg - pw / den;
+                            g = p.alpha * pw1 * lg - (FAST ? __fdividef(pw, den) : pw / den);
                             npos += 1;
                         } else {
-                            const float den = om + p.eps, lg = logf(den);
+                            const float den = om + p.eps, lg = FAST ? __logf(den) : logf(den);
                             const float pa = std_exp ? pr * pr : powf(pr, p.alpha);
                             const float pa1 = std_exp ? pr : powf(pr, p.alpha - 1.0f);
                             const float ot = 1.0f - tg, ot2 = ot * ot;
                             const float wgt = std_exp ? ot2 * ot2 : powf(ot, p.gamma);
                             loss = -lg * pa * wgt;
-                            g = wgt * (pa / den - p.alpha * pa1 * lg);
+                            g = wgt * ((FAST ? __fdividef(pa, den) : pa / den) - p.alpha * pa1 * lg);
                         }
                         lq += loss;
                         v[j] = g;
@@ -678,8 +697,9 @@ extern "C" size_t dh_focal_loss_workspace_bytes(int64_t B, int64_t C, int64_t H,
 extern "C" int dh_gaussian_focal_loss(void* stream, const float* pred, const int32_t* centers, const int32_t* radii,
                                       const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t B,
                                       int64_t T, int64_t C, int64_t H, int64_t W, float diameter_to_sigma_factor,
-                                      float k_scale, float alpha, float gamma, float eps, float* grad_pred,
-                                      double* loss_out2, void* workspace, size_t workspace_bytes) {
+                                      float k_scale, float alpha, float gamma, float eps, int fast_math,
+                                      float* grad_pred, double* loss_out2, void* workspace,
+                                      size_t workspace_bytes) {
     if (B < 0 || T < 0 || C < 0) return DH_ERR_INVALID_ARGUMENT;
     if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
     if (H < 1 || W < 1 || !(k_scale > 0.0f) || !(diameter_to_sigma_factor != 0.0f)) return DH_ERR_INVALID_ARGUMENT;
@@ -712,6 +732,7 @@ extern "C" int dh_gaussian_focal_loss(void* stream, const float* pred, const int
     p.alpha = alpha;
     p.gamma = gamma;
     p.eps = eps;
+    p.fast = fast_math != 0;
     const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(pred) & 15u) == 0) &&
                      ((reinterpret_cast<uintptr_t>(grad_pred) & 15u) == 0);
     dh::gs_plan(p, sms, vec);
@@ -720,8 +741,16 @@ extern "C" int dh_gaussian_focal_loss(void* stream, const float* pred, const int
     p.partial_loss = (double*)workspace;
     p.partial_pos = (long long*)((char*)workspace + (((size_t)p.total_units * 8 + 15) & ~(size_t)15));
     const long long g = p.total_units < 0x7fffffffll ? p.total_units : 0x7fffffffll;
-    if (vec) dh::gaussians_kernel<4, false, false, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);
-    else dh::gaussians_kernel<1, false, false, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+    const int mode = (alpha == 2.0f && gamma == 4.0f) ? (fast_math ? 2 : 1) : 3;
+    if (vec) {
+        if (mode == 1) dh::gaussians_kernel<4, false, false, 1><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else if (mode == 2) dh::gaussians_kernel<4, false, false, 2><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else dh::gaussians_kernel<4, false, false, 3><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+    } else {
+        if (mode == 1) dh::gaussians_kernel<1, false, false, 1><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else if (mode == 2) dh::gaussians_kernel<1, false, false, 2><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else dh::gaussians_kernel<1, false, false, 3><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+    }
     dh::focal_reduce_kernel<<<1, 1024, 0, s>>>(p.partial_loss, p.partial_pos, p.total_units, loss_out2);
     dh::count_launches(2);
     return (int)cudaGetLastError();

@@ -567,7 +567,7 @@ std::tuple<at::Tensor, at::Tensor> gaussian_focal_loss(const at::Tensor& pred, c
                                                        const at::Tensor& radii, const at::Tensor& nums_targets,
                                                        const c10::optional<at::Tensor>& labels,
                                                        float diameter_to_sigma_factor, float k_scale, double alpha,
-                                                       double gamma, double eps, bool want_grad) {
+                                                       double gamma, double eps, bool want_grad, bool fast_math) {
     CHECK_INPUT(pred);
     CHECK_DTYPE(pred, at::kFloat);
     const bool classwise = labels.has_value();
@@ -585,7 +585,7 @@ std::tuple<at::Tensor, at::Tensor> gaussian_focal_loss(const at::Tensor& pred, c
                                         centers.data_ptr<int>(), radii.data_ptr<int>(), sizes, tag,
                                         classwise ? labels->data_ptr<int>() : nullptr, B, T, C, H, W,
                                         diameter_to_sigma_factor, k_scale, (float)alpha, (float)gamma, (float)eps,
-                                        want_grad ? grad.data_ptr<float>() : nullptr, out2.data_ptr<double>(),
+                                        fast_math ? 1 : 0, want_grad ? grad.data_ptr<float>() : nullptr, out2.data_ptr<double>(),
                                         ws.data_ptr(), wsb),
                  "gaussian_focal_loss");
     return {out2, grad};
@@ -660,7 +660,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           pybind11::arg("pred"), pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"),
           pybind11::arg("labels"), pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f,
           pybind11::arg("alpha") = 2.0, pybind11::arg("gamma") = 4.0, pybind11::arg("eps") = 1e-12,
-          pybind11::arg("want_grad") = true);
+          pybind11::arg("want_grad") = true, pybind11::arg("fast_math") = false);
     m.def("combine_data", &combine_data,
           "List of per-sample CUDA tensors [n_i, *data] -> (zero-padded tensor [B, T, *data], int64 sample sizes [B]); one launch.",
           pybind11::arg("data_list"), pybind11::arg("max_sample_size") = -1);

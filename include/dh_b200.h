@@ -263,6 +263,8 @@ int dh_gaussian_radius(void* stream, const float* det_hw, double min_overlap, in
  * pred float32 [B,(C),H,W] in (0,1); grad_pred (optional, same shape) receives d loss / d pred per pixel (unscaled);
  * loss_out2 = DEVICE double[2]: { sum of the loss over all pixels, number of pixels with target == 1 } — summed in a
  * fixed order (per-unit partials in `workspace`, then one block), so results are run-to-run identical.
+ * fast_math != 0 (alpha = 2, gamma = 4 only): log and division through the special-function unit (__logf,
+ * __fdividef; ~1e-6 relative on the sum).
  * k_scale > 0; radii in [0, 2048] (others draw nothing). The reference documents the formula but has no implementation:
  * PARITY UNPINNED (oracle = float64 numpy restatement, tests/test_focal_loss.py). Two launches. */
 size_t dh_focal_loss_workspace_bytes(int64_t batch_size, int64_t num_classes, int64_t height, int64_t width);
@@ -270,7 +272,8 @@ int dh_gaussian_focal_loss(void* stream, const float* pred, const int32_t* cente
                            const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t batch_size,
                            int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
                            float diameter_to_sigma_factor, float k_scale, float alpha, float gamma, float eps,
-                           float* grad_pred, double* loss_out2, void* workspace, size_t workspace_bytes);
+                           int fast_math, float* grad_pred, double* loss_out2, void* workspace,
+                           size_t workspace_bytes);
 
 /* ---- measurement helper ---------------------------------------------------------------
  * Pure 128-bit-store fill of `bytes` bytes (multiple of 16, 16-byte aligned) with zeros using the same

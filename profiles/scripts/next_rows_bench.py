@@ -98,3 +98,37 @@ for name, B in (("cfg2", None), ("cfg3", None), ("cfg5", 384)):
          "gpu_accumulate_GBps_rw": 2 * out_bytes / t_a / 1e6, "cpu_reference_arithmetic_1thread_ms_scaled": t_cpu,
          "cpu_sample": f"first {nb} samples, scaled to {w.B}", "speedup_fresh_vs_cpu_1thread": t_cpu / t_f}
     print(json.dumps(r), flush=True)
+
+# ------------------------------------------------------------------ N3
+for name, B in (("cfg3", None), ("cfg5", 384)):
+    w = workloads.make(name, B=B); cfg = w.cfg
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    sizes, lab = d(w.sizes), d(w.labels)
+    ci, ri = b200.radius_center(d(w.centers_f), d(w.bboxes_f), cfg.osf)
+    rb = lambda t: b200.RaggedBatch(t, sample_sizes=sizes)
+    shape = (w.B, cfg.C, cfg.H, cfg.W)
+    pred = torch.rand(shape, device=dev) * 0.98 + 0.01
+    px_bytes = int(np.prod(shape)) * 4
+    def fused_fwd():
+        b200.gaussian_focal_loss(pred, rb(ci), rb(ri), 6.0, 1.0, labels=rb(lab))
+    def fused_fwd_fast():
+        b200.gaussian_focal_loss(pred, rb(ci), rb(ri), 6.0, 1.0, labels=rb(lab), fast_math=True)
+    pg = pred.clone().requires_grad_(True)
+    def fused_fwd_bwd():
+        pg.grad = None
+        loss, npos = b200.gaussian_focal_loss(pg, rb(ci), rb(ri), 6.0, 1.0, labels=rb(lab))
+        loss.backward()
+    tgt_buf = torch.empty(shape, device=dev)
+    def unfused_fwd_bwd():
+        pg.grad = None
+        t = b200.render_heatmap_batched(rb(ci), rb(ri), labels=rb(lab), out=tgt_buf)          # our fast renderer
+        pos = t.eq(1)
+        l = torch.where(pos, -(pg + 1e-12).log() * (1 - pg) ** 2, -(1 - pg + 1e-12).log() * pg ** 2 * (1 - t) ** 4).sum()
+        l.backward()
+    reps = 10
+    r = {"row": "N3", "config": name, "samples": w.B, "planes": w.planes, "pred_MB": px_bytes / 1e6,
+         "fused_forward_ms": ev(fused_fwd, reps), "fused_forward_fast_math_ms": ev(fused_fwd_fast, reps), "fused_forward_backward_ms": ev(fused_fwd_bwd, reps),
+         "unfused_render_plus_torch_loss_fwd_bwd_ms": ev(unfused_fwd_bwd, 3)}
+    r["fused_forward_GBps_read"] = px_bytes / r["fused_forward_ms"] / 1e6
+    r["speedup_fwd_bwd"] = r["unfused_render_plus_torch_loss_fwd_bwd_ms"] / r["fused_forward_backward_ms"]
+    print(json.dumps(r), flush=True)

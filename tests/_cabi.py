@@ -49,8 +49,8 @@ SIGNATURES = {
                                          ctypes.c_double, _f, _f, ctypes.c_double, _p, _p, _p, _p, _p, _p, _p]),
     "dh_gaussian_radius": (_i, [_p, _p, ctypes.c_double, _i, ctypes.c_int32, _i64, _p, _p]),
     "dh_focal_loss_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64]),
-    "dh_gaussian_focal_loss": (_i, [_p, _p, _p, _p, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f, _f, _f, _f, _p, _p,
-                                    _p, _sz]),
+    "dh_gaussian_focal_loss": (_i, [_p, _p, _p, _p, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f, _f, _f, _f, _i, _p,
+                                    _p, _p, _sz]),
     "dh_fill_probe": (_i, [_p, _p, _sz]),
     "dh_expf_probe": (_i, [_p, ctypes.c_uint32, _i64, _p]),
 }

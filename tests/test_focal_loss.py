@@ -25,8 +25,8 @@ def test_argument_validation_needs_no_device(cabi):
 
     one = ctypes.c_void_p(16)
     f = cabi.dh_gaussian_focal_loss
-    assert f(None, one, one, one, one, 0, None, 1, 1, 1, 8, 8, 6.0, 0.0, 2.0, 4.0, 0.0, None, one, one, 1 << 20) == _cabi.DH_ERR_INVALID_ARGUMENT
-    assert f(None, one, one, one, one, 0, None, 1, 1, 1, 8, 8, 6.0, 1.0, 2.0, 4.0, 0.0, None, None, one, 1 << 20) == _cabi.DH_ERR_INVALID_ARGUMENT
+    assert f(None, one, one, one, one, 0, None, 1, 1, 1, 8, 8, 6.0, 0.0, 2.0, 4.0, 0.0, 0, None, one, one, 1 << 20) == _cabi.DH_ERR_INVALID_ARGUMENT
+    assert f(None, one, one, one, one, 0, None, 1, 1, 1, 8, 8, 6.0, 1.0, 2.0, 4.0, 0.0, 0, None, None, one, 1 << 20) == _cabi.DH_ERR_INVALID_ARGUMENT
     assert cabi.dh_focal_loss_workspace_bytes(16, 10, 180, 180) >= 16 * 160 + 16
 
 
@@ -57,6 +57,10 @@ def test_fused_loss_vs_oracle(cuda_dev, oracle, name, nb, with_labels):
     (loss / max(int(npos), 1)).backward()
     g = p.grad.cpu().numpy().astype(np.float64) * max(want_pos, 1)
     assert np.all(np.abs(g - want_grad) <= 1e-5 * np.abs(want_grad) + 1e-6)
+    # special-function-unit variant: same positives, loss within 1e-5 relative
+    loss_f, npos_f = b200.gaussian_focal_loss(dev(pred), rb(ci), rb(ri), 6.0, 1.0, labels=rb(w.labels) if with_labels else None,
+                                              fast_math=True)
+    assert int(npos_f) == want_pos and abs(float(loss_f) - want_loss) <= 1e-5 * abs(want_loss) + 1e-6
     # run-to-run identical (fixed-order reduction)
     loss2, _ = b200.gaussian_focal_loss(dev(pred), rb(ci), rb(ri), 6.0, 1.0, labels=rb(w.labels) if with_labels else None)
     assert float(loss2.detach()) == float(loss.detach())
