@@ -17,6 +17,7 @@
 // stores (input copied / zero-init fused for untouched pixels; in-place calls write touched groups only).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "dh_b200.h"
 #include "dh_ptx.cuh"
@@ -51,6 +52,7 @@ struct GsParams {
     int C, T, H, W, band_rows, bands_per_plane, bands_per_unit, units_per_plane;
     float factor;
     dh_status* status;
+    const int* gate;  // optional: the whole grid returns at once when *gate == 0 (fix-up pass with nothing to fix)
     // LOSS mode (N3): draw_heatmap semantics (integer radii, sigma = (2r+1)/factor, one k) + fused Gaussian focal loss
     const int32_t* radii_i;
     float dh_k, alpha, gamma, eps;
@@ -127,6 +129,7 @@ constexpr int kGsZeroBytes = 8192;  // constant zero tile of the FRESH mode
 template <int PX, bool INPLACE, bool FRESH, int LOSS_MODE = 0>
 __global__ void __launch_bounds__(kGsThreads, LOSS_MODE ? 2 : (PX == 4 ? 3 : 4)) gaussians_kernel(const GsParams p) {
     constexpr bool LOSS = LOSS_MODE != 0;
+    if (p.gate != nullptr && *p.gate == 0) return;
     constexpr bool std_exp = LOSS_MODE == 1 || LOSS_MODE == 2;
     constexpr bool FAST = LOSS_MODE == 2;
     __shared__ GObj s_list[kGsListCap];
@@ -454,11 +457,69 @@ __global__ void __launch_bounds__(1024) focal_reduce_kernel(const double* __rest
 }
 }  // namespace dh
 
+namespace dh {
+
+static const bool g_gs_force_fast = getenv("DH_GS_FORCE_FAST") != nullptr;  // tests: take the fast path at any size
+
+int launch_weighted_fresh(cudaStream_t stream, float* heat, const int32_t* centers, const int32_t* radii_eff,
+                          const float* weights, const int32_t* labels, const void* sizes, int sizes_i64,
+                          const float* k_classes, long long B, long long T, long long C, long long H, long long W);  // dh_kernels.cu
+
+// FRESH fast path, pass 0: classify every slot. An object whose reference window is the symmetric integer square
+// [c - R, c + R]^2 (always the case unless the fp32 add centre -/+ radius rounds across an integer, the radius is
+// negative or sigma^2 under/overflows) is handed to the main renderer (groups_kernel, SRC_WEIGHTED) as (R, 1/(2 sigma^2));
+// the rest is flagged for the exact pixel-owner kernel, which then runs in place over the flagged objects only.
+__global__ void __launch_bounds__(256) gs_prepare_kernel(const GsParams p, long long B, int32_t* __restrict__ radii_eff,
+                                                         float* __restrict__ weights, uint8_t* __restrict__ special,
+                                                         int* __restrict__ n_special) {
+    const long long total = B * p.T;
+    int mine = 0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long b = i / p.T, t = i - b * p.T;
+        const long long n = p.sizes_i64 ? reinterpret_cast<const long long*>(p.sizes)[b] : (long long)reinterpret_cast<const int*>(p.sizes)[b];
+        int reff = -1;
+        float w = 0.0f;
+        bool sp = false;
+        const int cls = p.slice_ids ? p.slice_ids[i] : 0;
+        if (t < n && (p.active == nullptr || p.active[i] != 0) && cls >= 0 && cls < p.C && cls < p.num_k) {
+            const float r = p.radii[i];
+            const int2 cc = *reinterpret_cast<const int2*>(p.centers + 2 * i);
+            const float fx = (float)cc.x, fy = (float)cc.y;
+            if (fabsf(r) <= kGsMaxRadius && fabsf(fx) <= 16777216.0f && fabsf(fy) <= 16777216.0f) {
+                const int el = cc.x - (int)floorf(__fsub_rn(fx, r)), er = (int)ceilf(__fadd_rn(fx, r)) - cc.x;
+                const int et = cc.y - (int)floorf(__fsub_rn(fy, r)), eb = (int)ceilf(__fadd_rn(fy, r)) - cc.y;
+                const float sigma = __fmul_rn(r, p.factor);
+                const float inv = __fdiv_rn(1.0f, __fmul_rn(__fmul_rn(2.0f, sigma), sigma));
+                if (el == er && et == eb && el == et && el >= 0 && inv > 0.0f && inv < __int_as_float(0x7f800000)) {
+                    reff = el;
+                    w = inv;
+                } else {
+                    sp = true;
+                }
+            }
+        }
+        radii_eff[i] = reff;
+        weights[i] = w;
+        special[i] = sp ? 1 : 0;
+        mine += sp ? 1 : 0;
+    }
+    mine = __reduce_add_sync(0xffffffffu, mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(n_special, mine);
+}
+
+}  // namespace dh
+
+extern "C" size_t dh_draw_gaussians_workspace_bytes(int64_t B, int64_t T) {
+    if (B <= 0 || T <= 0) return 16;
+    const size_t n = (size_t)B * (size_t)T;
+    return ((n * 4 + 15) & ~(size_t)15) * 2 + ((n + 15) & ~(size_t)15) + 16;
+}
+
 extern "C" int dh_draw_gaussians(void* stream, const float* heatmap_in, float* heatmap_out, const int32_t* centers,
                                  const float* radii, const int32_t* slice_ids, const uint8_t* active,
                                  const void* nums_targets, int nums_dtype, const float* k_for_classes, int64_t num_k,
                                  int64_t B, int64_t T, int64_t C, int64_t H, int64_t W, float radius_to_sigma_factor,
-                                 dh_status* status) {
+                                 dh_status* status, void* workspace, size_t workspace_bytes) {
     if (B < 0 || T < 0 || C < 0 || num_k < 0) return DH_ERR_INVALID_ARGUMENT;
     if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
     if (H < 1 || W < 1) return DH_ERR_INVALID_ARGUMENT;
@@ -493,9 +554,41 @@ extern "C" int dh_draw_gaussians(void* stream, const float* heatmap_in, float* h
     p.status = status;
     const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heatmap_out) & 15u) == 0) &&
                      (heatmap_in == nullptr || (reinterpret_cast<uintptr_t>(heatmap_in) & 15u) == 0);
+    cudaStream_t s = (cudaStream_t)stream;
+    // FRESH fast path (needs the caller's workspace): classify -> main renderer for the symmetric objects (bulk-store /
+    // cluster-launch-control path of groups_kernel) -> exact kernel in place over the few flagged objects, if any.
+    // (three launches: only worth it when the output is large — measured break-even ~200 MB on B200)
+    const bool big = (double)B * (double)C * (double)H * (double)W * 4.0 >= (double)(256ll << 20) || dh::g_gs_force_fast;
+    if (big && heatmap_in == nullptr && vec && T > 0 && workspace != nullptr && status == nullptr &&
+        workspace_bytes >= dh_draw_gaussians_workspace_bytes(B, T) && (reinterpret_cast<uintptr_t>(workspace) & 15u) == 0) {
+        const size_t n = (size_t)B * (size_t)T, a4 = (n * 4 + 15) & ~(size_t)15, a1 = (n + 15) & ~(size_t)15;
+        char* ws = (char*)workspace;
+        int32_t* radii_eff = (int32_t*)ws;
+        float* weights = (float*)(ws + a4);
+        uint8_t* special = (uint8_t*)(ws + 2 * a4);
+        int* n_special = (int*)(ws + 2 * a4 + a1);
+        cudaError_t e = cudaMemsetAsync(n_special, 0, 4, s);
+        if (e != cudaSuccess) return (int)e;
+        long long pb = ((long long)n + 255) / 256;
+        if (pb > (long long)sms * 8) pb = (long long)sms * 8;
+        dh::gs_prepare_kernel<<<(int)pb, 256, 0, s>>>(p, B, radii_eff, weights, special, n_special);
+        const int st = dh::launch_weighted_fresh(s, heatmap_out, centers, radii_eff, weights, slice_ids, nums_targets,
+                                                 p.sizes_i64, k_for_classes, B, T, C, H, W);
+        if (st == DH_OK) {
+            dh::GsParams q = p;  // exact kernel, in place, flagged objects only; returns at once when there are none
+            q.in = heatmap_out;
+            q.active = special;
+            q.gate = n_special;
+            dh::gs_plan(q, sms, vec);
+            const long long g2 = q.total_units < 0x7fffffffll ? q.total_units : 0x7fffffffll;
+            dh::gaussians_kernel<4, true, false><<<(int)g2, dh::kGsThreads, 0, s>>>(q);
+            dh::count_launches(2);  // + the groups_kernel counted by its launcher
+            return (int)cudaGetLastError();
+        }
+        if (st != DH_ERR_UNSUPPORTED_SHAPE) return st;
+    }
     dh::gs_plan(p, sms, vec);
     const long long g = p.total_units < 0x7fffffffll ? p.total_units : 0x7fffffffll;
-    cudaStream_t s = (cudaStream_t)stream;
     if (vec) {
         if (inplace) dh::gaussians_kernel<4, true, false><<<(int)g, dh::kGsThreads, 0, s>>>(p);
         else if (heatmap_in == nullptr) dh::gaussians_kernel<4, false, true><<<(int)g, dh::kGsThreads, 0, s>>>(p);

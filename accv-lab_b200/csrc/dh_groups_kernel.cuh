@@ -266,9 +266,10 @@ struct UnitSrc {
 // lane's own entry when the unit has <= 32 objects (`small`). FRESH: the group leaves with one bulk store.
 template <bool ACCUM, int SRC, bool DIGEST>
 __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& ws, float* __restrict__ plane_ptr,
-                                             long long plane_index0, int y0, int nrows, int W, int G, bool kneg, int lane,
+                                             long long plane_index0, int y0, int nrows, int W, int G, bool kneg, float kk, int lane,
                                              bool small, const ObjI& mine, const ObjI* __restrict__ list, int ucnt,
                                              const UnitSrc& us, Digest& dg) {
+    const float k = (SRC == SRC_WEIGHTED) ? kk : p.k;  // per-class peak only in the weighted mode
     const int y1 = y0 + nrows - 1;
     float* const gdst = plane_ptr + (long long)y0 * W;
     const long long gindex = plane_index0 + (long long)y0 * W;
@@ -297,7 +298,7 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
                 const unsigned rest = bal & (bal - 1u);
                 const int sb = rest ? __ffs(rest) - 1 : sa;
                 const ObjI A = shfl_obj(mine, sa), B = shfl_obj(mine, sb);
-                sparse_group<ACCUM, DIGEST>(buf, gdst, gindex, y0, nrows, W, A, B, rest != 0u, kneg, p.k, lane, ux0, ux1, dg);
+                sparse_group<ACCUM, DIGEST>(buf, gdst, gindex, y0, nrows, W, A, B, rest != 0u, kneg, k, lane, ux0, ux1, dg);
             }
         } else {
             finish = true;
@@ -327,6 +328,9 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
                     int x, y, r;
                     if (load_slot<SRC>(p, us.src_base, e, us.cls, us.plane, false, x, y, r))
                         hit = make_obji(x, y, r, p.factor, y0, y1 + 1, W, o, nullptr, false);
+                    if constexpr (SRC == SRC_WEIGHTED) {
+                        if (hit) o.w = __ldg(p.weights + us.src_base + e);
+                    }
                 }
             }
             unsigned bal = __ballot_sync(0xffffffffu, hit);
@@ -341,7 +345,7 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
     }
     if (finish && ux1 >= ux0) {
         for (int rr = 0; rr < nrows; ++rr)
-            finish_row<ACCUM, DIGEST>(buf + rr * W, gdst + (long long)rr * W, gindex + (long long)rr * W, ux0, ux1, kneg, p.k,
+            finish_row<ACCUM, DIGEST>(buf + rr * W, gdst + (long long)rr * W, gindex + (long long)rr * W, ux0, ux1, kneg, k,
                                       lane, dg);
     }
     if constexpr (!ACCUM) {
@@ -382,7 +386,7 @@ __device__ __forceinline__ int unit_header(const RenderParams& p, long long u, i
     }
     uy0 = ug * bpu * G;
     uy1 = min(uy0 + bpu * G, p.H);
-    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_WEIGHTED) {
         const long long sample = us.plane / p.C;
         us.cls = (int)(us.plane - sample * p.C);
         long long ns = p.sizes_i64 ? __ldg(reinterpret_cast<const long long*>(p.sizes) + sample)
@@ -413,7 +417,26 @@ template <int SRC>
 __device__ __forceinline__ bool scan_slot(const RenderParams& p, const UnitSrc& us, int t, int nscan, int uy0, int uy1, int W,
                                           bool count_skips, ObjI& o) {
     bool pred = false;
-    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+    if constexpr (SRC == SRC_WEIGHTED) {  // integer window + per-object weight prepared by gs_prepare_kernel
+        if (t < nscan) {
+            const long long i = us.src_base + t;
+            int lab = us.cls;
+            if (p.labels != nullptr) lab = __ldg(p.labels + i);
+            const int2 c = __ldg(reinterpret_cast<const int2*>(p.centers) + i);
+            const int r = __ldg(p.radii + i);
+            const float w = __ldg(p.weights + i);
+            if (t < us.n && lab == us.cls && r >= 0) {
+                const long long X = c.x, Y = c.y, R = r;
+                if (!(Y + R < uy0 || Y - R >= uy1 || X + R < 0 || X - R >= W)) {
+                    o.x = c.x;
+                    o.y = c.y;
+                    o.r = r;
+                    o.w = w;
+                    pred = true;
+                }
+            }
+        }
+    } else if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
         if (t < nscan) {
             const long long i = us.src_base + t;
             int lab = us.cls;
@@ -525,7 +548,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
     __shared__ __align__(8) unsigned long long s_bar;  // its mbarrier
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const bool kneg = p.k < 0.0f;
+    const bool kneg0 = p.k < 0.0f;
     const int W = p.W, G = p.band_cols /* rows per group */;
     const long long plane_elems = (long long)p.H * W;
     {  // zero tile and staging buffers start all-zero (contiguous in shared memory)
@@ -548,6 +571,12 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         const int nscan = unit_header<SRC>(p, u, G, us, uy0, uy1, count_skips);
         float* const plane_ptr = p.heat + us.plane * plane_elems;
         const int ngroups = (uy1 - uy0 + G - 1) / G;
+        float kk = p.k;
+        bool kneg = kneg0;
+        if constexpr (SRC == SRC_WEIGHTED) {
+            kk = __ldg(p.k_classes + us.cls);
+            kneg = kk < 0.0f;
+        }
 
         __syncthreads();  // every warp is done with the previous unit's list (and shared memory is initialised)
 #ifdef DH_TRACE_UNITS
@@ -611,7 +640,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
             const int g = __ffsll((long long)gm) - 1;
             gm &= gm - 1ull;
             const int y0 = uy0 + g * G;
-            render_group<ACCUM, SRC, DIGEST>(p, ws, plane_ptr, plane_index0, y0, min(G, uy1 - y0), W, G, kneg, lane, small, mine,
+            render_group<ACCUM, SRC, DIGEST>(p, ws, plane_ptr, plane_index0, y0, min(G, uy1 - y0), W, G, kneg, kk, lane, small, mine,
                                              s_unit, ucnt, us, dg);
         }
 #ifdef DH_TRACE_UNITS

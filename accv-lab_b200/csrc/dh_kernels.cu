@@ -37,7 +37,7 @@ constexpr int kItemsPerThread = 8;
 constexpr int kBandCap = kThreads * kItemsPerThread;  // items (float4 or float) per band
 constexpr int kListCap = 1024;                        // objects per shared-memory list
 
-enum Source : int { SRC_BATCHED = 0, SRC_BOXES = 1, SRC_CSR = 2, SRC_FLATSCAN = 3 };
+enum Source : int { SRC_BATCHED = 0, SRC_BOXES = 1, SRC_CSR = 2, SRC_FLATSCAN = 3, SRC_WEIGHTED = 4 };
 
 struct __align__(16) Obj {
     float fx, fy, fr, wv;  // centre, radius (exact small ints as floats), signed 1/var
@@ -71,6 +71,10 @@ struct RenderParams {
     int bands_per_unit2, units_per_plane2;
     float factor, k;
     dh_status* status;
+    // SRC_WEIGHTED (groups_kernel only; the DALI draw_gaussians fast path): per-object 1/(2 sigma^2) instead of the
+    // radius -> sigma rule, per-class peak instead of one k
+    const float* weights;    // [B,T]
+    const float* k_classes;  // [C]
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -763,6 +767,35 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
     else render_kernel<1, false, SRC><<<grid, kThreads, 0, stream>>>(p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return (int)cudaGetLastError();
+}
+
+// FRESH render of symmetric integer windows with per-object weights and per-class peaks through the main renderer
+// (used by dh_gaussians.cu for the DALI draw_gaussians semantics). DH_ERR_UNSUPPORTED_SHAPE when the map does not
+// qualify for groups_kernel (W % 4, alignment, W > kGMaxW): the caller then uses its own kernel.
+int launch_weighted_fresh(cudaStream_t stream, float* heat, const int32_t* centers, const int32_t* radii_eff,
+                          const float* weights, const int32_t* labels, const void* sizes, int sizes_i64,
+                          const float* k_classes, long long B, long long T, long long C, long long H, long long W) {
+    DeviceInfo di;
+    int st = device_info(di);
+    if (st != DH_OK) return st;
+    if (!((W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heat) & 15u) == 0) && W <= kGMaxW)) return DH_ERR_UNSUPPORTED_SHAPE;
+    RenderParams p{};
+    p.heat = heat;
+    p.centers = centers;
+    p.radii = radii_eff;
+    p.weights = weights;
+    p.k_classes = k_classes;
+    p.labels = labels;
+    p.sizes = sizes;
+    p.sizes_i64 = sizes_i64;
+    p.num_planes = B * C;
+    p.C = (int)C;
+    p.T = (int)T;
+    p.H = (int)H;
+    p.W = (int)W;
+    p.factor = 1.0f;
+    p.k = 1.0f;
+    return launch_groups<false, SRC_WEIGHTED, false>(stream, p, di.sms);
 }
 
 }  // namespace dh

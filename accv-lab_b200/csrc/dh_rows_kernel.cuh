@@ -41,7 +41,7 @@ struct __align__(16) ObjI {
 template <int SRC>
 __device__ __forceinline__ bool load_slot(const RenderParams& p, long long src_base, int t, int cls, long long plane,
                                           bool cnt, int& x, int& y, int& r) {
-    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_WEIGHTED) {
         const long long i = src_base + t;
         if (p.labels != nullptr) {
             const int lab = __ldg(p.labels + i);

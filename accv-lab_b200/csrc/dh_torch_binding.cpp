@@ -464,10 +464,16 @@ at::Tensor draw_gaussians(const c10::optional<at::Tensor>& heatmap_in, at::Tenso
     int tag = 0;
     const void* sizes = sizes_ptr(nums_targets, tag);
     c10::cuda::CUDAGuard guard(heatmap_out.device());
+    at::Tensor ws;  // FRESH fast path (classify -> main renderer -> exact fix-up)
+    size_t wsb = 0;
+    if (!heatmap_in.has_value() && T > 0) {
+        wsb = dh_draw_gaussians_workspace_bytes(B, T);
+        ws = at::empty({(int64_t)wsb}, heatmap_out.options().dtype(at::kByte));
+    }
     check_status(dh_draw_gaussians(at::cuda::getCurrentCUDAStream().stream(), in_ptr, heatmap_out.data_ptr<float>(),
                                    centers.data_ptr<int>(), radii.data_ptr<float>(), sl_ptr, act_ptr, sizes, tag,
                                    k_for_classes.data_ptr<float>(), k_for_classes.numel(), B, T, C, H, W,
-                                   (float)radius_to_sigma_factor, nullptr),
+                                   (float)radius_to_sigma_factor, nullptr, ws.defined() ? ws.data_ptr() : nullptr, wsb),
                  "draw_gaussians");
     return heatmap_out;
 }

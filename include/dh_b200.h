@@ -212,12 +212,19 @@ int dh_pack_radius_center(void* stream, const float* const* centers_ptrs, const 
  * Deliberate differences: a slice_id outside [0, min(C, num_k)) skips the object and counts it in
  * dh_status.skipped_label (the reference fails the batch, or writes out of bounds when slice_id >= C); radii that are
  * NaN or |r| > 2048 are skipped and counted in skipped_radius (the reference's int32 squares overflow / its
- * float -> int casts are undefined there). One launch. */
+ * float -> int casts are undefined there). One launch (three with the workspace below). */
 int dh_draw_gaussians(void* stream, const float* heatmap_in, float* heatmap_out, const int32_t* centers,
                       const float* radii, const int32_t* slice_ids, const uint8_t* active, const void* nums_targets,
                       int nums_dtype, const float* k_for_classes, int64_t num_k, int64_t batch_size,
                       int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
-                      float radius_to_sigma_factor, dh_status* status);
+                      float radius_to_sigma_factor, dh_status* status, void* workspace, size_t workspace_bytes);
+/* Optional DEVICE workspace (16-byte aligned, dh_draw_gaussians_workspace_bytes(B, T) bytes) enables the FRESH fast
+ * path (heatmap_in == NULL, output >= 256 MiB, width % 4 == 0, width <= 1024, status == NULL): 3 launches — classify the objects; the
+ * main renderer (dh_draw_heatmap_batched's kernel, bulk stores + cluster launch control) draws every object whose
+ * window is the symmetric integer square; the exact kernel then redraws, in place, only the objects it is not
+ * (fp32-rounded asymmetric windows, negative radii, degenerate sigma) and returns at once when there are none.
+ * workspace == NULL: the single exact kernel. Results are identical either way. */
+size_t dh_draw_gaussians_workspace_bytes(int64_t batch_size, int64_t max_num_targets);
 
 /* Front half of the reference's BoundingBoxToHeatmapConverter — everything between the annotation boxes and
  * draw_gaussians, ~10 DALI CPU operators per sample in the reference — as ONE launch over the RaggedBatch slots:

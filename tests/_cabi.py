@@ -44,7 +44,9 @@ SIGNATURES = {
                                                      _f, _f, _p, _sz, _i64]),
     "dh_pack_ragged": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i]),
     "dh_pack_radius_center": (_i, [_p, _p, _p, _p, _f, _i64, _i64, _p, _p]),
-    "dh_draw_gaussians": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _i64, _f, _p]),
+    "dh_draw_gaussians": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _i64, _f, _p, _p,
+                               _sz]),
+    "dh_draw_gaussians_workspace_bytes": (_sz, [_i64, _i64]),
     "dh_boxes_to_gaussian_params": (_i, [_p, _p, _p, _p, _p, _p, _i, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64,
                                          ctypes.c_double, _f, _f, ctypes.c_double, _p, _p, _p, _p, _p, _p, _p]),
     "dh_gaussian_radius": (_i, [_p, _p, ctypes.c_double, _i, ctypes.c_int32, _i64, _p, _p]),

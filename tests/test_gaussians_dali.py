@@ -14,6 +14,7 @@ import pytest
 
 import _cabi
 
+FORCED_FAST = os.environ.get("DH_GS_FORCE_FAST") is not None  # set in conftest.py before the library loads
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_dali.npz")
 CASES = ("typical", "integer_r", "tiny_r", "two_d", "neg_k", "near_int")
 
@@ -90,6 +91,36 @@ def test_gpu_matches_reference_operator_goldens(cabi, cuda_dev, name):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("name", CASES)
+def test_gpu_fresh_fast_path_on_the_golden_objects(cuda_dev, oracle, name):
+    """FRESH rendering of every golden case's objects through the Python API (classify -> main renderer -> exact fix-up
+    of asymmetric / negative-radius / degenerate-sigma objects) == the oracle on zeros (itself bit-identical to the
+    reference operator) and == the single exact kernel bit for bit."""
+    import torch
+    from accvlab.draw_heatmap import b200
+    from accvlab.draw_heatmap import draw_heatmap_ext as ext
+
+    c = _case(np.load(GOLD), name)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda_dev)
+    sizes = dev(c["sizes"])
+    rb = lambda a: b200.RaggedBatch(dev(a), sample_sizes=sizes)
+    shape = c["heat_in"].shape
+    want = np.zeros(shape, np.float32)
+    oracle.draw_gaussians(want, c["centers"], c["radii"], c["sizes"], c["k"], float(c["factor"]), c["slice_ids"], c["active"])
+    l0 = b200.launch_count()
+    fast = b200.draw_gaussians(None, rb(c["active"]), rb(c["slice_ids"]), rb(c["centers"]), rb(c["radii"]), dev(c["k"]),
+                               float(c["factor"]), shape=shape)
+    W = shape[-1]
+    assert b200.launch_count() - l0 == (3 if (W % 4 == 0 and W <= 1024 and FORCED_FAST) else 1)
+    _check(fast.cpu().numpy(), want, name + " fresh fast")
+    zeros = torch.zeros(shape, device=cuda_dev)
+    exact = b200.draw_gaussians(zeros, rb(c["active"]), rb(c["slice_ids"]), rb(c["centers"]), rb(c["radii"]), dev(c["k"]),
+                                float(c["factor"]))
+    # max(0, .) over a zero input == the fresh result, except that a negative k leaves -0.0 vs 0.0 apart: compare values
+    assert np.array_equal(fast.cpu().numpy(), exact.cpu().numpy())
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("H,W,T,C", [(33, 47, 40, 3), (8, 4100, 30, 1), (232, 400, 100, 10), (64, 64, 700, 2)])
 def test_gpu_vs_oracle_shapes(cabi, cuda_dev, oracle, H, W, T, C):
     """Scalar path (W % 4 != 0), rows wider than one pass, a BASELINE-sized map, and T beyond one list chunk (700 > 512);
@@ -110,18 +141,28 @@ def test_gpu_vs_oracle_shapes(cabi, cuda_dev, oracle, H, W, T, C):
     dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda_dev)
     d = dict(c=dev(centers), r=dev(radii), s=dev(slice_ids), a=dev(active), n=dev(sizes), k=dev(k))
 
-    def run(hin, out):
+    wsb = cabi.dh_draw_gaussians_workspace_bytes(B, T)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=cuda_dev)
+
+    def run(hin, out, fast=False):
         rc = cabi.dh_draw_gaussians(_cabi.stream_ptr(), _cabi.ptr(hin), _cabi.ptr(out), _cabi.ptr(d["c"]), _cabi.ptr(d["r"]),
                                     _cabi.ptr(d["s"]), _cabi.ptr(d["a"]), _cabi.ptr(d["n"]), _cabi.DH_SIZES_I64,
-                                    _cabi.ptr(d["k"]), C, B, T, C, H, W, factor, None)
+                                    _cabi.ptr(d["k"]), C, B, T, C, H, W, factor, None, _cabi.ptr(ws) if fast else None,
+                                    wsb if fast else 0)
         _cabi.check(cabi, rc, "dh_draw_gaussians")
         torch.cuda.synchronize()
 
     want = np.zeros((B, C, H, W), np.float32)
     oracle.draw_gaussians(want, centers, radii, sizes, k, factor, slice_ids, active)
     out = torch.full((B, C, H, W), 9.0, device=cuda_dev)
-    run(None, out)  # fresh
+    run(None, out)  # fresh, single exact kernel
     _check(out.cpu().numpy(), want, "fresh")
+    out_f = torch.full((B, C, H, W), 9.0, device=cuda_dev)
+    l0 = cabi.dh_launch_count()
+    run(None, out_f, fast=True)  # fresh, classify -> main renderer -> exact fix-up (when the map qualifies)
+    assert cabi.dh_launch_count() - l0 == (3 if (W % 4 == 0 and W <= 1024 and FORCED_FAST) else 1)
+    _check(out_f.cpu().numpy(), want, "fresh fast path")
+    assert torch.equal(out_f, out), "fast path and exact kernel must agree bit for bit"
     bg = (rng.random((B, C, H, W), dtype=np.float32) * 0.6 * (rng.random((B, C, H, W)) < 0.3)).astype(np.float32)
     want2 = bg.copy()
     oracle.draw_gaussians(want2, centers, radii, sizes, k, factor, slice_ids, active)
@@ -144,7 +185,7 @@ def test_gpu_out_of_range_classes_and_radii_are_skipped_and_counted(cabi, cuda_d
     keep = [dev(centers), dev(radii), dev(slice_ids), dev(np.array([T], np.int64)), dev(np.array([1.0, 1.0], np.float32))]
     rc = cabi.dh_draw_gaussians(_cabi.stream_ptr(), None, _cabi.ptr(out), _cabi.ptr(keep[0]), _cabi.ptr(keep[1]),
                                 _cabi.ptr(keep[2]), None, _cabi.ptr(keep[3]), _cabi.DH_SIZES_I64, _cabi.ptr(keep[4]), 2,
-                                B, T, C, H, W, 0.3, _cabi.ptr(status))
+                                B, T, C, H, W, 0.3, _cabi.ptr(status), None, 0)
     _cabi.check(cabi, rc, "dh_draw_gaussians")
     torch.cuda.synchronize()
     want = np.zeros((B, C, H, W), np.float32)
