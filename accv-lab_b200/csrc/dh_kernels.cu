@@ -649,14 +649,15 @@ static int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
 }
-static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 131072);
+static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 196608);
 static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
 static const int g_no_clc = env_int("DH_G_NOCLC", 0);
 static const int g_tail_div = env_int("DH_G_TAIL_DIV", 2);            // tail-tier units are 1/this of a full unit (1 = off)
 static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail tier = this/2 waves of full-size units
 
 // Plan of the groups kernels: row group = G whole rows (<= kGStageCap bytes), unit = up to 64 groups of one plane,
-// ~128 KB when the problem is large (amortises the per-unit list build; measured optimum on cfg5: 3 units per plane), smaller when it
+// ~192 KB when the problem is large (amortises the per-unit list build; with the tail tier of half-size units the measured
+// optimum on cfg5 is 2 units per plane: 1.600 vs 1.631 ms for 3), smaller when it
 // is not, so that every resident CTA slot still sees several units.
 static void make_groups_plan(RenderParams& p, long long max_ctas) {
     // rows per group: as many as a staging buffer holds while DH_G_MINB CTAs still fit the SM's shared memory
