@@ -233,145 +233,145 @@ __global__ void __launch_bounds__(kGsThreads, LOSS_MODE ? 2 : (PX == 4 ? 3 : 4))
                 }
             }
         }
-      for (int b = ub0; b < ub1; ++b) {
-        const int by0 = b * p.band_rows, by1 = min(by0 + p.band_rows, p.H) - 1;  // inclusive
-        const int nitems = (by1 - by0 + 1) * wunits;
-        if (!((mask >> (b - ub0)) & 1u)) {  // nothing lands in this band
-            if constexpr (!INPLACE && !FRESH) {
-                // whole rows: the band is one contiguous range of the plane
-                const long long base = (long long)by0 * wunits;
-                if constexpr (PX == 4) {
-                    const float4* const i4 = in_plane ? reinterpret_cast<const float4*>(in_plane) + base : nullptr;
-                    float4* const o4 = reinterpret_cast<float4*>(out_plane) + base;
-#pragma unroll 4
-                    for (int it = tid; it < nitems; it += kGsThreads) o4[it] = i4 ? i4[it] : make_float4(0.f, 0.f, 0.f, 0.f);
-                } else {
-                    for (int it = tid; it < nitems; it += kGsThreads) out_plane[base + it] = in_plane ? in_plane[base + it] : 0.0f;
-                }
-            }
-            continue;
-        }
-
-        for (int item0 = 0; item0 < nitems; item0 += kGsThreads * kGsItems) {
-            float best[kGsItems][PX];
-            unsigned touched = 0u;  // bit (q*PX + j)
-            int rows[kGsItems], cols[kGsItems];
-#pragma unroll
-            for (int q = 0; q < kGsItems; ++q) {
-                const int it = item0 + q * kGsThreads + tid;
-                const bool valid = it < nitems;
-                // item -> (row, col): the divisions are hoisted out of the band loop for the first (usually only) pass
-                const int dr = item0 == 0 ? drow0[q] : it / wunits;
-                const int dc = item0 == 0 ? dcol0[q] : (it % wunits) * PX;
-                rows[q] = valid ? by0 + dr : -1 - (1 << 30);  // invalid items fail every row test
-                cols[q] = valid ? dc : 0;
-#pragma unroll
-                for (int j = 0; j < PX; ++j) best[q][j] = INF;
-            }
-            // input pixels of all items up front: the loads are in flight while the objects are evaluated (issued one
-            // item at a time next to their stores they serialise on the memory latency: out may alias in)
-            float vin[kGsItems][PX];
-#pragma unroll
-            for (int q = 0; q < kGsItems; ++q) {
-#pragma unroll
-                for (int j = 0; j < PX; ++j) vin[q][j] = 0.0f;
-                if (in_plane != nullptr && rows[q] >= 0) {
-                    const int idx = rows[q] * p.W + cols[q];
+        for (int b = ub0; b < ub1; ++b) {
+            const int by0 = b * p.band_rows, by1 = min(by0 + p.band_rows, p.H) - 1;  // inclusive
+            const int nitems = (by1 - by0 + 1) * wunits;
+            if (!((mask >> (b - ub0)) & 1u)) {  // nothing lands in this band
+                if constexpr (!INPLACE && !FRESH) {
+                    // whole rows: the band is one contiguous range of the plane
+                    const long long base = (long long)by0 * wunits;
                     if constexpr (PX == 4) {
-                        const float4 a = __ldg(reinterpret_cast<const float4*>(in_plane + idx));
-                        vin[q][0] = a.x; vin[q][1] = a.y; vin[q][2] = a.z; vin[q][3] = a.w;
+                        const float4* const i4 = in_plane ? reinterpret_cast<const float4*>(in_plane) + base : nullptr;
+                        float4* const o4 = reinterpret_cast<float4*>(out_plane) + base;
+#pragma unroll 4
+                        for (int it = tid; it < nitems; it += kGsThreads) o4[it] = i4 ? i4[it] : make_float4(0.f, 0.f, 0.f, 0.f);
                     } else {
-                        vin[q][0] = __ldg(in_plane + idx);
+                        for (int it = tid; it < nitems; it += kGsThreads) out_plane[base + it] = in_plane ? in_plane[base + it] : 0.0f;
                     }
                 }
+                continue;
             }
-            for (int c0 = 0; c0 < (single ? 1 : n); c0 += kGsListCap) {
-                if (!single) cnt = build(c0, count && item0 == 0 && b == ub0);
-                for (int e = 0; e < cnt; ++e) {
-                    const GObj o = s_list[e];  // broadcast
-                    if (o.y1 < by0 || o.y0 > by1) continue;  // block-uniform: the object misses this band of the unit
+
+            for (int item0 = 0; item0 < nitems; item0 += kGsThreads * kGsItems) {
+                float best[kGsItems][PX];
+                unsigned touched = 0u;  // bit (q*PX + j)
+                int rows[kGsItems], cols[kGsItems];
 #pragma unroll
-                    for (int q = 0; q < kGsItems; ++q) {
-                        if (rows[q] < o.y0 || rows[q] > o.y1) continue;
-                        if (cols[q] > o.x1 || cols[q] + (PX - 1) < o.x0) continue;
-                        const float fdy = (float)rows[q] - o.cy;
-                        const float fy2 = __fmul_rn(fdy, fdy);
+                for (int q = 0; q < kGsItems; ++q) {
+                    const int it = item0 + q * kGsThreads + tid;
+                    const bool valid = it < nitems;
+                    // item -> (row, col): the divisions are hoisted out of the band loop for the first (usually only) pass
+                    const int dr = item0 == 0 ? drow0[q] : it / wunits;
+                    const int dc = item0 == 0 ? dcol0[q] : (it % wunits) * PX;
+                    rows[q] = valid ? by0 + dr : -1 - (1 << 30);  // invalid items fail every row test
+                    cols[q] = valid ? dc : 0;
 #pragma unroll
-                        for (int j = 0; j < PX; ++j) {
-                            const int x = cols[q] + j;
-                            const float fdx = (float)x - o.cx;
-                            // (float)(dy^2 + dx^2): both squares are exact (< 2^24), the sum rounds once like the int -> float cast
-                            float t = __fmul_rn(__fadd_rn(fy2, __fmul_rn(fdx, fdx)), o.inv);
-                            t = kneg ? -t : t;
-                            if (x >= o.x0 && x <= o.x1 && t == t) {  // NaN (0 * inf) never wins the reference's max
-                                best[q][j] = fminf(best[q][j], t);
-                                touched |= 1u << (q * PX + j);
+                    for (int j = 0; j < PX; ++j) best[q][j] = INF;
+                }
+                // input pixels of all items up front: the loads are in flight while the objects are evaluated (issued one
+                // item at a time next to their stores they serialise on the memory latency: out may alias in)
+                float vin[kGsItems][PX];
+#pragma unroll
+                for (int q = 0; q < kGsItems; ++q) {
+#pragma unroll
+                    for (int j = 0; j < PX; ++j) vin[q][j] = 0.0f;
+                    if (in_plane != nullptr && rows[q] >= 0) {
+                        const int idx = rows[q] * p.W + cols[q];
+                        if constexpr (PX == 4) {
+                            const float4 a = __ldg(reinterpret_cast<const float4*>(in_plane + idx));
+                            vin[q][0] = a.x; vin[q][1] = a.y; vin[q][2] = a.z; vin[q][3] = a.w;
+                        } else {
+                            vin[q][0] = __ldg(in_plane + idx);
+                        }
+                    }
+                }
+                for (int c0 = 0; c0 < (single ? 1 : n); c0 += kGsListCap) {
+                    if (!single) cnt = build(c0, count && item0 == 0 && b == ub0);
+                    for (int e = 0; e < cnt; ++e) {
+                        const GObj o = s_list[e];  // broadcast
+                        if (o.y1 < by0 || o.y0 > by1) continue;  // block-uniform: the object misses this band of the unit
+#pragma unroll
+                        for (int q = 0; q < kGsItems; ++q) {
+                            if (rows[q] < o.y0 || rows[q] > o.y1) continue;
+                            if (cols[q] > o.x1 || cols[q] + (PX - 1) < o.x0) continue;
+                            const float fdy = (float)rows[q] - o.cy;
+                            const float fy2 = __fmul_rn(fdy, fdy);
+#pragma unroll
+                            for (int j = 0; j < PX; ++j) {
+                                const int x = cols[q] + j;
+                                const float fdx = (float)x - o.cx;
+                                // (float)(dy^2 + dx^2): both squares are exact (< 2^24), the sum rounds once like the int -> float cast
+                                float t = __fmul_rn(__fadd_rn(fy2, __fmul_rn(fdx, fdx)), o.inv);
+                                t = kneg ? -t : t;
+                                if (x >= o.x0 && x <= o.x1 && t == t) {  // NaN (0 * inf) never wins the reference's max
+                                    best[q][j] = fminf(best[q][j], t);
+                                    touched |= 1u << (q * PX + j);
+                                }
                             }
                         }
                     }
                 }
-            }
 #pragma unroll
-            for (int q = 0; q < kGsItems; ++q) {
-                if (rows[q] < 0) continue;
-                const unsigned tq = (touched >> (q * PX)) & ((1u << PX) - 1u);
-                if (INPLACE && tq == 0u) continue;
-                const int idx = rows[q] * p.W + cols[q];  // H*W < 2^31
-                float v[PX];
+                for (int q = 0; q < kGsItems; ++q) {
+                    if (rows[q] < 0) continue;
+                    const unsigned tq = (touched >> (q * PX)) & ((1u << PX) - 1u);
+                    if (INPLACE && tq == 0u) continue;
+                    const int idx = rows[q] * p.W + cols[q];  // H*W < 2^31
+                    float v[PX];
 #pragma unroll
-                for (int j = 0; j < PX; ++j) v[j] = vin[q][j];
-                if constexpr (LOSS) {
-                    // v[] = prediction. Target of the pixel exactly as the FRESH renderer would have stored it, then
-                    //   target == 1: loss = -(1-p)^alpha log(p+eps);  else: loss = -p^alpha log(1-p+eps) (1-target)^gamma
-                    float lq = 0.0f;
+                    for (int j = 0; j < PX; ++j) v[j] = vin[q][j];
+                    if constexpr (LOSS) {
+                        // v[] = prediction. Target of the pixel exactly as the FRESH renderer would have stored it, then
+                        //   target == 1: loss = -(1-p)^alpha log(p+eps);  else: loss = -p^alpha log(1-p+eps) (1-target)^gamma
+                        float lq = 0.0f;
 #pragma unroll
-                    for (int j = 0; j < PX; ++j) {
-                        float tg = 0.0f;
-                        if (tq & (1u << j)) {
-                            const float val = __fmul_rn(expf(-best[q][j]), k);
-                            tg = (0.0f >= val) ? 0.0f : val;
+                        for (int j = 0; j < PX; ++j) {
+                            float tg = 0.0f;
+                            if (tq & (1u << j)) {
+                                const float val = __fmul_rn(expf(-best[q][j]), k);
+                                tg = (0.0f >= val) ? 0.0f : val;
+                            }
+                            const float pr = v[j], om = 1.0f - pr;
+                            float loss, g;
+                            if (tg == 1.0f) {
+                                const float den = pr + p.eps, lg = FAST ? __logf(den) : logf(den);
+                                const float pw = std_exp ? om * om : powf(om, p.alpha);
+                                const float pw1 = std_exp ? om : powf(om, p.alpha - 1.0f);
+                                loss = -lg * pw;
+                                g = p.alpha * pw1 * lg - (FAST ? __fdividef(pw, den) : pw / den);
+                                npos += 1;
+                            } else {
+                                const float den = om + p.eps, lg = FAST ? __logf(den) : logf(den);
+                                const float pa = std_exp ? pr * pr : powf(pr, p.alpha);
+                                const float pa1 = std_exp ? pr : powf(pr, p.alpha - 1.0f);
+                                const float ot = 1.0f - tg, ot2 = ot * ot;
+                                const float wgt = std_exp ? ot2 * ot2 : powf(ot, p.gamma);
+                                loss = -lg * pa * wgt;
+                                g = wgt * ((FAST ? __fdividef(pa, den) : pa / den) - p.alpha * pa1 * lg);
+                            }
+                            lq += loss;
+                            v[j] = g;
                         }
-                        const float pr = v[j], om = 1.0f - pr;
-                        float loss, g;
-                        if (tg == 1.0f) {
-                            const float den = pr + p.eps, lg = FAST ? __logf(den) : logf(den);
-                            const float pw = std_exp ? om * om : powf(om, p.alpha);
-                            const float pw1 = std_exp ? om : powf(om, p.alpha - 1.0f);
-                            loss = -lg * pw;
-                            g = p.alpha * pw1 * lg - (FAST ? __fdividef(pw, den) : pw / den);
-                            npos += 1;
-                        } else {
-                            const float den = om + p.eps, lg = FAST ? __logf(den) : logf(den);
-                            const float pa = std_exp ? pr * pr : powf(pr, p.alpha);
-                            const float pa1 = std_exp ? pr : powf(pr, p.alpha - 1.0f);
-                            const float ot = 1.0f - tg, ot2 = ot * ot;
-                            const float wgt = std_exp ? ot2 * ot2 : powf(ot, p.gamma);
-                            loss = -lg * pa * wgt;
-                            g = wgt * ((FAST ? __fdividef(pa, den) : pa / den) - p.alpha * pa1 * lg);
+                        lsum += (double)lq;
+                        if (p.out != nullptr) {
+                            if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
+                            else out_plane[idx] = v[0];
                         }
-                        lq += loss;
-                        v[j] = g;
-                    }
-                    lsum += (double)lq;
-                    if (p.out != nullptr) {
-                        if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
-                        else out_plane[idx] = v[0];
-                    }
-                } else {
-                if (tq != 0u) {  // one expf per pixel of a touched item, unconditionally: no per-pixel divergence
+                    } else {
+                    if (tq != 0u) {  // one expf per pixel of a touched item, unconditionally: no per-pixel divergence
 #pragma unroll
-                    for (int j = 0; j < PX; ++j) {
-                        const float t = kneg ? -best[q][j] : best[q][j];
-                        const float val = __fmul_rn(k, expf(-t));
-                        v[j] = ((tq & (1u << j)) && v[j] < val) ? val : v[j];  // std::max(pixel, val)
+                        for (int j = 0; j < PX; ++j) {
+                            const float t = kneg ? -best[q][j] : best[q][j];
+                            const float val = __fmul_rn(k, expf(-t));
+                            v[j] = ((tq & (1u << j)) && v[j] < val) ? val : v[j];  // std::max(pixel, val)
+                        }
+                    }
+                    if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
+                    else out_plane[idx] = v[0];
                     }
                 }
-                if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
-                else out_plane[idx] = v[0];
-                }
             }
-        }
-      }  // bands of the unit
+        }  // bands of the unit
         if constexpr (LOSS) {  // fixed-order reduction of the unit: lanes (xor tree) -> warps (in order) -> partial[u]
             __shared__ double s_l[kGsThreads / 32];
             __shared__ int s_n[kGsThreads / 32];
