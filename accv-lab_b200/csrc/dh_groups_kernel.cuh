@@ -99,15 +99,18 @@ __device__ __forceinline__ void sweep_obj(unsigned* __restrict__ buf, int y0, in
                 rowp[x] = max(rowp[x], t);
             }
         } else {  // wide span: four pixels per lane, 128-bit shared-memory accesses
+            // every x visited lies inside the row (x0 & ~3 >= 0, W % 4 == 0), so the window test is |dx| <= r alone;
+            // dx as a float: one conversion per lane, then exact +1 steps (|dx| < 2^24)
+            const float fr = (float)o.r;
             for (int xv = (x0 & ~3) + 4 * lane; xv <= x1; xv += 128) {
                 uint4 q = *reinterpret_cast<uint4*>(rowp + xv);
                 unsigned* qc = reinterpret_cast<unsigned*>(&q);
+                const float fdx0 = (float)(xv - o.x);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
-                    const int x = xv + c;
-                    const float fdx = (float)(x - o.x);
+                    const float fdx = fdx0 + (float)c;
                     const unsigned t = enc_m(__fmul_rn(__fadd_rn(fi, __fmul_rn(fdx, fdx)), o.w), kneg);
-                    if (x >= x0 && x <= x1) qc[c] = max(qc[c], t);
+                    qc[c] = (fabsf(fdx) <= fr) ? max(qc[c], t) : qc[c];
                 }
                 *reinterpret_cast<uint4*>(rowp + xv) = q;
             }

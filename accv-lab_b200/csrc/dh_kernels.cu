@@ -652,6 +652,7 @@ static int env_int(const char* name, int dflt) {
 static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 196608);
 static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
 static const int g_no_clc = env_int("DH_G_NOCLC", 0);
+static const int g_heavy_per_slot = env_int("DH_G_HEAVY_PER_SLOT", 8);
 static const int g_tail_div = env_int("DH_G_TAIL_DIV", 2);            // tail-tier units are 1/this of a full unit (1 = off)
 static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail tier = this/2 waves of full-size units
 
@@ -674,7 +675,10 @@ static void make_groups_plan(RenderParams& p, long long max_ctas) {
     p.bands_per_plane = groups_y;
     const long long group_bytes = (long long)G * p.W * 4;
     const long long total_groups = p.num_planes * groups_y;
-    long long gpu = total_groups / (4 * max_ctas);
+    // units per resident CTA slot: 4, or 8 when samples can hold many objects (units are then compute-heavy and of
+    // similar cost, so the last, partly filled wave is expensive: cfg4 ran 4.1 waves of 1024-object units)
+    const long long per_slot = (p.T >= 256) ? g_heavy_per_slot : 4;
+    long long gpu = total_groups / (per_slot * max_ctas);
     const long long cap = (g_unit_bytes + group_bytes - 1) / group_bytes;
     if (gpu > cap) gpu = cap;
     if (gpu < kGWarps) gpu = kGWarps;  // at least one group per warp, however small the problem
