@@ -652,6 +652,7 @@ static int env_int(const char* name, int dflt) {
 static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 196608);
 static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
 static const int g_no_clc = env_int("DH_G_NOCLC", 0);
+static const int g_single_wave = env_int("DH_G_SINGLE_WAVE", 1);
 static const int g_heavy_per_slot = env_int("DH_G_HEAVY_PER_SLOT", 8);
 static const int g_tail_div = env_int("DH_G_TAIL_DIV", 2);            // tail-tier units are 1/this of a full unit (1 = off)
 static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail tier = this/2 waves of full-size units
@@ -681,6 +682,15 @@ static void make_groups_plan(RenderParams& p, long long max_ctas) {
     long long gpu = total_groups / (per_slot * max_ctas);
     const long long cap = (g_unit_bytes + group_bytes - 1) / group_bytes;
     if (gpu > cap) gpu = cap;
+    // Small problems (fewer planes than resident CTA slots, not object-heavy): ONE wave. Every unit pays ~3 us of pure
+    // latency, so a second, partly filled wave of small units costs more than fewer, larger units in a single wave.
+    if (g_single_wave && p.T < 256 && p.num_planes <= max_ctas) {
+        long long upp = max_ctas / p.num_planes;
+        if (upp > groups_y / kGWarps) upp = groups_y / kGWarps;
+        if (upp < 1) upp = 1;
+        const long long one_wave = (groups_y + upp - 1) / upp;
+        if (one_wave <= cap && one_wave > gpu) gpu = one_wave;
+    }
     if (gpu < kGWarps) gpu = kGWarps;  // at least one group per warp, however small the problem
     if (gpu > kGMaxGroups) gpu = kGMaxGroups;
     if (gpu > groups_y) gpu = groups_y;
