@@ -30,6 +30,14 @@ void check_status(int st, const char* what) {
     TORCH_CHECK(st == DH_OK, what, " failed: ", dh_status_string(st), " (status ", st, ")");
 }
 
+// The C ABI reads "labels == NULL" as "one plane per sample". A class-wise call with max_num_targets == 0 has an empty
+// labels tensor whose data pointer is NULL too: hand over a non-NULL stand-in (never dereferenced: there are no slots).
+const int32_t* labels_ptr(const at::Tensor& labels) {
+    static const int32_t dummy = 0;
+    const int32_t* p = labels.data_ptr<int>();
+    return p != nullptr ? p : &dummy;
+}
+
 const void* sizes_ptr(const at::Tensor& nums_targets, int& tag) {
     TORCH_CHECK(nums_targets.scalar_type() == at::kInt || nums_targets.scalar_type() == at::kLong,
                 "nums_targets must have dtype int32 or int64, got ", nums_targets.scalar_type());
@@ -116,7 +124,7 @@ void batched_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tens
     const void* sizes = sizes_ptr(nums_targets, tag);
     const bool cw = labels != nullptr;
     check_status(dh_draw_heatmap_batched(stream.stream(), heatmap.data_ptr<float>(), centers.data_ptr<int>(),
-                                         radii.data_ptr<int>(), sizes, tag, cw ? labels->data_ptr<int>() : nullptr,
+                                         radii.data_ptr<int>(), sizes, tag, cw ? labels_ptr(*labels) : nullptr,
                                          heatmap.size(0), radii.size(1), cw ? heatmap.size(1) : 1,
                                          heatmap.size(cw ? 2 : 1), heatmap.size(cw ? 3 : 2), factor, k, mode, nullptr),
                  "draw_heatmap_batched");
@@ -210,7 +218,7 @@ void render_heatmap_from_boxes(at::Tensor& heatmaps, const at::Tensor& centers, 
     const void* sizes = sizes_ptr(nums_targets, tag);
     check_status(dh_draw_heatmap_batched_from_boxes(
                      stream.stream(), heatmaps.data_ptr<float>(), centers.data_ptr<float>(), bboxes.data_ptr<float>(),
-                     (float)out_size_factor, sizes, tag, cw ? lab->data_ptr<int>() : nullptr, heatmaps.size(0),
+                     (float)out_size_factor, sizes, tag, cw ? labels_ptr(*lab) : nullptr, heatmaps.size(0),
                      centers.size(1), cw ? heatmaps.size(1) : 1, heatmaps.size(cw ? 2 : 1), heatmaps.size(cw ? 3 : 2),
                      diameter_to_sigma_factor, k_scale, fresh ? DH_MODE_FRESH : DH_MODE_ACCUMULATE, nullptr, nullptr,
                      nullptr),
@@ -297,7 +305,7 @@ void render_heatmap_from_boxes_host(const c10::optional<at::Tensor>& heatmap_hos
     check_status(dh_draw_heatmap_batched_from_boxes_host(
                      at::cuda::getCurrentCUDAStream().stream(), hh, hd, ck, centers.data_ptr<float>(),
                      bboxes.data_ptr<float>(), (float)out_size_factor, nums_targets.data_ptr<int64_t>(),
-                     cw ? labels->data_ptr<int>() : nullptr, B, T, C, height, width, diameter_to_sigma_factor, k_scale,
+                     cw ? labels_ptr(*labels) : nullptr, B, T, C, height, width, diameter_to_sigma_factor, k_scale,
                      scratch.data_ptr(), (size_t)scratch.nbytes(), chunk_samples),
                  "render_heatmap_from_boxes_host");
 }
@@ -589,7 +597,7 @@ std::tuple<at::Tensor, at::Tensor> gaussian_focal_loss(const at::Tensor& pred, c
     at::Tensor ws = at::empty({(int64_t)wsb}, pred.options().dtype(at::kByte));
     check_status(dh_gaussian_focal_loss(at::cuda::getCurrentCUDAStream().stream(), pred.data_ptr<float>(),
                                         centers.data_ptr<int>(), radii.data_ptr<int>(), sizes, tag,
-                                        classwise ? labels->data_ptr<int>() : nullptr, B, T, C, H, W,
+                                        classwise ? labels_ptr(*labels) : nullptr, B, T, C, H, W,
                                         diameter_to_sigma_factor, k_scale, (float)alpha, (float)gamma, (float)eps,
                                         fast_math ? 1 : 0, want_grad ? grad.data_ptr<float>() : nullptr, out2.data_ptr<double>(),
                                         ws.data_ptr(), wsb),

@@ -96,7 +96,9 @@ int dh_radius_center(void* stream, const float* centers_xy, const float* bboxes_
  *   num_classes  C; ignored (treated as 1) when labels == NULL
  *   mode         DH_MODE_ACCUMULATE | DH_MODE_FRESH
  *   status       optional device dh_status*, may be NULL
- * Plane offsets are 64-bit (the reference overflows int32 at B*C*H*W >= 2^31, cuh:99-104). */
+ * Plane offsets are 64-bit (the reference overflows int32 at B*C*H*W >= 2^31, cuh:99-104).
+ * Note: `labels == NULL` selects the one-plane-per-sample layout. A class-wise call with max_num_targets == 0 (empty
+ * labels array) must still pass a non-NULL pointer (it is never dereferenced). */
 int dh_draw_heatmap_batched(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
                             const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t batch_size,
                             int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
