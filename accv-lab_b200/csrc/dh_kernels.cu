@@ -624,7 +624,10 @@ static void make_rows_plan(RenderParams& p, long long max_ctas) {
 
 template <bool ACCUM, int SRC>
 static int launch_rows(cudaStream_t stream, RenderParams& p, int sms) {
-    static int occ = 0;  // per instantiation; also marks "attribute set"
+    static int occ_dev[64] = {0};  // per instantiation and device (function attributes are per device); also "attribute set"
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
+    int& occ = occ_dev[dev];
     if (occ == 0) {
         cudaError_t e = cudaFuncSetAttribute(rows_kernel<ACCUM, SRC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)kRowsSmemBytes);
@@ -724,7 +727,10 @@ static void make_groups_plan(RenderParams& p, long long max_ctas) {
 
 template <bool ACCUM, int SRC, bool DIGEST>
 static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
-    static bool attr_set = false;
+    static bool attr_set_dev[64] = {false};  // function attributes are per device: one process may drive several GPUs
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
+    bool& attr_set = attr_set_dev[dev];
     if (!attr_set) {
         const int cap = (int)groups_smem_bytes(kGStageCap);  // widest map: fewer CTAs per SM then
         cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST>,

@@ -175,3 +175,30 @@ def test_against_unmodified_reference_cuda_extension(cuda_dev, build, abs_tol):
         ref.draw_heatmap(a3, ci[valid].contiguous(), ri[valid].contiguous(), idx, 6.0, 1.0)
         ours.draw_heatmap(b3, ci[valid].contiguous(), ri[valid].contiguous(), idx, 6.0, 1.0)
         assert torch.equal(b3, b2) and float((a3 - b3).abs().max()) <= abs_tol
+
+
+def test_one_process_two_devices(cuda_dev):
+    """One process driving several GPUs: kernel attributes (dynamic shared memory opt-in) are per device, streams and
+    allocations follow the tensors' device. Skipped on single-GPU boxes."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import workloads
+    import accvlab.draw_heatmap as dh
+    from accvlab.draw_heatmap import b200
+
+    w = workloads.make("cfg2")
+    cfg = w.cfg
+    outs = []
+    for d in (0, 1, 0):
+        dev = torch.device("cuda", d)
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        heat = b200.render_heatmap_from_boxes(up(w.centers_f), up(w.bboxes_f), cfg.osf, up(w.sizes), cfg.H, cfg.W, cfg.C, up(w.labels))
+        assert heat.device == dev
+        acc = torch.zeros_like(heat)
+        ci, ri = b200.radius_center(up(w.centers_f), up(w.bboxes_f), cfg.osf)
+        rb = lambda t: b200.RaggedBatch(t, sample_sizes=up(w.sizes))
+        dh.draw_heatmap_batched(acc, rb(ci), rb(ri), 6.0, 1.0, labels=rb(up(w.labels)))
+        torch.cuda.synchronize(dev)
+        assert torch.equal(acc, heat)
+        outs.append(heat.cpu())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
