@@ -90,18 +90,21 @@ def _tensor_and_sizes(x):
 
 def render_heatmap_batched(centers, radii, height: Optional[int] = None, width: Optional[int] = None,
                            num_classes: Optional[int] = None, labels=None, diameter_to_sigma_factor: float = 6.0,
-                           k_scale: float = 1.0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                           k_scale: float = 1.0, out: Optional[torch.Tensor] = None,
+                           dtype: torch.dtype = torch.float32) -> torch.Tensor:
     """Render a fresh heatmap (every pixel written once; zeros where nothing is drawn). Returns the heatmap.
 
     ``centers``/``radii``/``labels`` are RaggedBatches (or anything with ``.tensor`` and ``.sample_sizes``).
     Either pass ``out`` (any contents, fully overwritten) or ``height``/``width`` (+ ``num_classes`` with labels).
+    ``dtype`` (or the dtype of ``out``) may be ``torch.float16`` / ``torch.bfloat16``: the values are the float32
+    result rounded once to nearest even, at half the output bytes (not in the reference, whose heatmaps are float32).
     """
     ct, sizes = _tensor_and_sizes(centers)
     rt, _ = _tensor_and_sizes(radii)
     lt = None if labels is None else _tensor_and_sizes(labels)[0]
     if out is None:
         shape = (ct.shape[0], height, width) if lt is None else (ct.shape[0], num_classes, height, width)
-        out = torch.empty(shape, dtype=torch.float32, device=ct.device)
+        out = torch.empty(shape, dtype=dtype, device=ct.device)
     _ext.render_heatmap_batched(out, ct, rt, sizes, lt, diameter_to_sigma_factor, k_scale, True)
     return out
 
@@ -110,11 +113,13 @@ def render_heatmap_from_boxes(centers: torch.Tensor, bboxes: torch.Tensor, out_s
                               sample_sizes: torch.Tensor, height: Optional[int] = None, width: Optional[int] = None,
                               num_classes: Optional[int] = None, labels: Optional[torch.Tensor] = None,
                               diameter_to_sigma_factor: float = 6.0, k_scale: float = 1.0,
-                              out: Optional[torch.Tensor] = None, fresh: bool = True) -> torch.Tensor:
-    """Float centres ``[B,T,2]`` + boxes ``[B,T,4]`` -> heatmap, radius/centre computation fused (one launch)."""
+                              out: Optional[torch.Tensor] = None, fresh: bool = True,
+                              dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """Float centres ``[B,T,2]`` + boxes ``[B,T,4]`` -> heatmap, radius/centre computation fused (one launch).
+    float16 / bfloat16 heatmaps (``dtype`` or ``out``) are served in fresh mode only."""
     if out is None:
         shape = (centers.shape[0], height, width) if labels is None else (centers.shape[0], num_classes, height, width)
-        out = torch.empty(shape, dtype=torch.float32, device=centers.device)
+        out = torch.empty(shape, dtype=dtype, device=centers.device)
         fresh = True
     _ext.render_heatmap_from_boxes(out, centers, bboxes, float(out_size_factor), sample_sizes, labels,
                                    diameter_to_sigma_factor, k_scale, fresh)

@@ -55,6 +55,15 @@ __device__ __forceinline__ unsigned enc_m(float m, bool kneg) {
     return kneg ? b + 1u : ~b;
 }
 
+// 16-bit heatmap planes (FRESH mode only): OUT = 0 fp32 (the reference's only type), 1 fp16, 2 bf16. The value
+// is computed in fp32 exactly as before and rounded ONCE, to nearest even, when it is staged for the bulk store.
+enum OutType : int { OUT_F32 = 0, OUT_F16 = 1, OUT_BF16 = 2 };
+template <int OUT>
+__device__ __forceinline__ unsigned short cvt16(float f) {
+    if constexpr (OUT == OUT_F16) return __half_as_ushort(__float2half_rn(f));
+    else return __bfloat16_as_ushort(__float2bfloat16_rn(f));
+}
+
 // Pixel index -> 64-bit digest contribution (== dh_host.cu, oracle/oracle.py:_mix_index): 32-bit IMADs only — the
 // renderer is instruction-issue bound, a 64-bit splitmix per touched pixel cost 12 % of the step.
 __device__ __forceinline__ unsigned long long mix_index(unsigned long long i) {
@@ -119,9 +128,10 @@ __device__ __forceinline__ void sweep_obj(unsigned* __restrict__ buf, int y0, in
 }
 
 // Dense path, K4: the span union of one staged row, one expf per touched pixel (cuh:45), in place.
-template <bool ACCUM, bool DIGEST>
-__device__ __forceinline__ void finish_row(unsigned* __restrict__ rowp, float* __restrict__ grow, long long gindex, int x0,
-                                           int x1, bool kneg, float k, int lane, Digest& dg) {
+template <bool ACCUM, bool DIGEST, int OUT>
+__device__ __forceinline__ void finish_row(unsigned* __restrict__ rowp, float* __restrict__ grow,
+                                           unsigned short* __restrict__ hrow, long long gindex, int x0, int x1, bool kneg,
+                                           float k, int lane, Digest& dg) {
     for (int x = x0 + lane; x <= x1; x += 32) {
         const unsigned t = rowp[x];
         if (t != 0u) {
@@ -133,7 +143,12 @@ __device__ __forceinline__ void finish_row(unsigned* __restrict__ rowp, float* _
                 if (!(g >= v)) grow[x] = v;  // cuh:30: keep old iff old >= v
             } else {
                 const float f = (0.0f >= v) ? 0.0f : v;  // max-blend into the fused zero-init
-                rowp[x] = __float_as_uint(f);
+                if constexpr (OUT == OUT_F32) {
+                    rowp[x] = __float_as_uint(f);
+                } else {  // 16-bit planes: the fp32 row is scratch (back to all-zero), the value goes to the 16-bit row
+                    rowp[x] = 0u;
+                    hrow[x] = cvt16<OUT>(f);
+                }
                 if constexpr (DIGEST) dg.add(f, gindex + x);
             }
         }
@@ -145,7 +160,7 @@ __device__ __forceinline__ void finish_row(unsigned* __restrict__ rowp, float* _
 //   k >= 0: max_o k*expf(-m_o) = k*expf(-min_o m_o);  k < 0: the max picks max_o m_o = -min_o(-m_o)
 // (expf is monotone: verified exhaustively on the device by tests/test_gpu_properties.py), so `ws` = +-1/var and one
 // fminf cover both signs; negation is exact, so every rounding is the reference's.
-template <bool ACCUM, bool DIGEST>
+template <bool ACCUM, bool DIGEST, int OUT>
 __device__ __forceinline__ void sparse_group(unsigned* __restrict__ buf, float* __restrict__ gdst, long long gindex, int y0,
                                              int nrows, int W, const ObjI& A, const ObjI& B, bool hasB, bool kneg, float k,
                                              int lane, int& ux0, int& ux1, Digest& dg) {
@@ -186,7 +201,8 @@ __device__ __forceinline__ void sparse_group(unsigned* __restrict__ buf, float* 
                     if (!(g >= v)) *gp = v;  // cuh:30
                 } else {
                     const float f = (0.0f >= v) ? 0.0f : v;
-                    buf[rr * W + x] = __float_as_uint(f);
+                    if constexpr (OUT == OUT_F32) buf[rr * W + x] = __float_as_uint(f);
+                    else reinterpret_cast<unsigned short*>(buf)[rr * W + x] = cvt16<OUT>(f);  // `buf` = the 16-bit buffer
                     if constexpr (DIGEST) dg.add(f, gindex + (long long)rr * W + x);
                 }
             }
@@ -267,25 +283,39 @@ struct UnitSrc {
 
 // K3 + K4b for ONE touched row group, by one warp. `list`/`ucnt` is the unit list in shared memory, `mine` the
 // lane's own entry when the unit has <= 32 objects (`small`). FRESH: the group leaves with one bulk store.
-template <bool ACCUM, int SRC, bool DIGEST>
-__device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& ws, float* __restrict__ plane_ptr,
+// 16-bit planes (OUT != OUT_F32, FRESH only): the warp's first staging region is the fp32 scratch of the dense path
+// (all-zero again after finish_row), the second one holds the two alternating 16-bit output buffers.
+template <bool ACCUM, int SRC, bool DIGEST, int OUT>
+__device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& ws, char* __restrict__ plane_b,
                                              long long plane_index0, int y0, int nrows, int W, int G, bool kneg, float kk, int lane,
                                              bool small, const ObjI& mine, const ObjI* __restrict__ list, int ucnt,
                                              const UnitSrc& us, Digest& dg) {
+    static_assert(OUT == OUT_F32 || !ACCUM, "16-bit planes exist in FRESH mode only");
+    constexpr int ES = (OUT == OUT_F32) ? 4 : 2;
     const float k = (SRC == SRC_WEIGHTED) ? kk : p.k;  // per-class peak only in the weighted mode
     const int y1 = y0 + nrows - 1;
-    float* const gdst = plane_ptr + (long long)y0 * W;
+    float* const gdst = reinterpret_cast<float*>(plane_b + (long long)y0 * W * ES);  // fp32 view: OUT_F32 only
     const long long gindex = plane_index0 + (long long)y0 * W;
-    unsigned* const buf = ws.cur ? ws.buf1 : ws.buf0;
+    // `obuf`: what the bulk store reads; `buf`: where the dense path sweeps (the same buffer for fp32 planes)
+    unsigned* const obuf = (OUT == OUT_F32) ? (ws.cur ? ws.buf1 : ws.buf0)
+                                            : reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws.buf1) +
+                                                                          (ws.cur ? (p.stage_bytes >> 1) : 0));
+    unsigned* const buf = (OUT == OUT_F32) ? obuf : ws.buf0;
     if constexpr (!ACCUM) {
-        if (lane == 0) bulk_wait_read<1>();  // the store that last read `buf` is older than my latest one
+        if (lane == 0) bulk_wait_read<1>();  // the store that last read `obuf` is older than my latest one
         __syncwarp();
         const int cx0 = ws.cur ? ws.c1x0 : ws.c0x0, cx1 = ws.cur ? ws.c1x1 : ws.c0x1;
-        if (cx1 >= cx0) {  // back to all-zero: clear only what its last use wrote (128-bit stores, W % 4 == 0)
+        if (cx1 >= cx0) {  // back to all-zero: clear only what its last use wrote (4 pixels per store, W % 4 == 0)
             const int q0 = cx0 >> 2, q1 = cx1 >> 2, w4 = W >> 2;
-            uint4* const b4 = reinterpret_cast<uint4*>(buf);
-            for (int rr = 0; rr < G; ++rr)
-                for (int q = q0 + lane; q <= q1; q += 32) b4[rr * w4 + q] = make_uint4(0u, 0u, 0u, 0u);
+            if constexpr (OUT == OUT_F32) {
+                uint4* const b4 = reinterpret_cast<uint4*>(obuf);
+                for (int rr = 0; rr < G; ++rr)
+                    for (int q = q0 + lane; q <= q1; q += 32) b4[rr * w4 + q] = make_uint4(0u, 0u, 0u, 0u);
+            } else {
+                uint2* const b2 = reinterpret_cast<uint2*>(obuf);
+                for (int rr = 0; rr < G; ++rr)
+                    for (int q = q0 + lane; q <= q1; q += 32) b2[rr * w4 + q] = make_uint2(0u, 0u);
+            }
             __syncwarp();
         }
     }
@@ -301,7 +331,8 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
                 const unsigned rest = bal & (bal - 1u);
                 const int sb = rest ? __ffs(rest) - 1 : sa;
                 const ObjI A = shfl_obj(mine, sa), B = shfl_obj(mine, sb);
-                sparse_group<ACCUM, DIGEST>(buf, gdst, gindex, y0, nrows, W, A, B, rest != 0u, kneg, k, lane, ux0, ux1, dg);
+                sparse_group<ACCUM, DIGEST, OUT>(obuf, gdst, gindex, y0, nrows, W, A, B, rest != 0u, kneg, k, lane, ux0, ux1,
+                                                 dg);
             }
         } else {
             finish = true;
@@ -348,14 +379,15 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
     }
     if (finish && ux1 >= ux0) {
         for (int rr = 0; rr < nrows; ++rr)
-            finish_row<ACCUM, DIGEST>(buf + rr * W, gdst + (long long)rr * W, gindex + (long long)rr * W, ux0, ux1, kneg, k,
-                                      lane, dg);
+            finish_row<ACCUM, DIGEST, OUT>(buf + rr * W, gdst + (long long)rr * W,
+                                           reinterpret_cast<unsigned short*>(obuf) + rr * W, gindex + (long long)rr * W, ux0,
+                                           ux1, kneg, k, lane, dg);
     }
     if constexpr (!ACCUM) {
         fence_proxy_async();  // my generic-proxy writes to `buf` -> visible to the bulk-copy engine
         __syncwarp();
         if (lane == 0) {
-            bulk_store(gdst, buf, (unsigned)(nrows * W * 4));
+            bulk_store(gdst, obuf, (unsigned)(nrows * W * ES));
             bulk_commit();
         }
         if (ws.cur) {
@@ -478,8 +510,8 @@ __device__ __forceinline__ unsigned long long group_bits(const ObjI& o, int uy0,
 
 // K4a for the groups whose bit is set in `z` (untouched ones): each maximal run leaves as bulk stores of the zero tile.
 // Called by lanes in parallel: lane `g` starts the run that begins at group g (and g + 32).
-__device__ __forceinline__ void zero_runs(unsigned long long z, int lane, float* __restrict__ plane_ptr, int uy0, int uy1,
-                                          int W, int G, const float4* zero_tile) {
+__device__ __forceinline__ void zero_runs(unsigned long long z, int lane, char* __restrict__ plane_b, int uy0, int uy1,
+                                          int W, int G, int es, const float4* zero_tile) {
     bool any = false;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -489,8 +521,8 @@ __device__ __forceinline__ void zero_runs(unsigned long long z, int lane, float*
             const unsigned long long inv = ~(z >> g);
             const int run = inv ? __ffsll((long long)inv) - 1 : 64 - g;
             const int r0 = uy0 + g * G, r1 = min(r0 + run * G, uy1);
-            char* dst = reinterpret_cast<char*>(plane_ptr + (long long)r0 * W);
-            int bytes = (r1 - r0) * W * 4;
+            char* dst = plane_b + (long long)r0 * W * es;
+            int bytes = (r1 - r0) * W * es;
             while (bytes > 0) {
                 const int c = min(bytes, kGZeroBytes);
                 bulk_store(dst, zero_tile, (unsigned)c);
@@ -539,8 +571,9 @@ __device__ unsigned long long* g_trace = nullptr;
 __device__ long long g_trace_units = 0;
 #endif
 
-template <bool ACCUM, int SRC, bool DIGEST>
+template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32>
 __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const RenderParams p) {
+    constexpr int ES = (OUT == OUT_F32) ? 4 : 2;  // bytes per heatmap element
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float4* const zero_tile = reinterpret_cast<float4*>(smem_raw);
     const int stage = p.stage_bytes;  // G*W*4 rounded up to 128
@@ -572,7 +605,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         int uy0, uy1;
         bool count_skips;
         const int nscan = unit_header<SRC>(p, u, G, us, uy0, uy1, count_skips);
-        float* const plane_ptr = p.heat + us.plane * plane_elems;
+        char* const plane_b = reinterpret_cast<char*>(p.heat) + us.plane * plane_elems * ES;
         const int ngroups = (uy1 - uy0 + G - 1) / G;
         float kk = p.k;
         bool kneg = kneg0;
@@ -633,7 +666,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         if constexpr (!ACCUM) {  // K4a: untouched runs, by warp 7 (it gets the fewest striped groups in a short unit)
             if (warp == kGWarps - 1) {
                 const unsigned long long valid = ngroups >= 64 ? ~0ull : ((1ull << ngroups) - 1ull);
-                zero_runs(~mask & valid, lane, plane_ptr, uy0, uy1, W, G, zero_tile);
+                zero_runs(~mask & valid, lane, plane_b, uy0, uy1, W, G, ES, zero_tile);
             }
         }
         // K3/K4b: touched groups, striped over the warps; no block barrier in here
@@ -643,8 +676,8 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
             const int g = __ffsll((long long)gm) - 1;
             gm &= gm - 1ull;
             const int y0 = uy0 + g * G;
-            render_group<ACCUM, SRC, DIGEST>(p, ws, plane_ptr, plane_index0, y0, min(G, uy1 - y0), W, G, kneg, kk, lane, small, mine,
-                                             s_unit, ucnt, us, dg);
+            render_group<ACCUM, SRC, DIGEST, OUT>(p, ws, plane_b, plane_index0, y0, min(G, uy1 - y0), W, G, kneg, kk, lane, small,
+                                                  mine, s_unit, ucnt, us, dg);
         }
 #ifdef DH_TRACE_UNITS
         if (lane == 0 && g_trace && u < g_trace_units) {

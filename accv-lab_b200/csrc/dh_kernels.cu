@@ -18,6 +18,8 @@
 //   K4  write           : every pixel is stored exactly once with 128-bit coalesced stores; zero-init is
 //                         fused (FRESH mode writes zeros where nothing was drawn and never reads).
 // No tensor cores: this is HBM-write-bound byte work, not a contraction.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdlib.h>
 #include <stdint.h>
@@ -664,20 +666,27 @@ static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail ti
 // ~192 KB when the problem is large (amortises the per-unit list build; with the tail tier of half-size units the measured
 // optimum on cfg5 is 2 units per plane: 1.600 vs 1.631 ms for 3), smaller when it
 // is not, so that every resident CTA slot still sees several units.
-static void make_groups_plan(RenderParams& p, long long max_ctas) {
+// `es` = bytes per heatmap element (4, or 2 for the 16-bit planes: rows per group still follow the fp32 scratch).
+// Returns false when 16-bit planes cannot be cut into 16-byte aligned groups.
+static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4) {
     // rows per group: as many as a staging buffer holds while DH_G_MINB CTAs still fit the SM's shared memory
     const long long smem_budget = (227ll * 1024) / DH_G_MINB - 1024;
     const long long stage_budget = (smem_budget - (long long)groups_smem_bytes(0)) / (2 * kGWarps);
     int G = (int)((stage_budget < kGStageCap ? stage_budget : kGStageCap) / (p.W * 4));
     if (G < 1) G = 1;
     if (G > p.H) G = p.H;
+    if (es == 2) {  // bulk stores move multiples of 16 bytes from 16-byte aligned addresses
+        if (((long long)p.H * p.W) % 8 != 0) return false;
+        if (p.W % 8 != 0) G &= ~1;
+        if (G < 1) return false;
+    }
     p.band_cols = G;  // rows per group
     p.band_rows = G;
     const int groups_y = (p.H + G - 1) / G;
     p.bands_y = groups_y;
     p.bands_x = 1;
     p.bands_per_plane = groups_y;
-    const long long group_bytes = (long long)G * p.W * 4;
+    const long long group_bytes = (long long)G * p.W * es;
     const long long total_groups = p.num_planes * groups_y;
     // units per resident CTA slot: 4, or 8 when samples can hold many objects (units are then compute-heavy and of
     // similar cost, so the last, partly filled wave is expensive: cfg4 ran 4.1 waves of 1024-object units)
@@ -722,10 +731,11 @@ static void make_groups_plan(RenderParams& p, long long max_ctas) {
     }
     p.tier1_units = p.tier1_planes * p.units_per_plane;
     p.total_units = p.tier1_units + (p.num_planes - p.tier1_planes) * p.units_per_plane2;
-    p.stage_bytes = (int)((group_bytes + 127) & ~127ll);
+    p.stage_bytes = (int)(((long long)G * p.W * 4 + 127) & ~127ll);
+    return true;
 }
 
-template <bool ACCUM, int SRC, bool DIGEST>
+template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32>
 static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     static bool attr_set_dev[64] = {false};  // function attributes are per device: one process may drive several GPUs
     int dev = 0;
@@ -733,13 +743,13 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     bool& attr_set = attr_set_dev[dev];
     if (!attr_set) {
         const int cap = (int)groups_smem_bytes(kGStageCap);  // widest map: fewer CTAs per SM then
-        cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST>,
+        cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST, OUT>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
     const long long max_ctas = (long long)sms * DH_G_MINB;
-    make_groups_plan(p, max_ctas);
+    if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2)) return DH_ERR_UNSUPPORTED_SHAPE;
     if (p.total_units == 0) return DH_OK;
     // Flat grid, one CTA per unit: the block scheduler hands units out dynamically and in address order, which
     // balances SMs that see different effective store bandwidth; a static grid-stride loop runs at the pace of the
@@ -749,7 +759,7 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     p.use_clc = !g_persistent && !g_no_clc && g <= 0x7fffffffll;  // a clamped grid falls back to the static stride
     if (g_persistent && g > max_ctas) g = max_ctas;
     if (g > 0x7fffffffll) g = 0x7fffffffll;
-    groups_kernel<ACCUM, SRC, DIGEST><<<(int)g, kGThreads, groups_smem_bytes(p.stage_bytes), stream>>>(p);
+    groups_kernel<ACCUM, SRC, DIGEST, OUT><<<(int)g, kGThreads, groups_smem_bytes(p.stage_bytes), stream>>>(p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return (int)cudaGetLastError();
 }
@@ -788,6 +798,18 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
     else render_kernel<1, false, SRC><<<grid, kThreads, 0, stream>>>(p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return (int)cudaGetLastError();
+}
+
+// FRESH render into fp16 / bf16 planes: main renderer only.
+template <int SRC>
+static int launch_render16(cudaStream_t stream, RenderParams& p, int out_dtype) {
+    DeviceInfo di;
+    int st = device_info(di);
+    if (st != DH_OK) return st;
+    if (!((p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0) && p.W <= kGMaxW))
+        return DH_ERR_UNSUPPORTED_SHAPE;
+    if (out_dtype == DH_OUT_F16) return launch_groups<false, SRC, false, OUT_F16>(stream, p, di.sms);
+    return launch_groups<false, SRC, false, OUT_BF16>(stream, p, di.sms);
 }
 
 // FRESH render of symmetric integer windows with per-object weights and per-class peaks through the main renderer
@@ -946,6 +968,46 @@ int dh_draw_heatmap_batched_from_boxes_digest(void* stream, float* heatmap, cons
     return batched_common(stream, heatmap, nullptr, nullptr, centers_xy, bboxes_xyxy, out_size_factor, nums_targets,
                           nums_dtype, labels, batch_size, max_num_targets, num_classes, height, width,
                           diameter_to_sigma_factor, k_scale, DH_MODE_FRESH, status, digest_out3, index_base);
+}
+
+int dh_render_heatmap_batched_16(void* stream, void* heatmap, int out_dtype, const int32_t* centers, const int32_t* radii,
+                                 const float* centers_xy, const float* bboxes_xyxy, float out_size_factor,
+                                 const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t B, int64_t T,
+                                 int64_t C, int64_t H, int64_t W, float factor, float k, dh_status* status) {
+    if (out_dtype != DH_OUT_F16 && out_dtype != DH_OUT_BF16) return DH_ERR_INVALID_ARGUMENT;
+    if (B < 0 || T < 0) return DH_ERR_INVALID_ARGUMENT;
+    if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
+    const bool boxes = (centers_xy != nullptr) || (bboxes_xyxy != nullptr);
+    if (boxes && (centers != nullptr || radii != nullptr)) return DH_ERR_INVALID_ARGUMENT;  // one source, not both
+    if (labels == nullptr) C = 1;
+    if (C < 0 || C > INT32_MAX) return DH_ERR_INVALID_ARGUMENT;
+    if (C == 0) return DH_OK;
+    int st = dh::check_shape(H, W);
+    if (st != DH_OK) return st;
+    if (B == 0) return DH_OK;
+    if (T > INT32_MAX) return DH_ERR_UNSUPPORTED_SHAPE;
+    if (!heatmap || !nums_targets) return DH_ERR_INVALID_ARGUMENT;
+    if (T > 0 && (boxes ? (!centers_xy || !bboxes_xyxy) : (!centers || !radii))) return DH_ERR_INVALID_ARGUMENT;
+    dh::RenderParams p{};
+    p.heat = reinterpret_cast<float*>(heatmap);
+    p.centers = centers;
+    p.radii = radii;
+    p.centers_f = centers_xy;
+    p.bboxes_f = bboxes_xyxy;
+    p.osf = out_size_factor;
+    p.labels = labels;
+    p.sizes = nums_targets;
+    p.sizes_i64 = (nums_dtype == DH_SIZES_I64);
+    p.num_planes = B * C;
+    p.C = (int)C;
+    p.T = (int)T;
+    p.H = (int)H;
+    p.W = (int)W;
+    p.factor = factor;
+    p.k = k;
+    p.status = status;
+    if (boxes) return dh::launch_render16<dh::SRC_BOXES>((cudaStream_t)stream, p, out_dtype);
+    return dh::launch_render16<dh::SRC_BATCHED>((cudaStream_t)stream, p, out_dtype);
 }
 
 // Flat path: direct scan when (units x objects) is small, else counting sort by plane.

@@ -81,8 +81,15 @@ void draw_heatmap(at::Tensor& heatmaps, const at::Tensor& centers, const at::Ten
 }
 
 // ---- batched entries (draw_heatmap_cuda.cu:91-165) ---------------------------------------------------------
+// 16-bit planes (b200 additions only): 0 for float32, else the DH_OUT_* tag
+int out16_tag(const at::Tensor& heatmap) {
+    if (heatmap.scalar_type() == at::kHalf) return DH_OUT_F16;
+    if (heatmap.scalar_type() == at::kBFloat16) return DH_OUT_BF16;
+    return 0;
+}
+
 void batched_checks(const at::Tensor& heatmap, const at::Tensor& centers, const at::Tensor& radii,
-                    const at::Tensor& nums_targets, const at::Tensor* labels) {
+                    const at::Tensor& nums_targets, const at::Tensor* labels, bool allow16 = false) {
     CHECK_INPUT(heatmap);
     CHECK_INPUT(centers);
     CHECK_INPUT(radii);
@@ -107,7 +114,7 @@ void batched_checks(const at::Tensor& heatmap, const at::Tensor& centers, const 
         CHECK_DTYPE(labels_, at::kInt);
         CHECK_SAME_DEVICE(labels_, heatmap);
     }
-    CHECK_DTYPE(heatmap, at::kFloat);
+    if (!(allow16 && out16_tag(heatmap) != 0)) CHECK_DTYPE(heatmap, at::kFloat);
     CHECK_SAME_DEVICE(centers, heatmap);
     CHECK_SAME_DEVICE(radii, heatmap);
     CHECK_SAME_DEVICE(nums_targets, heatmap);
@@ -115,7 +122,7 @@ void batched_checks(const at::Tensor& heatmap, const at::Tensor& centers, const 
 
 void batched_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tensor& radii, const at::Tensor& nums_targets,
                   const at::Tensor* labels, float factor, float k, int mode) {
-    batched_checks(heatmap, centers, radii, nums_targets, labels);
+    batched_checks(heatmap, centers, radii, nums_targets, labels, mode == DH_MODE_FRESH);
     CHECK_DTYPE(centers, at::kInt);
     CHECK_DTYPE(radii, at::kInt);
     c10::cuda::CUDAGuard guard(heatmap.device());
@@ -123,6 +130,15 @@ void batched_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tens
     int tag = 0;
     const void* sizes = sizes_ptr(nums_targets, tag);
     const bool cw = labels != nullptr;
+    if (const int o16 = out16_tag(heatmap)) {  // fp16 / bf16 planes: FRESH only
+        check_status(dh_render_heatmap_batched_16(stream.stream(), heatmap.data_ptr(), o16, centers.data_ptr<int>(),
+                                                  radii.data_ptr<int>(), nullptr, nullptr, 1.0f, sizes, tag,
+                                                  cw ? labels_ptr(*labels) : nullptr, heatmap.size(0), radii.size(1),
+                                                  cw ? heatmap.size(1) : 1, heatmap.size(cw ? 2 : 1),
+                                                  heatmap.size(cw ? 3 : 2), factor, k, nullptr),
+                     "render_heatmap_batched (16-bit planes)");
+        return;
+    }
     check_status(dh_draw_heatmap_batched(stream.stream(), heatmap.data_ptr<float>(), centers.data_ptr<int>(),
                                          radii.data_ptr<int>(), sizes, tag, cw ? labels_ptr(*labels) : nullptr,
                                          heatmap.size(0), radii.size(1), cw ? heatmap.size(1) : 1,
@@ -195,7 +211,8 @@ void render_heatmap_from_boxes(at::Tensor& heatmaps, const at::Tensor& centers, 
     CHECK_INPUT(heatmaps);
     CHECK_INPUT(centers);
     CHECK_INPUT(nums_targets);
-    CHECK_DTYPE(heatmaps, at::kFloat);
+    const int o16 = fresh ? out16_tag(heatmaps) : 0;
+    if (o16 == 0) CHECK_DTYPE(heatmaps, at::kFloat);
     TORCH_CHECK(nums_targets.dim() == 1 && nums_targets.size(0) == heatmaps.size(0) && centers.size(0) == heatmaps.size(0),
                 "batch_size (dim 0) need to be the same for all inputs");
     CHECK_SAME_DEVICE(centers, heatmaps);
@@ -216,6 +233,16 @@ void render_heatmap_from_boxes(at::Tensor& heatmaps, const at::Tensor& centers, 
     auto stream = at::cuda::getCurrentCUDAStream();
     int tag = 0;
     const void* sizes = sizes_ptr(nums_targets, tag);
+    if (o16 != 0) {  // fp16 / bf16 planes: FRESH only
+        check_status(dh_render_heatmap_batched_16(stream.stream(), heatmaps.data_ptr(), o16, nullptr, nullptr,
+                                                  centers.data_ptr<float>(), bboxes.data_ptr<float>(),
+                                                  (float)out_size_factor, sizes, tag, cw ? labels_ptr(*lab) : nullptr,
+                                                  heatmaps.size(0), centers.size(1), cw ? heatmaps.size(1) : 1,
+                                                  heatmaps.size(cw ? 2 : 1), heatmaps.size(cw ? 3 : 2),
+                                                  diameter_to_sigma_factor, k_scale, nullptr),
+                     "render_heatmap_from_boxes (16-bit planes)");
+        return;
+    }
     check_status(dh_draw_heatmap_batched_from_boxes(
                      stream.stream(), heatmaps.data_ptr<float>(), centers.data_ptr<float>(), bboxes.data_ptr<float>(),
                      (float)out_size_factor, sizes, tag, cw ? labels_ptr(*lab) : nullptr, heatmaps.size(0),

@@ -129,6 +129,23 @@ int dh_draw_heatmap_batched_from_boxes_digest(void* stream, float* heatmap, cons
                                               float k_scale, int64_t index_base, uint64_t* digest_out3,
                                               dh_status* status);
 
+/* ---- 16-bit heatmap planes (not in the reference, whose heatmaps are float32 only:
+ * draw_heatmap_cuda.cu:84,117,160 `data_ptr<float>()`) -------------------------------------
+ * DH_MODE_FRESH render into fp16 or bf16 planes: every value is computed in fp32 exactly as by the fp32 entries and
+ * rounded once (to nearest even) when it is stored, so the result equals the fp32 result cast to the 16-bit type,
+ * bit for bit; half the output bytes. Objects come EITHER from (centers i32 [B,T,2], radii i32 [B,T]) OR from float
+ * boxes (centers_xy f32 [B,T,2], bboxes_xyxy f32 [B,T,4], out_size_factor) — pass the other pair as NULL.
+ * Shapes: width % 4 == 0, width <= 1024, (height*width) % 8 == 0, heatmap base 16-byte aligned; anything else
+ * returns DH_ERR_UNSUPPORTED_SHAPE (render fp32 and convert). No accumulate mode, no fused digest. */
+#define DH_OUT_F16 1
+#define DH_OUT_BF16 2
+int dh_render_heatmap_batched_16(void* stream, void* heatmap, int out_dtype, const int32_t* centers,
+                                 const int32_t* radii, const float* centers_xy, const float* bboxes_xyxy,
+                                 float out_size_factor, const void* nums_targets, int nums_dtype,
+                                 const int32_t* labels, int64_t batch_size, int64_t max_num_targets,
+                                 int64_t num_classes, int64_t height, int64_t width, float diameter_to_sigma_factor,
+                                 float k_scale, dh_status* status);
+
 /* ---- flat entry (concatenated objects + per-object plane index) ----------------------
  * Replaces draw_heatmap_cuda(cudaStream_t, float*, const int*, const int*, const int*, int H, int W,
  *   float factor, float k, int N, int M) (draw_heatmap_cuda.cu:29-41; kernel cuh:51-74).

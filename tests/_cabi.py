@@ -36,6 +36,8 @@ SIGNATURES = {
                                                 _i, _p, _p, _p]),
     "dh_draw_heatmap_batched_from_boxes_digest": (_i, [_p, _p, _p, _p, _f, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f,
                                                        _f, _i64, _p, _p]),
+    "dh_render_heatmap_batched_16": (_i, [_p, _p, _i, _p, _p, _p, _p, _f, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f,
+                                          _p]),
     "dh_draw_heatmap_workspace_bytes": (_sz, [_i64, _i64]),
     "dh_draw_heatmap": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _i, _p, _sz, _p]),
     "dh_checksum": (_i, [_p, _p, _i64, _i64, _p]),
@@ -130,6 +132,30 @@ def draw_from_boxes(lib, heat, centers_f, bboxes_f, osf, sizes, labels=None, fac
                                                 ptr(radii_out), None)
     check(lib, st, "dh_draw_heatmap_batched_from_boxes")
     return heat
+
+
+DH_OUT_F16, DH_OUT_BF16 = 1, 2
+
+
+def render16(lib, heat, sizes, labels=None, centers=None, radii=None, centers_f=None, bboxes_f=None, osf=1.0, factor=6.0,
+             k=1.0, status=None, check_status=True):
+    """dh_render_heatmap_batched_16 into a float16 / bfloat16 CUDA tensor (FRESH)."""
+    import torch
+
+    src = radii if radii is not None else centers_f
+    B, T = src.shape[:2]
+    if labels is not None:
+        C, H, W = heat.shape[1:]
+    else:
+        C, (H, W) = 1, heat.shape[1:]
+    tag = DH_SIZES_I64 if sizes.dtype == torch.int64 else DH_SIZES_I32
+    out = DH_OUT_F16 if heat.dtype == torch.float16 else DH_OUT_BF16
+    st = lib.dh_render_heatmap_batched_16(stream_ptr(), ptr(heat), out, ptr(centers), ptr(radii), ptr(centers_f),
+                                          ptr(bboxes_f), osf, ptr(sizes), tag, ptr(labels), B, T, C, H, W, factor, k,
+                                          ptr(status))
+    if check_status:
+        check(lib, st, "dh_render_heatmap_batched_16")
+    return st
 
 
 def draw_from_boxes_digest(lib, heat, centers_f, bboxes_f, osf, sizes, labels=None, factor=6.0, k=1.0, index_base=0,
