@@ -43,7 +43,8 @@ def cuda_sources():
 
 def build_cuda_lib(force=False, verbose_ptxas=False):
     srcs = cuda_sources()
-    deps = srcs + [os.path.join(INCLUDE, "dh_b200.h")]
+    deps = srcs + [os.path.join(INCLUDE, "dh_b200.h")] + sorted(
+        os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh"))  # headers the .cu files include
     if force or not _fresh(LIB_PATH, deps):
         cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose_ptxas else []) + ["-shared", f"-I{INCLUDE}"] + srcs + [
             "-o", LIB_PATH, "-lcudart"]

@@ -167,6 +167,7 @@ __device__ __forceinline__ void sparse_group(unsigned* __restrict__ buf, float* 
     const int ax0 = max(A.x - A.r, 0), ax1 = min(A.x + A.r, W - 1);
     const int bx0 = max(B.x - B.r, 0), bx1 = min(B.x + B.r, W - 1);
     const float aw = kneg ? -A.w : A.w, bw = kneg ? -B.w : B.w;
+    const float fra = (float)A.r, frb = (float)B.r;
     for (int rr = 0; rr < nrows; ++rr) {
         const int dya = y0 + rr - A.y, dyb = y0 + rr - B.y;
         const bool inA = abs(dya) <= A.r, inB = hasB && abs(dyb) <= B.r;  // warp-uniform
@@ -178,21 +179,14 @@ __device__ __forceinline__ void sparse_group(unsigned* __restrict__ buf, float* 
         ux0 = min(ux0, rx0);
         ux1 = max(ux1, rx1);
         for (int xb = rx0; xb <= rx1; xb += 32) {
+            // branch-free: both candidates are evaluated (B is a copy of A when there is one object), then selected
             const int x = xb + lane;
-            const int dxa = x - A.x, dxb = x - B.x;
-            float acc = 0.0f;
-            bool touched = false;
-            if (inA && abs(dxa) <= A.r) {
-                const float fdx = (float)dxa;
-                acc = __fmul_rn(__fadd_rn(fia, __fmul_rn(fdx, fdx)), aw);
-                touched = true;
-            }
-            if (inB && abs(dxb) <= B.r) {
-                const float fdx = (float)dxb;
-                const float m = __fmul_rn(__fadd_rn(fib, __fmul_rn(fdx, fdx)), bw);
-                acc = touched ? fminf(acc, m) : m;
-                touched = true;
-            }
+            const float fdxa = (float)(x - A.x), fdxb = (float)(x - B.x);  // exact (|dx| < 2^24)
+            const float ma = __fmul_rn(__fadd_rn(fia, __fmul_rn(fdxa, fdxa)), aw);
+            const float mb = __fmul_rn(__fadd_rn(fib, __fmul_rn(fdxb, fdxb)), bw);
+            const bool ta = inA && fabsf(fdxa) <= fra, tb = inB && fabsf(fdxb) <= frb;
+            const float acc = ta ? (tb ? fminf(ma, mb) : ma) : mb;
+            const bool touched = ta || tb;
             if (touched && x <= rx1) {
                 const float v = __fmul_rn(expf(kneg ? acc : -acc), k);  // = expf(-m) * k
                 if constexpr (ACCUM) {
@@ -306,15 +300,25 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
         __syncwarp();
         const int cx0 = ws.cur ? ws.c1x0 : ws.c0x0, cx1 = ws.cur ? ws.c1x1 : ws.c0x1;
         if (cx1 >= cx0) {  // back to all-zero: clear only what its last use wrote (4 pixels per store, W % 4 == 0)
-            const int q0 = cx0 >> 2, q1 = cx1 >> 2, w4 = W >> 2;
+            const int q0 = cx0 >> 2, nq = (cx1 >> 2) - q0 + 1, w4 = W >> 2;
             if constexpr (OUT == OUT_F32) {
-                uint4* const b4 = reinterpret_cast<uint4*>(obuf);
-                for (int rr = 0; rr < G; ++rr)
-                    for (int q = q0 + lane; q <= q1; q += 32) b4[rr * w4 + q] = make_uint4(0u, 0u, 0u, 0u);
+                uint4* const b4 = reinterpret_cast<uint4*>(obuf) + q0 + lane;
+                if (nq <= 32) {  // the usual case (span <= 128 pixels): one store per row
+                    if (lane < nq)
+                        for (int rr = 0; rr < G; ++rr) b4[rr * w4] = make_uint4(0u, 0u, 0u, 0u);
+                } else {
+                    for (int rr = 0; rr < G; ++rr)
+                        for (int q = lane; q < nq; q += 32) b4[rr * w4 + q - lane] = make_uint4(0u, 0u, 0u, 0u);
+                }
             } else {
-                uint2* const b2 = reinterpret_cast<uint2*>(obuf);
-                for (int rr = 0; rr < G; ++rr)
-                    for (int q = q0 + lane; q <= q1; q += 32) b2[rr * w4 + q] = make_uint2(0u, 0u);
+                uint2* const b2 = reinterpret_cast<uint2*>(obuf) + q0 + lane;
+                if (nq <= 32) {
+                    if (lane < nq)
+                        for (int rr = 0; rr < G; ++rr) b2[rr * w4] = make_uint2(0u, 0u);
+                } else {
+                    for (int rr = 0; rr < G; ++rr)
+                        for (int q = lane; q < nq; q += 32) b2[rr * w4 + q - lane] = make_uint2(0u, 0u);
+                }
             }
             __syncwarp();
         }
