@@ -118,20 +118,52 @@ __device__ __forceinline__ bool gs_make(const GsParams& p, long long i, int cls,
 
 constexpr int kGsZeroBytes = 8192;  // constant zero tile of the FRESH mode
 
+// log(a) for the focal loss: a = pred + eps or 1 - pred + eps, i.e. a positive normal float. a = m * 2^e with m in
+// [2/3, 4/3), log(m) = f + f^2 P(f) with f = m - 1 and P a degree-7 polynomial fitted to (log1p(f) - f) / f^2 (minimax in
+// the relative error of log1p), everything in FMAs: 17 instructions instead of the ~30 of logf (which was a third of the
+// loss launch), at the same accuracy — max 1.05 ulp over all normal floats, 0.58 ulp around 1, exact 0 at 1
+// (tests/test_focal_loss.py restates it in numpy and checks it against float64 log). Outside the normal range the
+// result is patched by selects (no call: the loss body is unrolled 16 times): +0 / -0 and denormals (counted as 0) ->
+// -inf, +inf -> +inf, negative or NaN -> NaN.
+__device__ __forceinline__ float log_pos(float a) {
+    const int ia = __float_as_int(a);
+    const int e = (ia - 0x3f2aaaab) & (int)0xff800000;
+    const float m = __int_as_float(ia - e);
+    const float i = __fmul_rn((float)e, 1.1920928955078125e-07f);  // exponent as a float (e / 2^23)
+    const float f = __fadd_rn(m, -1.0f);                           // exact
+    const float s = __fmul_rn(f, f);
+    float q = __int_as_float(0x3e0fa12d);
+    q = fmaf(q, f, __int_as_float(0xbe1d9426));
+    q = fmaf(q, f, __int_as_float(0x3e0f512f));
+    q = fmaf(q, f, __int_as_float(0xbe281974));
+    q = fmaf(q, f, __int_as_float(0x3e4cea14));
+    q = fmaf(q, f, __int_as_float(0xbe800a40));
+    q = fmaf(q, f, __int_as_float(0x3eaaaa7d));
+    q = fmaf(q, f, __int_as_float(0xbeffffeb));
+    const float r = fmaf(i, 0.693147182f, fmaf(q, s, f));
+    if (a >= 1.17549435e-38f && a <= 3.40282347e38f) return r;
+    return (a >= 0.0f) ? (a > 1.0f ? __int_as_float(0x7f800000) : __int_as_float((int)0xff800000)) : __int_as_float(0x7fc00000);
+}
+
 // FRESH (no input heatmap, PX == 4): runs of untouched bands leave as bulk stores (SASS UBLKCP) from a zero tile, issued
 // by the lanes of warp 0 in parallel — no LSU or register traffic for the bytes nobody draws on.
 // LOSS (N3): nothing is drawn to memory. p.in is the prediction, the target value of every pixel is formed in registers
 // as in the FRESH renderer and consumed at once by the Gaussian focal loss (DH/docs/intro.rst:7-26); p.out (optional)
 // receives d loss / d pred; per-unit partial sums make the reduction order independent of the block scheduler.
-// LOSS_MODE: 0 = renderer; 1 = alpha 2 / gamma 4, IEEE-accurate log and division; 2 = same through the special-function
-// unit (__logf, __fdividef); 3 = general exponents (powf). Compile-time so that each variant's code stays small: a
-// run-time switch tripled the unrolled loss body and the kernel stalled on instruction fetch (ncu: no_instruction 2.8).
+// LOSS_MODE: 0 = renderer; 1 = alpha 2 / gamma 4, 1-ulp log (log_pos); 2 = same through the special-function
+// unit (__logf); 3 = general exponents (powf); 4, 5, 6 = the same three without d loss / d pred (forward only: the
+// gradient's division and extra products were 16 % of the forward launch's instructions). Compile-time so that each
+// variant's code stays small: a run-time switch tripled the unrolled loss body and the kernel stalled on instruction
+// fetch (ncu: no_instruction 2.8). The gradient's quotient is __fdividef (2 ulp) in every mode: there is no reference
+// value to match bit for bit, and the IEEE division cost 14 instructions per pixel.
 template <int PX, bool INPLACE, bool FRESH, int LOSS_MODE = 0>
 __global__ void __launch_bounds__(kGsThreads, LOSS_MODE ? 2 : (PX == 4 ? 3 : 4)) gaussians_kernel(const GsParams p) {
     constexpr bool LOSS = LOSS_MODE != 0;
     if (p.gate != nullptr && *p.gate == 0) return;
-    constexpr bool std_exp = LOSS_MODE == 1 || LOSS_MODE == 2;
-    constexpr bool FAST = LOSS_MODE == 2;
+    constexpr bool GRAD = LOSS_MODE >= 1 && LOSS_MODE <= 3;
+    constexpr int LM = LOSS_MODE > 3 ? LOSS_MODE - 3 : LOSS_MODE;
+    constexpr bool std_exp = LM == 1 || LM == 2;
+    constexpr bool FAST = LM == 2;
     __shared__ GObj s_list[kGsListCap];
     __shared__ int s_cnt;
     __shared__ __align__(128) float4 s_zero[FRESH ? kGsZeroBytes / 16 : 1];
@@ -323,39 +355,44 @@ __global__ void __launch_bounds__(kGsThreads, LOSS_MODE ? 2 : (PX == 4 ? 3 : 4))
                     if constexpr (LOSS) {
                         // v[] = prediction. Target of the pixel exactly as the FRESH renderer would have stored it, then
                         //   target == 1: loss = -(1-p)^alpha log(p+eps);  else: loss = -p^alpha log(1-p+eps) (1-target)^gamma
+                        // Branch-free (one logarithm per pixel, the four pixels of the item independent of each other: the
+                        // two-sided version ran at 54 % issue-active on dependency and instruction-fetch stalls):
+                        //   pos = target == 1;  a = pos ? p : 1-p;  b = pos ? 1-p : p;  w = pos ? 1 : (1-target)^gamma
+                        //   loss = -log(a+eps) b^alpha w;   d loss / d p = (pos ? -1 : 1) w (b^alpha / (a+eps) - alpha b^(alpha-1) log(a+eps))
                         float lq = 0.0f;
+                        float tg[PX];
+#pragma unroll
+                        for (int j = 0; j < PX; ++j) tg[j] = 0.0f;
+                        if (tq != 0u) {  // one expf per pixel of a touched item; untouched pixels hold +inf -> expf(-inf) = 0
+#pragma unroll
+                            for (int j = 0; j < PX; ++j) {
+                                const float val = __fmul_rn(expf(-best[q][j]), k);
+                                tg[j] = ((tq & (1u << j)) && !(0.0f >= val)) ? val : 0.0f;
+                            }
+                        }
 #pragma unroll
                         for (int j = 0; j < PX; ++j) {
-                            float tg = 0.0f;
-                            if (tq & (1u << j)) {
-                                const float val = __fmul_rn(expf(-best[q][j]), k);
-                                tg = (0.0f >= val) ? 0.0f : val;
-                            }
                             const float pr = v[j], om = 1.0f - pr;
-                            float loss, g;
-                            if (tg == 1.0f) {
-                                const float den = pr + p.eps, lg = FAST ? __logf(den) : logf(den);
-                                const float pw = std_exp ? om * om : powf(om, p.alpha);
-                                const float pw1 = std_exp ? om : powf(om, p.alpha - 1.0f);
-                                loss = -lg * pw;
-                                g = p.alpha * pw1 * lg - (FAST ? __fdividef(pw, den) : pw / den);
-                                npos += 1;
-                            } else {
-                                const float den = om + p.eps, lg = FAST ? __logf(den) : logf(den);
-                                const float pa = std_exp ? pr * pr : powf(pr, p.alpha);
-                                const float pa1 = std_exp ? pr : powf(pr, p.alpha - 1.0f);
-                                const float ot = 1.0f - tg, ot2 = ot * ot;
-                                const float wgt = std_exp ? ot2 * ot2 : powf(ot, p.gamma);
-                                loss = -lg * pa * wgt;
-                                g = wgt * ((FAST ? __fdividef(pa, den) : pa / den) - p.alpha * pa1 * lg);
+                            const bool pos = tg[j] == 1.0f;
+                            const float den = (pos ? pr : om) + p.eps, bs = pos ? om : pr;
+                            const float lg = FAST ? __logf(den) : log_pos(den);
+                            const float ot = 1.0f - tg[j], ot2 = ot * ot;
+                            const float wgt = pos ? 1.0f : (std_exp ? ot2 * ot2 : powf(ot, p.gamma));
+                            const float pw = std_exp ? bs * bs : powf(bs, p.alpha);
+                            lq += -lg * pw * wgt;
+                            npos += pos ? 1 : 0;
+                            if constexpr (GRAD) {
+                                const float pw1 = std_exp ? bs : powf(bs, p.alpha - 1.0f);
+                                const float gg = wgt * (__fdividef(pw, den) - p.alpha * pw1 * lg);
+                                v[j] = pos ? -gg : gg;
                             }
-                            lq += loss;
-                            v[j] = g;
                         }
                         lsum += (double)lq;
-                        if (p.out != nullptr) {
-                            if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
-                            else out_plane[idx] = v[0];
+                        if constexpr (GRAD) {
+                            if (p.out != nullptr) {
+                                if constexpr (PX == 4) *reinterpret_cast<float4*>(out_plane + idx) = make_float4(v[0], v[1], v[2], v[3]);
+                                else out_plane[idx] = v[0];
+                            }
                         }
                     } else {
                     if (tq != 0u) {  // one expf per pixel of a touched item, unconditionally: no per-pixel divergence
@@ -835,7 +872,11 @@ extern "C" int dh_gaussian_focal_loss(void* stream, const float* pred, const int
     p.partial_pos = (long long*)((char*)workspace + (((size_t)p.total_units * 8 + 15) & ~(size_t)15));
     const long long g = p.total_units < 0x7fffffffll ? p.total_units : 0x7fffffffll;
     const int mode = (alpha == 2.0f && gamma == 4.0f) ? (fast_math ? 2 : 1) : 3;
-    if (vec) {
+    if (vec && grad_pred == nullptr) {  // forward only
+        if (mode == 1) dh::gaussians_kernel<4, false, false, 4><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else if (mode == 2) dh::gaussians_kernel<4, false, false, 5><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+        else dh::gaussians_kernel<4, false, false, 6><<<(int)g, dh::kGsThreads, 0, s>>>(p);
+    } else if (vec) {
         if (mode == 1) dh::gaussians_kernel<4, false, false, 1><<<(int)g, dh::kGsThreads, 0, s>>>(p);
         else if (mode == 2) dh::gaussians_kernel<4, false, false, 2><<<(int)g, dh::kGsThreads, 0, s>>>(p);
         else dh::gaussians_kernel<4, false, false, 3><<<(int)g, dh::kGsThreads, 0, s>>>(p);

@@ -289,8 +289,9 @@ int dh_gaussian_radius(void* stream, const float* det_hw, double min_overlap, in
  * pred float32 [B,(C),H,W] in (0,1); grad_pred (optional, same shape) receives d loss / d pred per pixel (unscaled);
  * loss_out2 = DEVICE double[2]: { sum of the loss over all pixels, number of pixels with target == 1 } — summed in a
  * fixed order (per-unit partials in `workspace`, then one block), so results are run-to-run identical.
- * fast_math != 0 (alpha = 2, gamma = 4 only): log and division through the special-function unit (__logf,
- * __fdividef; ~1e-6 relative on the sum).
+ * Accuracy: logarithm <= 1.05 ulp (own polynomial, see csrc/dh_gaussians.cu log_pos; arguments below 2^-126 count as
+ * 0), gradient quotient 2 ulp (__fdividef). fast_math != 0 (alpha = 2, gamma = 4 only): logarithm through the
+ * special-function unit (__logf; ~1e-6 relative on the sum). grad_pred == NULL selects forward-only kernels.
  * k_scale > 0; radii in [0, 2048] (others draw nothing). The reference documents the formula but has no implementation:
  * PARITY UNPINNED (oracle = float64 numpy restatement, tests/test_focal_loss.py). Two launches. */
 size_t dh_focal_loss_workspace_bytes(int64_t batch_size, int64_t num_classes, int64_t height, int64_t width);

@@ -14,6 +14,7 @@ from accvlab.draw_heatmap import b200
 from oracle import oracle as orc
 
 dev = torch.device("cuda", 0)
+ROWS = os.environ.get("DH_ROWS", "N1,N2,N3").split(",")  # e.g. DH_ROWS=N3 for one row
 
 def wall(fn, n):
     for _ in range(3): fn()
@@ -31,7 +32,7 @@ def ev(fn, n):
     return a.elapsed_time(b) / n
 
 # ------------------------------------------------------------------ N1
-for name, B in (("cfg2", None), ("cfg3", None), ("cfg5", 3072)):
+for name, B in ((("cfg2", None), ("cfg3", None), ("cfg5", 3072)) if "N1" in ROWS else ()):
     w = workloads.make(name, B=B); cfg = w.cfg
     cf, bf, lab = (torch.from_numpy(a).to(dev) for a in (w.centers_f, w.bboxes_f, w.labels))
     cl = [cf[i, : w.sizes[i]] for i in range(w.B)]
@@ -62,7 +63,7 @@ for name, B in (("cfg2", None), ("cfg3", None), ("cfg5", 3072)):
     print(json.dumps(r), flush=True)
 
 # ------------------------------------------------------------------ N2
-for name, B in (("cfg2", None), ("cfg3", None), ("cfg5", 384)):
+for name, B in ((("cfg2", None), ("cfg3", None), ("cfg5", 384)) if "N2" in ROWS else ()):
     w = workloads.make(name, B=B); cfg = w.cfg
     ci, ri = orc.radius_center(w.centers_f, w.bboxes_f, cfg.osf)
     radii_f = (ri.astype(np.float32) + np.float32(0.37)).astype(np.float32)   # float radii, fractional
@@ -100,7 +101,7 @@ for name, B in (("cfg2", None), ("cfg3", None), ("cfg5", 384)):
     print(json.dumps(r), flush=True)
 
 # ------------------------------------------------------------------ N3
-for name, B in (("cfg3", None), ("cfg5", 384)):
+for name, B in ((("cfg3", None), ("cfg5", 384)) if "N3" in ROWS else ()):
     w = workloads.make(name, B=B); cfg = w.cfg
     d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     sizes, lab = d(w.sizes), d(w.labels)

@@ -1,7 +1,7 @@
 """N3: fused Gaussian-focal-loss consumer. PARITY UNPINNED — the reference documents the formula
 (docs/intro.rst:7-26) but has no implementation. Checked against a float64 numpy evaluation on the ORACLE's target
 heatmap: positives counted exactly, loss sum within 2e-6 relative, gradient within 1e-5 relative / 1e-6 absolute
-(fp32 logf / division on the device vs float64), run-to-run bit-identical (fixed-order reduction), and against
+(fp32 1-ulp log / 2-ulp division on the device vs float64), run-to-run bit-identical (fixed-order reduction), and against
 torch autograd of the unfused formula on the heatmap our renderer draws."""
 import numpy as np
 import pytest
@@ -18,6 +18,47 @@ def test_oracle_formula_known_answers(oracle):
     assert abs(loss - want) < 1e-12 and npos == 1
     assert abs(grad[0, 0] - (2 * 0.5 * np.log(0.5) - 0.25 / 0.5)) < 1e-12
     assert abs(grad[0, 1] - (0.0625 / 0.75 - 2 * 0.25 * np.log(0.75))) < 1e-12
+
+
+_LOG_POS_COEFFS = (0xbeffffeb, 0x3eaaaa7d, 0xbe800a40, 0x3e4cea14, 0xbe281974, 0x3e0f512f, 0xbe1d9426, 0x3e0fa12d)
+
+
+def _log_pos_numpy(x):
+    """`log_pos` of csrc/dh_gaussians.cu restated operation by operation (float32 FMAs emulated through float64: the
+    product of two float32 is exact there)."""
+    c = np.array(_LOG_POS_COEFFS, np.uint32).view(np.float32)
+    fma = lambda a, b, d: (a.astype(np.float64) * b.astype(np.float64) + d.astype(np.float64)).astype(np.float32)
+    ix = x.astype(np.float32).view(np.int32)
+    e = (ix - np.int32(0x3F2AAAAB)) & np.int32(-8388608)
+    m = (ix - e).view(np.float32)
+    i = e.astype(np.float32) * np.float32(2.0 ** -23)
+    f = (m - np.float32(1.0)).astype(np.float32)
+    s = (f * f).astype(np.float32)
+    q = np.full_like(f, c[7])
+    for k in range(6, -1, -1):
+        q = fma(q, f, np.full_like(f, c[k]))
+    return fma(i, np.full_like(f, np.float32(0.693147182)), fma(q, s, f))
+
+
+def test_log_pos_is_a_one_ulp_log():
+    """the loss kernel's logarithm: coefficients as in the CUDA source, <= 1.1 ulp from float64 log on every float32
+    in [0.5, 1.0001] (where 1 - pred + eps lives) and on samples of every binade; exactly 0 at 1"""
+    import os
+
+    src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "accv-lab_b200", "csrc",
+                            "dh_gaussians.cu")).read()
+    for h in _LOG_POS_COEFFS:
+        assert f"0x{h:08x}" in src, f"coefficient 0x{h:08x} not in the CUDA source: test and kernel diverged"
+    rng = np.random.default_rng(0)
+    xs = [np.arange(0x3F000000, 0x3F800400, dtype=np.uint32).view(np.float32),
+          rng.integers(0x00800000, 0x7F7FFFFF, 2_000_000, dtype=np.int64).astype(np.uint32).view(np.float32)]
+    for x in xs:
+        got = _log_pos_numpy(x).astype(np.float64)
+        want = np.log(x.astype(np.float64))
+        ulp = np.abs(np.spacing(want.astype(np.float32)).astype(np.float64))
+        ulp[ulp == 0] = 1.0
+        assert float((np.abs(got - want) / ulp).max()) <= 1.1
+    assert _log_pos_numpy(np.array([1.0], np.float32))[0] == 0.0
 
 
 def test_argument_validation_needs_no_device(cabi):
