@@ -81,6 +81,13 @@ __global__ void __launch_bounds__(256) checksum_kernel(const float* __restrict__
 }
 
 // ---- helper streams of the host entry (per device, created once) ------------------------------------
+static int host_env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+// measurement hooks (read once): growth factor of the input chunks, smallest input size that is pipelined (KiB)
+static const int g_host_growth = host_env_int("DH_HOST_GROWTH", 4);
+static const int g_host_pipeline_kib = host_env_int("DH_HOST_PIPELINE_KIB", 256);
 constexpr int kHostMaxChunks = 16;  // input chunks of the pipelined device-output path
 struct HostCtx {
     bool ready = false;
@@ -228,12 +235,36 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
     // between two render streams so the tail of one launch overlaps the head of the next.
     const size_t slot_bytes = 24 + (has_labels ? 4 : 0);
     const size_t in_bytes = (size_t)B * T * slot_bytes;
-    if (!heatmap_host && in_bytes >= ((size_t)2 << 20) && B >= 2 && chunk_samples >= 0) {
-        int64_t nch = (int64_t)(in_bytes >> 20);  // ~1 MB of inputs per chunk
-        if (chunk_samples > 0) nch = (B + chunk_samples - 1) / chunk_samples;
-        if (nch > dh::kHostMaxChunks) nch = dh::kHostMaxChunks;
-        if (nch > B) nch = B;
-        if (nch < 2) nch = 2;
+    if (!heatmap_host && in_bytes >= ((size_t)dh::g_host_pipeline_kib << 10) && B >= 2 && chunk_samples >= 0) {
+        // Chunk boundaries. Copying a sample's inputs takes ~1/10 of rendering it, so only the FIRST chunk's copy is
+        // exposed: chunks grow geometrically (x4: still hidden at a quarter of the usual PCIe rate) from a first one of
+        // ~100 KB of inputs — cfg5: 36 + 144 + 578 + 2314 samples, 4 launches instead of 8 equal ones (each launch
+        // costs ~10 us of ramp and tail that the next one only partly hides). A caller-given chunk_samples keeps
+        // equal chunks.
+        int64_t bounds[dh::kHostMaxChunks + 1];
+        int64_t nch;
+        if (chunk_samples > 0) {
+            nch = (B + chunk_samples - 1) / chunk_samples;
+            if (nch > dh::kHostMaxChunks) nch = dh::kHostMaxChunks;
+            if (nch > B) nch = B;
+            if (nch < 2) nch = 2;
+            for (int64_t c = 0; c <= nch; ++c) bounds[c] = B * c / nch;
+        } else {
+            const int64_t gr = dh::g_host_growth < 2 ? 2 : dh::g_host_growth;
+            nch = 2;
+            int64_t parts = 1 + gr;  // 1 + gr + ... + gr^(nch-1)
+            while (nch < 6 && in_bytes / (size_t)parts > ((size_t)128 << 10)) {
+                parts = parts * gr + 1;
+                ++nch;
+            }
+            int64_t acc = 0, w = 1;
+            bounds[0] = 0;
+            for (int64_t c = 1; c <= nch; ++c, w *= gr) {
+                acc += w;
+                bounds[c] = (int64_t)((__int128)B * acc / parts);
+            }
+            if (bounds[1] < 1) bounds[1] = 1;  // B >= 2: the first chunk is never empty
+        }
         std::lock_guard<std::mutex> lock(dh::g_ctx_mu);
         dh::HostCtx* ctx = nullptr;
         st = dh::host_ctx(ctx);
@@ -245,7 +276,7 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
         DH_TRY(cudaStreamWaitEvent(ctx->s[0], ctx->fork, 0));
         DH_TRY(cudaStreamWaitEvent(ctx->s[1], ctx->fork, 0));
         for (int64_t c = 0; c < nch; ++c) {
-            const int64_t s0 = B * c / nch, s1 = B * (c + 1) / nch, nb = s1 - s0;
+            const int64_t s0 = bounds[c], s1 = bounds[c + 1] > s0 ? bounds[c + 1] : s0, nb = s1 - s0;
             if (nb <= 0) continue;
             DH_TRY(cudaMemcpyAsync(d_centers + s0 * T * 2, centers_xy_host + s0 * T * 2, (size_t)nb * T * 8,
                                    cudaMemcpyHostToDevice, ctx->copy));

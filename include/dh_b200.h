@@ -178,8 +178,9 @@ int dh_checksum(void* stream, const float* values, int64_t n, int64_t index_base
  *     chunks are rendered into two staging buffers inside `device_scratch`, so device memory use is bounded
  *     independent of B; otherwise they are rendered in place into heatmap_device [B,(C),H,W].
  *   - heatmap_host == NULL: heatmap_device must be non-NULL and the result stays on the device. When the inputs
- *     are large (>= 2 MiB) they are cut into up to 16 sample chunks (~1 MiB each, or `chunk_samples` samples when
- *     > 0): chunk c+1 crosses PCIe on an internal copy stream while chunk c is rendered, consecutive chunks
+ *     are large (>= 256 KiB) they are cut into 2-6 sample chunks that grow geometrically (x4) from a first one of
+ *     ~100 KiB of inputs — only the first copy is exposed — or into up to 16 equal chunks of `chunk_samples` samples
+ *     when > 0: chunk c+1 crosses PCIe on an internal copy stream while chunk c is rendered, consecutive chunks
  *     alternating between the two internal render streams; otherwise (or with chunk_samples < 0) one copy per
  *     array and ONE render launch on `stream`.
  *   - checksum_host (optional, 3 x uint64, host): dh_checksum of the whole result, copied to the host (computed

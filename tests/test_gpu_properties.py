@@ -274,7 +274,7 @@ def test_host_buffer_entry(cabi, cuda_dev, oracle):
 
 
 def test_host_entry_pipelines_large_inputs(cabi, cuda_dev, oracle):
-    """Inputs >= 2 MiB: the host entry copies them in chunks on its copy stream while earlier chunks render on two
+    """Large inputs (>= 256 KiB; here 3.5 MiB): the host entry copies them in geometrically growing chunks on its copy stream while earlier chunks render on two
     alternating streams. Result and digest must equal the single-launch path (chunk_samples < 0) and the oracle."""
     cfg = workloads.Config("pipe", 2048, 2, 32, 64, 4, 0, 64, 64, 96, 777)
     w = workloads.make(cfg)
