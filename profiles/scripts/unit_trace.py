@@ -8,7 +8,8 @@ import numpy as np, torch
 import _cabi, workloads
 
 name = sys.argv[1] if len(sys.argv) > 1 else "cfg5"
-B = int(sys.argv[2]) if len(sys.argv) > 2 else None
+B = int(sys.argv[2]) if len(sys.argv) > 2 and sys.argv[2] != "-" else None
+MODE = _cabi.DH_MODE_ACCUMULATE if len(sys.argv) > 3 and sys.argv[3] == "accum" else _cabi.DH_MODE_FRESH  # accum: re-draw
 lib = _cabi.load()
 lib.dh_debug_set_trace.argtypes = [ctypes.c_void_p, ctypes.c_int64]
 dev = torch.device("cuda", 0)
@@ -21,10 +22,12 @@ sp = _cabi.stream_ptr()
 
 def run(i):
     st = lib.dh_draw_heatmap_batched_from_boxes(sp, _cabi.ptr(heat[i % 2]), _cabi.ptr(d[0]), _cabi.ptr(d[1]), float(cfg.osf),
-        _cabi.ptr(d[2]), _cabi.DH_SIZES_I64, _cabi.ptr(d[3]), w.B, w.T, cfg.C, cfg.H, cfg.W, 6.0, 1.0, _cabi.DH_MODE_FRESH, None, None, None)
+        _cabi.ptr(d[2]), _cabi.DH_SIZES_I64, _cabi.ptr(d[3]), w.B, w.T, cfg.C, cfg.H, cfg.W, 6.0, 1.0, MODE, None, None, None)
     assert st == 0
 
+for h in heat: h.zero_()
 for i in range(5): run(i)
+if MODE == _cabi.DH_MODE_ACCUMULATE: heat[0].zero_()  # the traced launch draws into zeros, like the drop-in call
 torch.cuda.synchronize()
 assert lib.dh_debug_set_trace(_cabi.ptr(trace), NU) == 0
 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
