@@ -157,7 +157,7 @@ __device__ __forceinline__ float log_pos(float a) {
 // fetch (ncu: no_instruction 2.8). The gradient's quotient is __fdividef (2 ulp) in every mode: there is no reference
 // value to match bit for bit, and the IEEE division cost 14 instructions per pixel.
 template <int PX, bool INPLACE, bool FRESH, int LOSS_MODE = 0>
-__global__ void __launch_bounds__(kGsThreads, LOSS_MODE ? 2 : (PX == 4 ? 3 : 4)) gaussians_kernel(const GsParams p) {
+__global__ void __launch_bounds__(kGsThreads, (PX == 4 || LOSS_MODE) ? 3 : 4) gaussians_kernel(const GsParams p) {
     constexpr bool LOSS = LOSS_MODE != 0;
     if (p.gate != nullptr && *p.gate == 0) return;
     constexpr bool GRAD = LOSS_MODE >= 1 && LOSS_MODE <= 3;
