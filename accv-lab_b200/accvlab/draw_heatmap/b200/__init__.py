@@ -217,7 +217,11 @@ class _GaussianFocalLoss(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_loss, _g_out2):
         (grad,) = ctx.saved_tensors
-        return (grad * g_loss,) + (None,) * 10
+        if g_loss.is_cuda and g_loss.dtype == torch.float32 and g_loss.numel() == 1:
+            out = _ext.scale_by(grad, g_loss.contiguous(), False)  # streaming kernel, the scalar is read on the device
+        else:
+            out = grad * g_loss
+        return (out,) + (None,) * 10
 
 
 def gaussian_focal_loss(pred: torch.Tensor, centers, radii, diameter_to_sigma_factor: float = 6.0, k_scale: float = 1.0,

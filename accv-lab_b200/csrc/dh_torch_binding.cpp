@@ -632,6 +632,20 @@ std::tuple<at::Tensor, at::Tensor> gaussian_focal_loss(const at::Tensor& pred, c
     return {out2, grad};
 }
 
+// grad * g (g: 0-dim / 1-element float32 CUDA tensor), into a new tensor or in place
+at::Tensor scale_by(const at::Tensor& grad, const at::Tensor& g, bool in_place) {
+    CHECK_INPUT(grad);
+    CHECK_DTYPE(grad, at::kFloat);
+    TORCH_CHECK(g.is_cuda() && g.numel() == 1 && g.scalar_type() == at::kFloat, "scale must be a 1-element float32 CUDA tensor");
+    CHECK_SAME_DEVICE(g, grad);
+    c10::cuda::CUDAGuard guard(grad.device());
+    at::Tensor out = in_place ? grad : at::empty_like(grad);
+    check_status(dh_scale_by_device_scalar(at::cuda::getCurrentCUDAStream().stream(), out.data_ptr<float>(),
+                                           grad.data_ptr<float>(), g.data_ptr<float>(), grad.numel()),
+                 "scale_by");
+    return out;
+}
+
 void fill_probe(at::Tensor& t) {
     CHECK_INPUT(t);
     c10::cuda::CUDAGuard guard(t.device());
@@ -696,6 +710,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           pybind11::arg("min_radius"), pybind11::arg("max_radius"), pybind11::arg("min_fraction_area"));
     m.def("gaussian_radius", &gaussian_radius, "CenterNet/CenterPoint gaussian_radius(det_size, min_overlap) -> (int32 radii, float32 radii).",
           pybind11::arg("det_hw"), pybind11::arg("min_overlap"), pybind11::arg("variant"), pybind11::arg("min_radius"));
+    m.def("scale_by", &scale_by, "grad * g with g a 1-element float32 CUDA tensor (no host synchronisation), at copy rate.",
+          pybind11::arg("grad"), pybind11::arg("g"), pybind11::arg("in_place") = false);
     m.def("gaussian_focal_loss", &gaussian_focal_loss,
           "Fused target rendering + Gaussian focal loss: (double[2] = {loss sum, #target==1}, d loss / d pred or undefined).",
           pybind11::arg("pred"), pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"),

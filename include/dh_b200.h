@@ -303,6 +303,11 @@ int dh_gaussian_focal_loss(void* stream, const float* pred, const int32_t* cente
                            int fast_math, float* grad_pred, double* loss_out2, void* workspace,
                            size_t workspace_bytes);
 
+/* Backward of dh_gaussian_focal_loss: dst[i] = src[i] * (*scale_device) for n float32 elements, the scalar read from
+ * DEVICE memory (the upstream gradient of the scalar loss as autograd hands it over; no host synchronisation). dst may
+ * equal src. One streaming launch at copy rate. */
+int dh_scale_by_device_scalar(void* stream, float* dst, const float* src, const float* scale_device, int64_t n);
+
 /* ---- measurement helper ---------------------------------------------------------------
  * Pure 128-bit-store fill of `bytes` bytes (multiple of 16, 16-byte aligned) with zeros using the same
  * store path and grid shape as the FRESH renderer: the write-only ceiling the renderer is compared to. */

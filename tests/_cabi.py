@@ -55,6 +55,7 @@ SIGNATURES = {
     "dh_focal_loss_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64]),
     "dh_gaussian_focal_loss": (_i, [_p, _p, _p, _p, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f, _f, _f, _f, _i, _p,
                                     _p, _p, _sz]),
+    "dh_scale_by_device_scalar": (_i, [_p, _p, _p, _p, _i64]),
     "dh_fill_probe": (_i, [_p, _p, _sz]),
     "dh_expf_probe": (_i, [_p, ctypes.c_uint32, _i64, _p]),
 }

@@ -134,3 +134,24 @@ def test_fused_loss_equals_unfused_torch_on_our_heatmap(cuda_dev):
     assert int(npos) == int(pos.sum())
     assert abs(float(loss.detach()) - float(ref.detach())) <= 1e-5 * abs(float(ref.detach()))
     assert torch.all((p2.grad - p1.grad).abs() <= 1e-4 * p1.grad.abs() + 1e-6)
+
+
+@pytest.mark.gpu
+def test_scale_by_device_scalar(cabi, cuda_dev):
+    """backward helper: dst = src * (*scale) with the scalar in device memory; aligned / misaligned / tails / in place"""
+    import torch
+
+    for n, off in ((1, 0), (3, 0), (4, 0), (4099, 0), (4099, 1), (2048 * 256 + 5, 0), (100000, 3)):
+        buf = torch.randn(n + 8, device=cuda_dev)
+        src = buf[off:off + n]
+        s = torch.tensor(-0.37, device=cuda_dev)
+        dst = torch.full((n + 8,), 9.0, device=cuda_dev)
+        out = dst[off:off + n]
+        _cabi.check(cabi, cabi.dh_scale_by_device_scalar(_cabi.stream_ptr(), _cabi.ptr(out), _cabi.ptr(src), _cabi.ptr(s), n))
+        assert torch.equal(out, src * s)
+        assert bool((dst[:off] == 9.0).all()) and bool((dst[off + n:] == 9.0).all())
+        want = src * s
+        _cabi.check(cabi, cabi.dh_scale_by_device_scalar(_cabi.stream_ptr(), _cabi.ptr(src), _cabi.ptr(src), _cabi.ptr(s), n))
+        assert torch.equal(src, want)
+    assert cabi.dh_scale_by_device_scalar(None, None, None, None, 0) == _cabi.DH_OK
+    assert cabi.dh_scale_by_device_scalar(None, None, None, None, 5) == _cabi.DH_ERR_INVALID_ARGUMENT
