@@ -275,8 +275,22 @@ __global__ void __launch_bounds__(kGsThreads, (PX == 4 || LOSS_MODE) ? 3 : 4) ga
                     if constexpr (PX == 4) {
                         const float4* const i4 = in_plane ? reinterpret_cast<const float4*>(in_plane) + base : nullptr;
                         float4* const o4 = reinterpret_cast<float4*>(out_plane) + base;
-#pragma unroll 4
-                        for (int it = tid; it < nitems; it += kGsThreads) o4[it] = i4 ? i4[it] : make_float4(0.f, 0.f, 0.f, 0.f);
+                        // four loads in flight before the first store: written as `o4[it] = i4[it]` the compiler has to
+                        // assume that out aliases in and serialises every load behind the previous store
+                        for (int it0 = tid; it0 < nitems; it0 += kGsThreads * 4) {
+                            float4 a[4];
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) {
+                                const int it = it0 + u * kGsThreads;
+                                a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                                if (i4 != nullptr && it < nitems) a[u] = __ldg(i4 + it);
+                            }
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) {
+                                const int it = it0 + u * kGsThreads;
+                                if (it < nitems) o4[it] = a[u];
+                            }
+                        }
                     } else {
                         for (int it = tid; it < nitems; it += kGsThreads) out_plane[base + it] = in_plane ? in_plane[base + it] : 0.0f;
                     }
