@@ -87,7 +87,7 @@ static int host_env_int(const char* name, int dflt) {
 }
 // measurement hooks (read once): growth factor of the input chunks, smallest input size that is pipelined (KiB)
 static const int g_host_growth = host_env_int("DH_HOST_GROWTH", 4);
-static const int g_host_pipeline_kib = host_env_int("DH_HOST_PIPELINE_KIB", 256);
+static const int g_host_pipeline_kib = host_env_int("DH_HOST_PIPELINE_KIB", 1536);
 constexpr int kHostMaxChunks = 16;  // input chunks of the pipelined device-output path
 struct HostCtx {
     bool ready = false;
@@ -118,6 +118,43 @@ static int host_ctx(HostCtx*& out) {
     }
     out = &c;
     return DH_OK;
+}
+
+// Small inputs in PINNED host memory: one kernel reads the four arrays straight over PCIe (UVA zero-copy) into the
+// device scratch — one launch instead of four cudaMemcpyAsync, whose fixed costs (~8 us each for a few hundred KB)
+// add up to more than the transfer itself. Pageable memory (not device-accessible) keeps the memcpy path.
+struct GatherArgs {
+    const void* src[4];
+    void* dst[4];
+    unsigned long long bytes[4];  // multiples of 4
+};
+__global__ void __launch_bounds__(256) gather_host_kernel(const GatherArgs a) {
+    const long long tid = blockIdx.x * 256ll + threadIdx.x, nthr = (long long)gridDim.x * 256;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const char* const s = (const char*)a.src[k];
+        char* const d = (char*)a.dst[k];
+        const unsigned long long nb = a.bytes[k];
+        if (nb == 0) continue;
+        if ((((uintptr_t)s | (uintptr_t)d) & 15u) == 0) {
+            const long long n16 = (long long)(nb >> 4);
+            for (long long i = tid; i < n16; i += nthr) ((int4*)d)[i] = ((const int4*)s)[i];
+            for (long long i = (n16 << 2) + tid; i < (long long)(nb >> 2); i += nthr) ((int*)d)[i] = ((const int*)s)[i];
+        } else {
+            for (long long i = tid; i < (long long)(nb >> 2); i += nthr) ((int*)d)[i] = ((const int*)s)[i];
+        }
+    }
+}
+static const int g_host_gather = host_env_int("DH_HOST_GATHER", 1);
+// device-visible alias of a pinned host pointer, or nullptr when the memory is pageable / unknown to the driver
+static const void* pinned_alias(const void* h) {
+    if (!h) return nullptr;
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, h) != cudaSuccess) {
+        cudaGetLastError();  // clear
+        return nullptr;
+    }
+    return (at.type == cudaMemoryTypeHost) ? at.devicePointer : nullptr;
 }
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -299,14 +336,41 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
         return DH_OK;
     }
 
-    // ---- inputs: host -> device, one copy per array ----
-    if (T > 0) {
-        DH_TRY(cudaMemcpyAsync(d_centers, centers_xy_host, (size_t)B * T * 2 * 4, cudaMemcpyHostToDevice, stream));
-        DH_TRY(cudaMemcpyAsync(d_bboxes, bboxes_xyxy_host, (size_t)B * T * 4 * 4, cudaMemcpyHostToDevice, stream));
-        if (has_labels)
-            DH_TRY(cudaMemcpyAsync(d_labels, labels_host, (size_t)B * T * 4, cudaMemcpyHostToDevice, stream));
+    // ---- inputs: host -> device. Pinned and small: one zero-copy gather launch; else one copy per array ----
+    bool gathered = false;
+    if (dh::g_host_gather && in_bytes <= ((size_t)8 << 20)) {
+        dh::GatherArgs ga{};
+        ga.src[0] = T > 0 ? dh::pinned_alias(centers_xy_host) : nullptr;
+        ga.src[1] = T > 0 ? dh::pinned_alias(bboxes_xyxy_host) : nullptr;
+        ga.src[2] = (T > 0 && has_labels) ? dh::pinned_alias(labels_host) : nullptr;
+        ga.src[3] = dh::pinned_alias(nums_targets_host);
+        ga.dst[0] = d_centers; ga.dst[1] = d_bboxes; ga.dst[2] = d_labels; ga.dst[3] = d_sizes;
+        ga.bytes[0] = T > 0 ? (unsigned long long)B * T * 8 : 0;
+        ga.bytes[1] = T > 0 ? (unsigned long long)B * T * 16 : 0;
+        ga.bytes[2] = (T > 0 && has_labels) ? (unsigned long long)B * T * 4 : 0;
+        ga.bytes[3] = (unsigned long long)B * 8;
+        bool ok = true;
+        for (int k2 = 0; k2 < 4; ++k2) ok = ok && (ga.bytes[k2] == 0 || ga.src[k2] != nullptr);
+        if (ok) {
+            const unsigned long long units = (ga.bytes[0] + ga.bytes[1] + ga.bytes[2] + ga.bytes[3]) >> 4;
+            long long blocks = (long long)((units + 255) / 256);
+            if (blocks < 1) blocks = 1;
+            if (blocks > 1184) blocks = 1184;
+            dh::gather_host_kernel<<<(int)blocks, 256, 0, stream>>>(ga);
+            DH_TRY(cudaGetLastError());
+            dh::count_launches(1);
+            gathered = true;
+        }
     }
-    DH_TRY(cudaMemcpyAsync(d_sizes, nums_targets_host, (size_t)B * 8, cudaMemcpyHostToDevice, stream));
+    if (!gathered) {
+        if (T > 0) {
+            DH_TRY(cudaMemcpyAsync(d_centers, centers_xy_host, (size_t)B * T * 2 * 4, cudaMemcpyHostToDevice, stream));
+            DH_TRY(cudaMemcpyAsync(d_bboxes, bboxes_xyxy_host, (size_t)B * T * 4 * 4, cudaMemcpyHostToDevice, stream));
+            if (has_labels)
+                DH_TRY(cudaMemcpyAsync(d_labels, labels_host, (size_t)B * T * 4, cudaMemcpyHostToDevice, stream));
+        }
+        DH_TRY(cudaMemcpyAsync(d_sizes, nums_targets_host, (size_t)B * 8, cudaMemcpyHostToDevice, stream));
+    }
     if (checksum_host) DH_TRY(cudaMemsetAsync(d_ck, 0, 24, stream));
 
     if (!heatmap_host) {  // result stays on the device, small inputs: one launch

@@ -178,11 +178,12 @@ int dh_checksum(void* stream, const float* values, int64_t n, int64_t index_base
  *     chunks are rendered into two staging buffers inside `device_scratch`, so device memory use is bounded
  *     independent of B; otherwise they are rendered in place into heatmap_device [B,(C),H,W].
  *   - heatmap_host == NULL: heatmap_device must be non-NULL and the result stays on the device. When the inputs
- *     are large (>= 256 KiB) they are cut into 2-6 sample chunks that grow geometrically (x4) from a first one of
+ *     are large (>= 1.5 MiB) they are cut into 2-6 sample chunks that grow geometrically (x4) from a first one of
  *     ~100 KiB of inputs — only the first copy is exposed — or into up to 16 equal chunks of `chunk_samples` samples
  *     when > 0: chunk c+1 crosses PCIe on an internal copy stream while chunk c is rendered, consecutive chunks
- *     alternating between the two internal render streams; otherwise (or with chunk_samples < 0) one copy per
- *     array and ONE render launch on `stream`.
+ *     alternating between the two internal render streams; otherwise (or with chunk_samples < 0) the inputs are
+ *     brought over and rendered by ONE launch on `stream` — when all of them lie in pinned (device-mapped) host memory
+ *     and are <= 8 MiB by one gather launch that reads them in place over PCIe, else by one cudaMemcpyAsync per array.
  *   - checksum_host (optional, 3 x uint64, host): dh_checksum of the whole result, copied to the host (computed
  *     inside the render launch when the shape allows it, by a separate dh_checksum pass otherwise).
  * labels_host == NULL -> heatmap is [B,H,W] and num_classes is ignored. nums_targets_host is int64 [B].

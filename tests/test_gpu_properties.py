@@ -273,8 +273,55 @@ def test_host_buffer_entry(cabi, cuda_dev, oracle):
         6.0, 1.0, _cabi.ptr(scratch), 16, 0) == _cabi.DH_ERR_WORKSPACE_TOO_SMALL
 
 
+def test_host_entry_pinned_gather_equals_pageable_copies(cabi, cuda_dev, oracle):
+    """Small inputs: pinned arrays are read in place by one gather launch, pageable ones (or a mix) go through
+    cudaMemcpyAsync; odd offsets exercise the 4-byte path of the gather. Same heatmap, same digest, no labels too."""
+    w = workloads.make("cfg2")
+    cfg = w.cfg
+    args = (w.B, w.T, cfg.C, cfg.H, cfg.W)
+    nbytes = cabi.dh_host_scratch_bytes(*args, 1, 0, 0)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=cuda_dev)
+    st = _cabi.stream_ptr()
+
+    def shifted_pin(a):  # pinned, but 4 bytes off the 16-byte grid
+        flat = np.ascontiguousarray(a).view(np.uint8).reshape(-1)
+        t = torch.empty(flat.size + 4, dtype=torch.uint8).pin_memory()
+        t[4:] = torch.from_numpy(flat.copy())
+        return t[4:]
+
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    plain = lambda a: torch.from_numpy(np.ascontiguousarray(a).copy())
+    results = []
+    for mk, launches in ((pin, 2), (plain, 1), (shifted_pin, 2), (None, 1)):
+        if mk is None:  # a mix: one array pageable -> the whole call takes the copy path
+            cf, bf, s, lab = pin(w.centers_f), plain(w.bboxes_f), pin(w.sizes), pin(w.labels)
+        else:
+            cf, bf, s, lab = mk(w.centers_f), mk(w.bboxes_f), mk(w.sizes), mk(w.labels)
+        for with_labels in (True, False):
+            shape = (w.B, cfg.C, cfg.H, cfg.W) if with_labels else (w.B, cfg.H, cfg.W)
+            hd = torch.full(shape, 7.0, device=cuda_dev)
+            ck = torch.zeros(3, dtype=torch.int64).pin_memory()
+            l0 = cabi.dh_launch_count()
+            rc = cabi.dh_draw_heatmap_batched_from_boxes_host(
+                st, None, _cabi.ptr(hd), _cabi.ptr(ck), _cabi.ptr(cf), _cabi.ptr(bf), float(cfg.osf), _cabi.ptr(s),
+                _cabi.ptr(lab) if with_labels else None, *args, 6.0, 1.0, _cabi.ptr(scratch), nbytes, 0)
+            _cabi.check(cabi, rc, "host entry")
+            torch.cuda.synchronize()
+            assert cabi.dh_launch_count() - l0 == launches
+            got = hd.cpu().numpy()
+            assert np.array_equal(ck.numpy(), oracle.digest_numpy(got))
+            results.append((with_labels, got))
+    for wl, got in results[2:]:
+        ref = results[0][1] if wl else results[1][1]
+        assert np.array_equal(got, ref)
+    ci, ri = oracle.radius_center(w.centers_f, w.bboxes_f, cfg.osf)
+    want = np.zeros(results[0][1].shape, np.float32)
+    oracle.draw_batched(want, ci, ri, w.sizes, 6.0, 1.0, w.labels)
+    assert np.abs(results[0][1] - want).max() <= 1e-6 and np.array_equal(results[0][1] > 0, want > 0)
+
+
 def test_host_entry_pipelines_large_inputs(cabi, cuda_dev, oracle):
-    """Large inputs (>= 256 KiB; here 3.5 MiB): the host entry copies them in geometrically growing chunks on its copy stream while earlier chunks render on two
+    """Large inputs (>= 1.5 MiB; here 3.5 MiB): the host entry copies them in geometrically growing chunks on its copy stream while earlier chunks render on two
     alternating streams. Result and digest must equal the single-launch path (chunk_samples < 0) and the oracle."""
     cfg = workloads.Config("pipe", 2048, 2, 32, 64, 4, 0, 64, 64, 96, 777)
     w = workloads.make(cfg)
@@ -300,7 +347,7 @@ def test_host_entry_pipelines_large_inputs(cabi, cuda_dev, oracle):
         _cabi.check(cabi, rc, "host entry (pipelined)")
         torch.cuda.synchronize()
         nl = cabi.dh_launch_count() - l0
-        assert (nl == 1) if chunk < 0 else (2 <= nl <= 16)
+        assert (nl == 2) if chunk < 0 else (2 <= nl <= 16)  # single shot = zero-copy gather of the pinned inputs + render
         results.append(hd.cpu().numpy())
         assert np.array_equal(ck.numpy(), oracle.digest_numpy(results[-1]))
     for r in results[1:]:
