@@ -219,8 +219,19 @@ def run_ours(args):
     if world > 1:
         import torch.distributed as dist
 
-
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL writes its version banner (any NCCL_DEBUG level >= VERSION) to STDOUT, where the contract is ONE JSON
+        # line: point fd 1 at stderr while the communicator comes up, then restore it.
+        sys.stdout.flush()
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.all_reduce(torch.zeros(1, device=dev))
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
     lib = _cabi.load()  # raises if libdh_b200.so is missing: no fallback
 
     w_all = workloads.make(args.workload, B=args.batch)
