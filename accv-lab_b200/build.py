@@ -23,6 +23,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 LIB_PATH = os.path.join(PKG, "libdh_b200.so")
 EXT_PATH = os.path.join(PKG, "draw_heatmap_ext" + (sysconfig.get_config_var("EXT_SUFFIX") or ".so"))
+SHIM_PATH = os.path.join(PKG, "libdh_ref_shim.so")
 
 
 def _run(cmd):
@@ -71,10 +72,22 @@ def build_torch_ext(force=False):
     return EXT_PATH
 
 
+def build_ref_shim(force=False):
+    """libdh_ref_shim.so: the reference's two C++-linkage launchers (draw_heatmap_cuda.cu:29-31,43-46) over the C ABI."""
+    src = os.path.join(CSRC, "dh_ref_shim.cpp")
+    deps = [src, os.path.join(INCLUDE, "dh_b200.h"), LIB_PATH]
+    if force or not _fresh(SHIM_PATH, deps):
+        _run(["g++", "-shared", "-fPIC", "-O2", "-std=c++17", "-fvisibility=hidden", src, "-o", SHIM_PATH, f"-I{INCLUDE}",
+              "-I/usr/local/cuda/include", f"-L{PKG}", "-L/usr/local/cuda/lib64", "-ldh_b200", "-lcudart",
+              "-Wl,-rpath,$ORIGIN"])
+    return SHIM_PATH
+
+
 def build_all(force=False):
     build_cuda_lib(force)
     build_torch_ext(force)
-    return LIB_PATH, EXT_PATH
+    build_ref_shim(force)
+    return LIB_PATH, EXT_PATH, SHIM_PATH
 
 
 if __name__ == "__main__":

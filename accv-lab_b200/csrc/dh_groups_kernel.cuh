@@ -461,7 +461,7 @@ __device__ __forceinline__ bool scan_slot(const RenderParams& p, const UnitSrc& 
             const long long i = us.src_base + t;
             int lab = us.cls;
             if (p.labels != nullptr) lab = __ldg(p.labels + i);
-            const int2 c = __ldg(reinterpret_cast<const int2*>(p.centers) + i);
+            const int2 c = ld_center_i(p, i);
             const int r = __ldg(p.radii + i);
             const float w = __ldg(p.weights + i);
             if (t < us.n && lab == us.cls && r >= 0) {
@@ -482,11 +482,11 @@ __device__ __forceinline__ bool scan_slot(const RenderParams& p, const UnitSrc& 
             if (p.labels != nullptr) lab = __ldg(p.labels + i);
             int x = 0, y = 0, r = -1;
             if constexpr (SRC == SRC_BOXES) {
-                const float2 c = __ldg(reinterpret_cast<const float2*>(p.centers_f) + i);
-                const float4 b = __ldg(reinterpret_cast<const float4*>(p.bboxes_f) + i);
-                if (lab == us.cls) radius_center_one(c.x, c.y, b.x, b.y, b.z, b.w, p.osf, x, y, r);
+                const float2 c = ld_center_f(p, i);
+                const float4 b = ld_box_f(p, i);
+                if (lab == us.cls || (count_skips && p.status)) radius_center_one(c.x, c.y, b.x, b.y, b.z, b.w, p.osf, x, y, r);
             } else {
-                const int2 c = __ldg(reinterpret_cast<const int2*>(p.centers) + i);
+                const int2 c = ld_center_i(p, i);
                 r = __ldg(p.radii + i);
                 x = c.x;
                 y = c.y;
@@ -494,8 +494,10 @@ __device__ __forceinline__ bool scan_slot(const RenderParams& p, const UnitSrc& 
             if (t < us.n) {
                 if (lab == us.cls)
                     pred = make_obji(x, y, r, p.factor, uy0, uy1, W, o, p.status, count_skips);
-                else if (count_skips && p.status && (lab < 0 || lab >= p.C))
-                    atomicAdd(&p.status->skipped_label, 1u);
+                else if (count_skips && p.status) {  // the counting unit sees every slot once: other classes' skips too
+                    if (lab < 0 || lab >= p.C) atomicAdd(&p.status->skipped_label, 1u);
+                    else if (r > DH_MAX_RADIUS) atomicAdd(&p.status->skipped_radius, 1u);
+                }
             }
         }
     } else if (t < us.n) {
@@ -591,17 +593,25 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
     const bool kneg0 = p.k < 0.0f;
     const int W = p.W, G = p.band_cols /* rows per group */;
     const long long plane_elems = (long long)p.H * W;
-    {  // zero tile and staging buffers start all-zero (contiguous in shared memory)
-        const int n16 = (kGZeroBytes + kGWarps * 2 * stage) / 16;
-        for (int i = tid; i < n16; i += kGThreads) zero_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    {  // Prologue. Only the 8 KB zero tile is cleared by the whole block before the first unit: the untouched runs of
+       // the first unit (the bulk of its bytes) can then leave as soon as its list is built. Every warp clears its own
+       // two staging buffers later, right before it renders its first touched group (off the path to the first store).
+        for (int i = tid; i < kGZeroBytes / 16; i += kGThreads) zero_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (tid == 0) mbar_init(&s_bar, 1);
         fence_proxy_async();  // zero tile and mbarrier -> visible to the async proxy
     }
     WarpStage ws;
     ws.buf0 = reinterpret_cast<unsigned*>(smem_raw + kGZeroBytes + warp * 2 * stage);
     ws.buf1 = ws.buf0 + stage / 4;
+    bool stage_clean = false;  // my staging buffers are all-zero (established before my first render_group)
     unsigned clc_phase = 0;
     Digest dg;
+    // Programmatic dependent launch: everything above overlaps the tail of the previous kernel in the stream when this
+    // launch carries cudaLaunchAttributeProgrammaticStreamSerialization; global memory (inputs may be that kernel's
+    // outputs, the heatmap may be its input) is touched only after the wait. Without the attribute both are no-ops.
+    // The kernel that FOLLOWS may start its own prologue as soon as every CTA of this grid is past this point.
+    pdl_wait();
+    pdl_launch_dependents();
 
     long long u = blockIdx.x;
     for (;;) {
@@ -700,6 +710,12 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         // K3/K4b: touched groups, striped over the warps; no block barrier in here
         const long long plane_index0 = p.digest_base + us.plane * plane_elems;
         unsigned long long gm = mask & (0x0101010101010101ull << warp);
+        if (gm != 0ull && !stage_clean) {  // first touched group of this warp: establish the all-zero invariant
+            uint4* const b4 = reinterpret_cast<uint4*>(ws.buf0);
+            for (int i = lane; i < (2 * stage) / 16; i += 32) b4[i] = make_uint4(0u, 0u, 0u, 0u);
+            __syncwarp();
+            stage_clean = true;
+        }
         while (gm) {
             const int g = __ffsll((long long)gm) - 1;
             gm &= gm - 1ull;

@@ -61,6 +61,7 @@ struct RenderParams {
     long long num_objects;     // N (flat sources)
     long long num_planes;
     int C, T, H, W;
+    int in_vec;  // centers / centers_f are 8-byte and bboxes_f 16-byte aligned: slots are read with one vector load each
     int wunits;  // W / PX
     int band_rows, band_cols, bands_x, bands_y, bands_per_plane, bands_per_unit, units_per_plane;
     int stage_bytes;  // groups_kernel: bytes of one per-warp staging buffer
@@ -659,6 +660,7 @@ static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
 static const int g_no_clc = env_int("DH_G_NOCLC", 0);
 static const int g_single_wave = env_int("DH_G_SINGLE_WAVE", 1);
 static const int g_heavy_per_slot = env_int("DH_G_HEAVY_PER_SLOT", 8);
+static const int g_pdl = env_int("DH_G_PDL", 1);  // programmatic dependent launch of groups_kernel
 static const int g_tail_div = env_int("DH_G_TAIL_DIV", 2);            // tail-tier units are 1/this of a full unit (1 = off)
 static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail tier = this/2 waves of full-size units
 
@@ -759,9 +761,27 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     p.use_clc = !g_persistent && !g_no_clc && g <= 0x7fffffffll;  // a clamped grid falls back to the static stride
     if (g_persistent && g > max_ctas) g = max_ctas;
     if (g > 0x7fffffffll) g = 0x7fffffffll;
-    groups_kernel<ACCUM, SRC, DIGEST, OUT><<<(int)g, kGThreads, groups_smem_bytes(p.stage_bytes), stream>>>(p);
+    // Programmatic dependent launch: the prologue of this launch (shared-memory set-up) may overlap the tail of whatever
+    // precedes it in the stream; the kernel waits (griddepcontrol.wait) before it touches global memory.
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)g);
+    cfg.blockDim = dim3(kGThreads);
+    cfg.dynamicSmemBytes = groups_smem_bytes(p.stage_bytes);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_pdl ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, groups_kernel<ACCUM, SRC, DIGEST, OUT>, p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
-    return (int)cudaGetLastError();
+    return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
+}
+
+// slot arrays aligned for one vector load per slot? (dh_rows_kernel.cuh ld_center_i / ld_center_f / ld_box_f)
+static int inputs_vec_ok(const RenderParams& p) {
+    return ((reinterpret_cast<uintptr_t>(p.centers) & 7u) == 0) && ((reinterpret_cast<uintptr_t>(p.centers_f) & 7u) == 0) &&
+           ((reinterpret_cast<uintptr_t>(p.bboxes_f) & 15u) == 0);
 }
 
 template <int SRC>
@@ -769,6 +789,7 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
     DeviceInfo di;
     int st = device_info(di);
     if (st != DH_OK) return st;
+    p.in_vec = inputs_vec_ok(p);
     const bool vec = (p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0);
     const bool accum = (mode == DH_MODE_ACCUMULATE);
     if (vec && p.W <= kGMaxW) {  // main path: row groups striped over warps, per-warp staging + bulk stores
@@ -808,6 +829,7 @@ static int launch_render16(cudaStream_t stream, RenderParams& p, int out_dtype) 
     if (st != DH_OK) return st;
     if (!((p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0) && p.W <= kGMaxW))
         return DH_ERR_UNSUPPORTED_SHAPE;
+    p.in_vec = inputs_vec_ok(p);
     if (out_dtype == DH_OUT_F16) return launch_groups<false, SRC, false, OUT_F16>(stream, p, di.sms);
     return launch_groups<false, SRC, false, OUT_BF16>(stream, p, di.sms);
 }
@@ -838,6 +860,7 @@ int launch_weighted_fresh(cudaStream_t stream, float* heat, const int32_t* cente
     p.W = (int)W;
     p.factor = 1.0f;
     p.k = 1.0f;
+    p.in_vec = inputs_vec_ok(p);
     return launch_groups<false, SRC_WEIGHTED, false>(stream, p, di.sms);
 }
 

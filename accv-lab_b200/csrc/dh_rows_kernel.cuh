@@ -37,6 +37,23 @@ struct __align__(16) ObjI {
     float w;  // 1/var (> 0)
 };
 
+// Slot loads of the RaggedBatch arrays: one 8- / 16-byte load when the array base allows it (`p.in_vec`, checked on the
+// host), scalar loads otherwise — a contiguous torch tensor may start at any 4-byte offset of its storage, and the
+// reference reads these arrays with scalar int loads (cuh:57-58,86-87), so such inputs must keep working.
+__device__ __forceinline__ int2 ld_center_i(const RenderParams& p, long long i) {
+    if (p.in_vec) return __ldg(reinterpret_cast<const int2*>(p.centers) + i);
+    return make_int2(__ldg(p.centers + 2 * i), __ldg(p.centers + 2 * i + 1));
+}
+__device__ __forceinline__ float2 ld_center_f(const RenderParams& p, long long i) {
+    if (p.in_vec) return __ldg(reinterpret_cast<const float2*>(p.centers_f) + i);
+    return make_float2(__ldg(p.centers_f + 2 * i), __ldg(p.centers_f + 2 * i + 1));
+}
+__device__ __forceinline__ float4 ld_box_f(const RenderParams& p, long long i) {
+    if (p.in_vec) return __ldg(reinterpret_cast<const float4*>(p.bboxes_f) + i);
+    return make_float4(__ldg(p.bboxes_f + 4 * i), __ldg(p.bboxes_f + 4 * i + 1), __ldg(p.bboxes_f + 4 * i + 2),
+                       __ldg(p.bboxes_f + 4 * i + 3));
+}
+
 // Raw slot -> (x, y, r) for the four sources; false if the slot does not belong to this plane.
 template <int SRC>
 __device__ __forceinline__ bool load_slot(const RenderParams& p, long long src_base, int t, int cls, long long plane,
@@ -46,16 +63,33 @@ __device__ __forceinline__ bool load_slot(const RenderParams& p, long long src_b
         if (p.labels != nullptr) {
             const int lab = __ldg(p.labels + i);
             if (lab != cls) {
-                if (cnt && p.status && (lab < 0 || lab >= p.C)) atomicAdd(&p.status->skipped_label, 1u);
+                // the counting unit (class 0, first unit of the sample) sees every slot once: it counts the objects of
+                // the OTHER classes that will be skipped too (a bad label, or a valid label with an oversize radius)
+                if (cnt && p.status) {
+                    if (lab < 0 || lab >= p.C) {
+                        atomicAdd(&p.status->skipped_label, 1u);
+                    } else {
+                        int rr;
+                        if constexpr (SRC == SRC_BOXES) {
+                            int xx, yy;
+                            const float2 c = ld_center_f(p, i);
+                            const float4 b = ld_box_f(p, i);
+                            radius_center_one(c.x, c.y, b.x, b.y, b.z, b.w, p.osf, xx, yy, rr);
+                        } else {
+                            rr = __ldg(p.radii + i);
+                        }
+                        if (rr > DH_MAX_RADIUS) atomicAdd(&p.status->skipped_radius, 1u);
+                    }
+                }
                 return false;
             }
         }
         if constexpr (SRC == SRC_BOXES) {
-            const float2 c = __ldg(reinterpret_cast<const float2*>(p.centers_f) + i);
-            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bboxes_f) + i);
+            const float2 c = ld_center_f(p, i);
+            const float4 b = ld_box_f(p, i);
             radius_center_one(c.x, c.y, b.x, b.y, b.z, b.w, p.osf, x, y, r);
         } else {
-            const int2 c = __ldg(reinterpret_cast<const int2*>(p.centers) + i);
+            const int2 c = ld_center_i(p, i);
             x = c.x;
             y = c.y;
             r = __ldg(p.radii + i);

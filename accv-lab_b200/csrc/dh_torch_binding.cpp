@@ -75,9 +75,14 @@ void draw_heatmap_mode(at::Tensor& heatmap, const at::Tensor& centers, const at:
                  "draw_heatmap");
 }
 
+// `assume_zero_init` (keyword-only, default false; NOT in the reference): the caller promises that the heatmap holds
+// zeros or nothing it wants to keep — every pixel is then written once (DH_MODE_FRESH, zero-init fused) instead of
+// read-max-written, which also makes the caller-side torch.zeros (e.g. DH/tests/test_draw_heatmap.py:70) unnecessary.
+// The positional signature is the reference's (draw_heatmap.cpp:132-144).
 void draw_heatmap(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
-                  const at::Tensor& heatmap_idxes, float diameter_to_sigma_factor, float k_scale) {
-    draw_heatmap_mode(heatmaps, centers, radii, heatmap_idxes, diameter_to_sigma_factor, k_scale, DH_MODE_ACCUMULATE);
+                  const at::Tensor& heatmap_idxes, float diameter_to_sigma_factor, float k_scale, bool assume_zero_init) {
+    draw_heatmap_mode(heatmaps, centers, radii, heatmap_idxes, diameter_to_sigma_factor, k_scale,
+                      assume_zero_init ? DH_MODE_FRESH : DH_MODE_ACCUMULATE);
 }
 
 // ---- batched entries (draw_heatmap_cuda.cu:91-165) ---------------------------------------------------------
@@ -147,14 +152,19 @@ void batched_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tens
 }
 
 void draw_heatmap_batched(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
-                          const at::Tensor& nums_targets, float diameter_to_sigma_factor, float k_scale) {
-    batched_mode(heatmaps, centers, radii, nums_targets, nullptr, diameter_to_sigma_factor, k_scale, DH_MODE_ACCUMULATE);
+                          const at::Tensor& nums_targets, float diameter_to_sigma_factor, float k_scale,
+                          bool assume_zero_init) {
+    if (assume_zero_init) CHECK_DTYPE(heatmaps, at::kFloat);  // the reference-named entries stay float32-only
+    batched_mode(heatmaps, centers, radii, nums_targets, nullptr, diameter_to_sigma_factor, k_scale,
+                 assume_zero_init ? DH_MODE_FRESH : DH_MODE_ACCUMULATE);
 }
 
 void draw_heatmap_batched_classwise(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
                                     const at::Tensor& nums_targets, const at::Tensor& labels,
-                                    float diameter_to_sigma_factor, float k_scale) {
-    batched_mode(heatmaps, centers, radii, nums_targets, &labels, diameter_to_sigma_factor, k_scale, DH_MODE_ACCUMULATE);
+                                    float diameter_to_sigma_factor, float k_scale, bool assume_zero_init) {
+    if (assume_zero_init) CHECK_DTYPE(heatmaps, at::kFloat);
+    batched_mode(heatmaps, centers, radii, nums_targets, &labels, diameter_to_sigma_factor, k_scale,
+                 assume_zero_init ? DH_MODE_FRESH : DH_MODE_ACCUMULATE);
 }
 
 // ---- additions -----------------------------------------------------------------------------------------------
@@ -659,14 +669,17 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     // --- the reference's surface (draw_heatmap.cpp:131-145) ---
     m.def("draw_heatmap", &draw_heatmap, "Draw Gaussians (max-blend, in place) from concatenated objects.",
           pybind11::arg("heatmaps"), pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("heatmap_idxes"),
-          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f);
+          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f, pybind11::kw_only(),
+          pybind11::arg("assume_zero_init") = false);
     m.def("draw_heatmap_batched_impl", &draw_heatmap_batched, "Draw Gaussians (max-blend, in place), one plane per sample.",
           pybind11::arg("heatmaps"), pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"),
-          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f);
+          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f, pybind11::kw_only(),
+          pybind11::arg("assume_zero_init") = false);
     m.def("draw_heatmap_batched_classwise_impl", &draw_heatmap_batched_classwise,
           "Draw Gaussians (max-blend, in place), one plane per (sample, class).", pybind11::arg("heatmaps"),
           pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"), pybind11::arg("labels"),
-          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f);
+          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f, pybind11::kw_only(),
+          pybind11::arg("assume_zero_init") = false);
     // --- additions ---
     m.def("render_heatmap_batched", &render_heatmap_batched,
           "Batched drawing with explicit mode: fresh=True overwrites every pixel (zero-init fused, nothing read).",

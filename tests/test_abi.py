@@ -77,7 +77,9 @@ def test_python_surface_matches_reference():
 
     assert dh.__all__ == ["__version__", "draw_heatmap", "draw_heatmap_batched"]
     sig = inspect.signature(dh.draw_heatmap_batched)
-    assert list(sig.parameters) == ["heatmap", "centers", "radii", "diameter_to_sigma_factor", "k_scale", "labels"]
+    positional = [n for n, q in sig.parameters.items() if q.kind is not inspect.Parameter.KEYWORD_ONLY]
+    assert positional == ["heatmap", "centers", "radii", "diameter_to_sigma_factor", "k_scale", "labels"]
+    assert [n for n in sig.parameters if n not in positional] == ["assume_zero_init"]  # keyword-only addition, default False
     assert sig.parameters["diameter_to_sigma_factor"].default == 6.0
     assert sig.parameters["k_scale"].default == 1.0 and sig.parameters["labels"].default is None
     from accvlab.draw_heatmap import draw_heatmap_ext as ext

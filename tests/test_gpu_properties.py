@@ -122,6 +122,48 @@ def test_full_size_properties_cfg4_cfg5(cabi, cuda_dev, name):
     assert float(fresh.min()) >= 0.0 and float(fresh.max()) == 1.0
 
 
+@pytest.mark.parametrize("name", ["cfg4", "cfg5"])
+def test_full_size_values_vs_oracle_cfg4_cfg5(cabi, cuda_dev, oracle, name):
+    """BASELINE.json's FULL sizes against the ORACLE itself (not against the renderer's other mode): cfg4 at B=32 and
+    cfg5 at B=3072 (30 720 planes, 11.4 GB). The oracle's threaded "refcpu" family (bit-identical to the reference's
+    Python CPU path on every golden, tests/test_oracle_golden.py) renders the batch in 384-sample chunks; every chunk
+    is compared with the GPU result — touched mask exact, values <= 1e-6 — and its digest (dh_checksum of the ORACLE's
+    pixels, with the chunk's index base) is accumulated: the mask-hash and count words must equal those of the
+    digest fused into the full-size render launch."""
+    import os
+
+    w = workloads.make(name)
+    cfg = w.cfg
+    cf, bf, s, lab = _upload(w, cuda_dev)
+    shape = (w.B, cfg.C, cfg.H, cfg.W)
+    sample_elems = cfg.C * cfg.H * cfg.W
+    got = torch.full(shape, 9.0, device=cuda_dev)
+    d_gpu = _cabi.draw_from_boxes_digest(cabi, got, cf, bf, float(cfg.osf), s, lab, 6.0, 1.0)
+    oci, ori = oracle.radius_center(w.centers_f, w.bboxes_f, cfg.osf)
+    co, ro = _cabi.radius_center(cabi, cf, bf, float(cfg.osf))
+    assert np.array_equal(co.cpu().numpy(), oci) and np.array_equal(ro.cpu().numpy(), ori)  # K1 bit-exact, full size
+    threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    chunk = 384
+    d_or = torch.zeros(3, dtype=torch.int64, device=cuda_dev)
+    max_err = 0.0
+    host = np.empty((min(chunk, w.B), cfg.C, cfg.H, cfg.W), np.float32)
+    for b0 in range(0, w.B, chunk):
+        b1 = min(w.B, b0 + chunk)
+        want = host[: b1 - b0]
+        oracle.refcpu_draw_batched(want, oci[b0:b1], ori[b0:b1], w.sizes[b0:b1], 6.0, 1.0, w.labels[b0:b1],
+                                   zero_first=True, nthreads=threads)
+        want_d = torch.from_numpy(want).to(cuda_dev)
+        part = got[b0:b1]
+        assert torch.equal(part > 0, want_d > 0), f"touched mask differs in samples [{b0}, {b1})"
+        max_err = max(max_err, float((part - want_d).abs().max()))
+        _cabi.checksum(cabi, want_d, b0 * sample_elems, d_or)
+        del want_d
+    assert max_err <= 1e-6, max_err
+    assert int(d_or[1]) == int(d_gpu[1]) and int(d_or[2]) == int(d_gpu[2])  # mask hash, touched count
+    # value-bits word: sum of fp32 bit patterns; a 2-ulp budget per touched pixel bounds the difference
+    assert abs(int(d_or[0]) - int(d_gpu[0])) <= 2 * int(d_gpu[2])
+
+
 def test_sharded_equals_unsharded_digest(cabi, cuda_dev):
     """G contiguous batch slices rendered independently give the unsharded result (digest additive)."""
     w = workloads.make("cfg5", B=96)
