@@ -362,6 +362,9 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
                 if (!overflow) {
                     o = list[e];
                     hit = (o.y + o.r >= y0) && (o.y - o.r <= y1);
+                } else if constexpr (SRC == SRC_BINNED) {
+                    o = ld_bin(p.bin_list, us.src_base + e);
+                    hit = (o.r >= 0) && (o.y + o.r >= y0) && (o.y - o.r <= y1);
                 } else {
                     int x, y, r;
                     if (load_slot<SRC>(p, us.src_base, e, us.cls, us.plane, false, x, y, r))

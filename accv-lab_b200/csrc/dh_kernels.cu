@@ -39,7 +39,7 @@ constexpr int kItemsPerThread = 8;
 constexpr int kBandCap = kThreads * kItemsPerThread;  // items (float4 or float) per band
 constexpr int kListCap = 1024;                        // objects per shared-memory list
 
-enum Source : int { SRC_BATCHED = 0, SRC_BOXES = 1, SRC_CSR = 2, SRC_FLATSCAN = 3, SRC_WEIGHTED = 4 };
+enum Source : int { SRC_BATCHED = 0, SRC_BOXES = 1, SRC_CSR = 2, SRC_FLATSCAN = 3, SRC_WEIGHTED = 4, SRC_BINNED = 5 };
 
 struct __align__(16) Obj {
     float fx, fy, fr, wv;  // centre, radius (exact small ints as floats), signed 1/var
@@ -78,6 +78,9 @@ struct RenderParams {
     // radius -> sigma rule, per-class peak instead of one k
     const float* weights;    // [B,T]
     const float* k_classes;  // [C]
+    // SRC_BINNED (groups2_kernel): output of bin_kernel in the caller's workspace
+    const void* bin_list;  // int4 (x, y, r, bits(1/var)) per object, a plane's objects contiguous
+    const void* bin_rec;   // int2 (first entry, count) per plane
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -432,6 +435,7 @@ __global__ void __launch_bounds__(kThreads) render_kernel(const RenderParams p) 
 }  // namespace dh
 #include "dh_rows_kernel.cuh"
 #include "dh_groups_kernel.cuh"
+#include "dh_groups2_kernel.cuh"
 namespace dh {
 
 // ------------------------------------------------------------------------------------------------
@@ -660,6 +664,7 @@ static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
 static const int g_no_clc = env_int("DH_G_NOCLC", 0);
 static const int g_single_wave = env_int("DH_G_SINGLE_WAVE", 1);
 static const int g_heavy_per_slot = env_int("DH_G_HEAVY_PER_SLOT", 8);
+static const int g_no_bin = env_int("DH_G_NOBIN", 0);  // 1: ignore the workspace, always the single-launch renderer
 static const int g_pdl = env_int("DH_G_PDL", 1);  // programmatic dependent launch of groups_kernel
 static const int g_tail_div = env_int("DH_G_TAIL_DIV", 2);            // tail-tier units are 1/this of a full unit (1 = off)
 static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail tier = this/2 waves of full-size units
@@ -737,6 +742,24 @@ static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4) {
     return true;
 }
 
+// One launch with the programmatic-dependent-launch attribute: the prologue of the launched kernel (shared-memory
+// set-up) may overlap the tail of whatever precedes it in the stream; our kernels wait (griddepcontrol.wait, dh_ptx.cuh
+// pdl_wait) before they touch global memory.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
 template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32>
 static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     static bool attr_set_dev[64] = {false};  // function attributes are per device: one process may drive several GPUs
@@ -761,21 +784,55 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     p.use_clc = !g_persistent && !g_no_clc && g <= 0x7fffffffll;  // a clamped grid falls back to the static stride
     if (g_persistent && g > max_ctas) g = max_ctas;
     if (g > 0x7fffffffll) g = 0x7fffffffll;
-    // Programmatic dependent launch: the prologue of this launch (shared-memory set-up) may overlap the tail of whatever
-    // precedes it in the stream; the kernel waits (griddepcontrol.wait) before it touches global memory.
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)g);
-    cfg.blockDim = dim3(kGThreads);
-    cfg.dynamicSmemBytes = groups_smem_bytes(p.stage_bytes);
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = g_pdl ? 1 : 0;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, groups_kernel<ACCUM, SRC, DIGEST, OUT>, p);
+    const cudaError_t e = launch_pdl(groups_kernel<ACCUM, SRC, DIGEST, OUT>, dim3((unsigned)g), dim3(kGThreads),
+                                     groups_smem_bytes(p.stage_bytes), stream, p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
+}
+
+// K2 pre-pass + warp-autonomous renderer (dh_groups2_kernel.cuh): two launches, the second one programmatically
+// dependent on the first (its prologue overlaps bin_kernel; it waits before it reads the lists).
+template <bool ACCUM, bool DIGEST, int OUT = OUT_F32>
+static int launch_groups2(cudaStream_t stream, RenderParams& p, int sms, long long B, void* workspace) {
+    static bool attr_set_dev[64] = {false};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
+    if (!attr_set_dev[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(groups2_kernel<ACCUM, DIGEST, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)groups_smem_bytes(kGStageCap));
+        if (e != cudaSuccess) return (int)e;
+        attr_set_dev[dev] = true;
+    }
+    const long long max_ctas = (long long)sms * DH_G_MINB;
+    if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2)) return DH_ERR_UNSUPPORTED_SHAPE;
+    if (p.total_units == 0) return DH_OK;
+    int2* const rec = reinterpret_cast<int2*>(workspace);
+    int4* const list = reinterpret_cast<int4*>(reinterpret_cast<char*>(workspace) + bin_rec_bytes(p.num_planes));
+    p.bin_rec = rec;
+    p.bin_list = list;
+    cudaError_t e;
+    if (p.centers_f != nullptr)
+        e = launch_pdl(bin_kernel<SRC_BOXES>, dim3((unsigned)B), dim3(kBinThreads), 0, stream, p, list, rec);
+    else
+        e = launch_pdl(bin_kernel<SRC_BATCHED>, dim3((unsigned)B), dim3(kBinThreads), 0, stream, p, list, rec);
+    if (e != cudaSuccess) return (int)e;
+    long long g = p.total_units;
+    p.use_clc = !g_persistent && !g_no_clc && g <= 0x7fffffffll;
+    if (g_persistent && g > max_ctas) g = max_ctas;
+    if (g > 0x7fffffffll) g = 0x7fffffffll;
+    e = launch_pdl(groups2_kernel<ACCUM, DIGEST, OUT>, dim3((unsigned)g), dim3(kGThreads), groups_smem_bytes(p.stage_bytes),
+                   stream, p);
+    g_launches.fetch_add(2, std::memory_order_relaxed);
+    return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
+}
+
+// Does the binned two-launch path serve this call? (main-path shape, class counters fit bin_kernel's shared memory,
+// list offsets fit int32, workspace present, aligned and large enough)
+static bool binned_ok(const RenderParams& p, long long B, const void* workspace, size_t workspace_bytes) {
+    if (workspace == nullptr || (reinterpret_cast<uintptr_t>(workspace) & 15u) || g_no_bin) return false;
+    if (!((p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0) && p.W <= kGMaxW)) return false;
+    if (p.C > kBinMaxC || B * (long long)p.T > 0x7fffffffll || B > 0x7fffffffll || p.T < 1) return false;
+    return workspace_bytes >= bin_workspace_bytes(B, p.T, p.C);
 }
 
 // slot arrays aligned for one vector load per slot? (dh_rows_kernel.cuh ld_center_i / ld_center_f / ld_box_f)
@@ -785,13 +842,21 @@ static int inputs_vec_ok(const RenderParams& p) {
 }
 
 template <int SRC>
-static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
+static int launch_render(cudaStream_t stream, RenderParams& p, int mode, long long B = 0, void* workspace = nullptr,
+                         size_t workspace_bytes = 0) {
     DeviceInfo di;
     int st = device_info(di);
     if (st != DH_OK) return st;
     p.in_vec = inputs_vec_ok(p);
     const bool vec = (p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0);
     const bool accum = (mode == DH_MODE_ACCUMULATE);
+    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+        if (binned_ok(p, B, workspace, workspace_bytes)) {  // K2 pre-pass + warp-autonomous renderer
+            if (accum) return launch_groups2<true, false>(stream, p, di.sms, B, workspace);
+            if (p.digest != nullptr) return launch_groups2<false, true>(stream, p, di.sms, B, workspace);
+            return launch_groups2<false, false>(stream, p, di.sms, B, workspace);
+        }
+    }
     if (vec && p.W <= kGMaxW) {  // main path: row groups striped over warps, per-warp staging + bulk stores
         if (accum) return launch_groups<true, SRC, false>(stream, p, di.sms);
         if (p.digest != nullptr) return launch_groups<false, SRC, true>(stream, p, di.sms);
@@ -823,13 +888,18 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode) {
 
 // FRESH render into fp16 / bf16 planes: main renderer only.
 template <int SRC>
-static int launch_render16(cudaStream_t stream, RenderParams& p, int out_dtype) {
+static int launch_render16(cudaStream_t stream, RenderParams& p, int out_dtype, long long B, void* workspace,
+                           size_t workspace_bytes) {
     DeviceInfo di;
     int st = device_info(di);
     if (st != DH_OK) return st;
     if (!((p.W % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.heat) & 15u) == 0) && p.W <= kGMaxW))
         return DH_ERR_UNSUPPORTED_SHAPE;
     p.in_vec = inputs_vec_ok(p);
+    if (binned_ok(p, B, workspace, workspace_bytes)) {
+        if (out_dtype == DH_OUT_F16) return launch_groups2<false, false, OUT_F16>(stream, p, di.sms, B, workspace);
+        return launch_groups2<false, false, OUT_BF16>(stream, p, di.sms, B, workspace);
+    }
     if (out_dtype == DH_OUT_F16) return launch_groups<false, SRC, false, OUT_F16>(stream, p, di.sms);
     return launch_groups<false, SRC, false, OUT_BF16>(stream, p, di.sms);
 }
@@ -912,7 +982,7 @@ static int batched_common(void* stream, float* heatmap, const int32_t* centers, 
                           const float* centers_f, const float* bboxes_f, float osf, const void* nums_targets,
                           int nums_dtype, const int32_t* labels, int64_t B, int64_t T, int64_t C, int64_t H, int64_t W,
                           float factor, float k, int mode, dh_status* status, uint64_t* digest = nullptr,
-                          int64_t digest_base = 0) {
+                          int64_t digest_base = 0, void* workspace = nullptr, size_t workspace_bytes = 0) {
     if (B < 0 || T < 0) return DH_ERR_INVALID_ARGUMENT;
     if (mode != DH_MODE_ACCUMULATE && mode != DH_MODE_FRESH) return DH_ERR_INVALID_ARGUMENT;
     if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
@@ -945,17 +1015,33 @@ static int batched_common(void* stream, float* heatmap, const int32_t* centers, 
     p.status = status;
     p.digest = reinterpret_cast<unsigned long long*>(digest);
     p.digest_base = digest_base;
-    if (centers_f) return dh::launch_render<dh::SRC_BOXES>((cudaStream_t)stream, p, mode);
-    return dh::launch_render<dh::SRC_BATCHED>((cudaStream_t)stream, p, mode);
+    if (centers_f) return dh::launch_render<dh::SRC_BOXES>((cudaStream_t)stream, p, mode, B, workspace, workspace_bytes);
+    return dh::launch_render<dh::SRC_BATCHED>((cudaStream_t)stream, p, mode, B, workspace, workspace_bytes);
+}
+
+size_t dh_batched_workspace_bytes(int64_t batch_size, int64_t max_num_targets, int64_t num_classes) {
+    if (batch_size < 0 || max_num_targets < 0 || num_classes < 0) return 0;
+    if (num_classes < 1) num_classes = 1;
+    return dh::bin_workspace_bytes(batch_size, max_num_targets, num_classes) + 16;
+}
+
+int dh_draw_heatmap_batched_ws(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
+                               const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t batch_size,
+                               int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
+                               float diameter_to_sigma_factor, float k_scale, int mode, dh_status* status,
+                               void* workspace, size_t workspace_bytes) {
+    return batched_common(stream, heatmap, centers, radii, nullptr, nullptr, 1.0f, nums_targets, nums_dtype, labels,
+                          batch_size, max_num_targets, num_classes, height, width, diameter_to_sigma_factor, k_scale,
+                          mode, status, nullptr, 0, workspace, workspace_bytes);
 }
 
 int dh_draw_heatmap_batched(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
                             const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t batch_size,
                             int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
                             float diameter_to_sigma_factor, float k_scale, int mode, dh_status* status) {
-    return batched_common(stream, heatmap, centers, radii, nullptr, nullptr, 1.0f, nums_targets, nums_dtype, labels,
-                          batch_size, max_num_targets, num_classes, height, width, diameter_to_sigma_factor, k_scale,
-                          mode, status);
+    return dh_draw_heatmap_batched_ws(stream, heatmap, centers, radii, nums_targets, nums_dtype, labels, batch_size,
+                                      max_num_targets, num_classes, height, width, diameter_to_sigma_factor, k_scale, mode,
+                                      status, nullptr, 0);
 }
 
 int dh_draw_heatmap_batched_from_boxes(void* stream, float* heatmap, const float* centers_xy, const float* bboxes_xyxy,
@@ -964,6 +1050,19 @@ int dh_draw_heatmap_batched_from_boxes(void* stream, float* heatmap, const float
                                        int64_t num_classes, int64_t height, int64_t width,
                                        float diameter_to_sigma_factor, float k_scale, int mode, int32_t* centers_out,
                                        int32_t* radii_out, dh_status* status) {
+    return dh_draw_heatmap_batched_from_boxes_ws(stream, heatmap, centers_xy, bboxes_xyxy, out_size_factor, nums_targets,
+                                                 nums_dtype, labels, batch_size, max_num_targets, num_classes, height, width,
+                                                 diameter_to_sigma_factor, k_scale, mode, centers_out, radii_out, status,
+                                                 nullptr, 0);
+}
+
+int dh_draw_heatmap_batched_from_boxes_ws(void* stream, float* heatmap, const float* centers_xy, const float* bboxes_xyxy,
+                                          float out_size_factor, const void* nums_targets, int nums_dtype,
+                                          const int32_t* labels, int64_t batch_size, int64_t max_num_targets,
+                                          int64_t num_classes, int64_t height, int64_t width,
+                                          float diameter_to_sigma_factor, float k_scale, int mode, int32_t* centers_out,
+                                          int32_t* radii_out, dh_status* status, void* workspace,
+                                          size_t workspace_bytes) {
     if ((centers_out == nullptr) != (radii_out == nullptr)) return DH_ERR_INVALID_ARGUMENT;
     if (batch_size > 0 && max_num_targets > 0 && (!centers_xy || !bboxes_xyxy)) return DH_ERR_INVALID_ARGUMENT;
     if (centers_out != nullptr) {  // integer outputs requested: K1 then the integer-input renderer
@@ -972,11 +1071,11 @@ int dh_draw_heatmap_batched_from_boxes(void* stream, float* heatmap, const float
         if (st != DH_OK) return st;
         return batched_common(stream, heatmap, centers_out, radii_out, nullptr, nullptr, 1.0f, nums_targets, nums_dtype,
                               labels, batch_size, max_num_targets, num_classes, height, width,
-                              diameter_to_sigma_factor, k_scale, mode, status);
+                              diameter_to_sigma_factor, k_scale, mode, status, nullptr, 0, workspace, workspace_bytes);
     }
     return batched_common(stream, heatmap, nullptr, nullptr, centers_xy, bboxes_xyxy, out_size_factor, nums_targets,
                           nums_dtype, labels, batch_size, max_num_targets, num_classes, height, width,
-                          diameter_to_sigma_factor, k_scale, mode, status);
+                          diameter_to_sigma_factor, k_scale, mode, status, nullptr, 0, workspace, workspace_bytes);
 }
 
 int dh_draw_heatmap_batched_from_boxes_digest(void* stream, float* heatmap, const float* centers_xy,
@@ -986,17 +1085,41 @@ int dh_draw_heatmap_batched_from_boxes_digest(void* stream, float* heatmap, cons
                                               int64_t height, int64_t width, float diameter_to_sigma_factor,
                                               float k_scale, int64_t index_base, uint64_t* digest_out3,
                                               dh_status* status) {
+    return dh_draw_heatmap_batched_from_boxes_digest_ws(stream, heatmap, centers_xy, bboxes_xyxy, out_size_factor,
+                                                        nums_targets, nums_dtype, labels, batch_size, max_num_targets,
+                                                        num_classes, height, width, diameter_to_sigma_factor, k_scale,
+                                                        index_base, digest_out3, status, nullptr, 0);
+}
+
+int dh_draw_heatmap_batched_from_boxes_digest_ws(void* stream, float* heatmap, const float* centers_xy,
+                                                 const float* bboxes_xyxy, float out_size_factor,
+                                                 const void* nums_targets, int nums_dtype, const int32_t* labels,
+                                                 int64_t batch_size, int64_t max_num_targets, int64_t num_classes,
+                                                 int64_t height, int64_t width, float diameter_to_sigma_factor,
+                                                 float k_scale, int64_t index_base, uint64_t* digest_out3,
+                                                 dh_status* status, void* workspace, size_t workspace_bytes) {
     if (!digest_out3) return DH_ERR_INVALID_ARGUMENT;
     if (batch_size > 0 && max_num_targets > 0 && (!centers_xy || !bboxes_xyxy)) return DH_ERR_INVALID_ARGUMENT;
     return batched_common(stream, heatmap, nullptr, nullptr, centers_xy, bboxes_xyxy, out_size_factor, nums_targets,
                           nums_dtype, labels, batch_size, max_num_targets, num_classes, height, width,
-                          diameter_to_sigma_factor, k_scale, DH_MODE_FRESH, status, digest_out3, index_base);
+                          diameter_to_sigma_factor, k_scale, DH_MODE_FRESH, status, digest_out3, index_base, workspace,
+                          workspace_bytes);
 }
 
 int dh_render_heatmap_batched_16(void* stream, void* heatmap, int out_dtype, const int32_t* centers, const int32_t* radii,
                                  const float* centers_xy, const float* bboxes_xyxy, float out_size_factor,
                                  const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t B, int64_t T,
                                  int64_t C, int64_t H, int64_t W, float factor, float k, dh_status* status) {
+    return dh_render_heatmap_batched_16_ws(stream, heatmap, out_dtype, centers, radii, centers_xy, bboxes_xyxy,
+                                           out_size_factor, nums_targets, nums_dtype, labels, B, T, C, H, W, factor, k, status,
+                                           nullptr, 0);
+}
+
+int dh_render_heatmap_batched_16_ws(void* stream, void* heatmap, int out_dtype, const int32_t* centers,
+                                    const int32_t* radii, const float* centers_xy, const float* bboxes_xyxy,
+                                    float out_size_factor, const void* nums_targets, int nums_dtype, const int32_t* labels,
+                                    int64_t B, int64_t T, int64_t C, int64_t H, int64_t W, float factor, float k,
+                                    dh_status* status, void* workspace, size_t workspace_bytes) {
     if (out_dtype != DH_OUT_F16 && out_dtype != DH_OUT_BF16) return DH_ERR_INVALID_ARGUMENT;
     if (B < 0 || T < 0) return DH_ERR_INVALID_ARGUMENT;
     if (nums_dtype != DH_SIZES_I32 && nums_dtype != DH_SIZES_I64) return DH_ERR_INVALID_ARGUMENT;
@@ -1029,8 +1152,8 @@ int dh_render_heatmap_batched_16(void* stream, void* heatmap, int out_dtype, con
     p.factor = factor;
     p.k = k;
     p.status = status;
-    if (boxes) return dh::launch_render16<dh::SRC_BOXES>((cudaStream_t)stream, p, out_dtype);
-    return dh::launch_render16<dh::SRC_BATCHED>((cudaStream_t)stream, p, out_dtype);
+    if (boxes) return dh::launch_render16<dh::SRC_BOXES>((cudaStream_t)stream, p, out_dtype, B, workspace, workspace_bytes);
+    return dh::launch_render16<dh::SRC_BATCHED>((cudaStream_t)stream, p, out_dtype, B, workspace, workspace_bytes);
 }
 
 // Flat path: direct scan when (units x objects) is small, else counting sort by plane.

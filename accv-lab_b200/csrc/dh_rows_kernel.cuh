@@ -37,6 +37,17 @@ struct __align__(16) ObjI {
     float w;  // 1/var (> 0)
 };
 
+// entry of a pre-binned object list (bin_kernel, dh_groups2_kernel.cuh)
+__device__ __forceinline__ ObjI ld_bin(const void* __restrict__ list, long long i) {
+    const int4 q = __ldg(reinterpret_cast<const int4*>(list) + i);
+    ObjI o;
+    o.x = q.x;
+    o.y = q.y;
+    o.r = q.z;
+    o.w = __int_as_float(q.w);
+    return o;
+}
+
 // Slot loads of the RaggedBatch arrays: one 8- / 16-byte load when the array base allows it (`p.in_vec`, checked on the
 // host), scalar loads otherwise — a contiguous torch tensor may start at any 4-byte offset of its storage, and the
 // reference reads these arrays with scalar int loads (cuh:57-58,86-87), so such inputs must keep working.

@@ -45,6 +45,13 @@ const void* sizes_ptr(const at::Tensor& nums_targets, int& tag) {
     return nums_targets.data_ptr();
 }
 
+// Bin-list workspace of the batched entries (K2 pre-pass, dh_b200.h dh_batched_workspace_bytes): from torch's caching
+// allocator on the current stream — stream-ordered, no device synchronisation, re-used across calls by the allocator.
+at::Tensor bin_workspace(const at::Tensor& like, int64_t B, int64_t T, int64_t C, size_t& bytes) {
+    bytes = dh_batched_workspace_bytes(B, T, C);
+    return at::empty({(int64_t)std::max<size_t>(bytes, 16)}, like.options().dtype(at::kByte));
+}
+
 // ---- flat entry (draw_heatmap_cuda.cu:62-89) ---------------------------------------------------------------
 void draw_heatmap_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tensor& radii,
                        const at::Tensor& heatmap_idxes, float diameter_to_sigma_factor, float k_scale, int mode) {
@@ -135,19 +142,22 @@ void batched_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tens
     int tag = 0;
     const void* sizes = sizes_ptr(nums_targets, tag);
     const bool cw = labels != nullptr;
+    size_t wsb = 0;
+    at::Tensor ws = bin_workspace(heatmap, heatmap.size(0), radii.size(1), cw ? heatmap.size(1) : 1, wsb);
     if (const int o16 = out16_tag(heatmap)) {  // fp16 / bf16 planes: FRESH only
-        check_status(dh_render_heatmap_batched_16(stream.stream(), heatmap.data_ptr(), o16, centers.data_ptr<int>(),
-                                                  radii.data_ptr<int>(), nullptr, nullptr, 1.0f, sizes, tag,
-                                                  cw ? labels_ptr(*labels) : nullptr, heatmap.size(0), radii.size(1),
-                                                  cw ? heatmap.size(1) : 1, heatmap.size(cw ? 2 : 1),
-                                                  heatmap.size(cw ? 3 : 2), factor, k, nullptr),
+        check_status(dh_render_heatmap_batched_16_ws(stream.stream(), heatmap.data_ptr(), o16, centers.data_ptr<int>(),
+                                                     radii.data_ptr<int>(), nullptr, nullptr, 1.0f, sizes, tag,
+                                                     cw ? labels_ptr(*labels) : nullptr, heatmap.size(0), radii.size(1),
+                                                     cw ? heatmap.size(1) : 1, heatmap.size(cw ? 2 : 1),
+                                                     heatmap.size(cw ? 3 : 2), factor, k, nullptr, ws.data_ptr(), wsb),
                      "render_heatmap_batched (16-bit planes)");
         return;
     }
-    check_status(dh_draw_heatmap_batched(stream.stream(), heatmap.data_ptr<float>(), centers.data_ptr<int>(),
-                                         radii.data_ptr<int>(), sizes, tag, cw ? labels_ptr(*labels) : nullptr,
-                                         heatmap.size(0), radii.size(1), cw ? heatmap.size(1) : 1,
-                                         heatmap.size(cw ? 2 : 1), heatmap.size(cw ? 3 : 2), factor, k, mode, nullptr),
+    check_status(dh_draw_heatmap_batched_ws(stream.stream(), heatmap.data_ptr<float>(), centers.data_ptr<int>(),
+                                            radii.data_ptr<int>(), sizes, tag, cw ? labels_ptr(*labels) : nullptr,
+                                            heatmap.size(0), radii.size(1), cw ? heatmap.size(1) : 1,
+                                            heatmap.size(cw ? 2 : 1), heatmap.size(cw ? 3 : 2), factor, k, mode, nullptr,
+                                            ws.data_ptr(), wsb),
                  "draw_heatmap_batched");
 }
 
@@ -243,22 +253,24 @@ void render_heatmap_from_boxes(at::Tensor& heatmaps, const at::Tensor& centers, 
     auto stream = at::cuda::getCurrentCUDAStream();
     int tag = 0;
     const void* sizes = sizes_ptr(nums_targets, tag);
+    size_t wsb = 0;
+    at::Tensor ws = bin_workspace(heatmaps, heatmaps.size(0), centers.size(1), cw ? heatmaps.size(1) : 1, wsb);
     if (o16 != 0) {  // fp16 / bf16 planes: FRESH only
-        check_status(dh_render_heatmap_batched_16(stream.stream(), heatmaps.data_ptr(), o16, nullptr, nullptr,
-                                                  centers.data_ptr<float>(), bboxes.data_ptr<float>(),
-                                                  (float)out_size_factor, sizes, tag, cw ? labels_ptr(*lab) : nullptr,
-                                                  heatmaps.size(0), centers.size(1), cw ? heatmaps.size(1) : 1,
-                                                  heatmaps.size(cw ? 2 : 1), heatmaps.size(cw ? 3 : 2),
-                                                  diameter_to_sigma_factor, k_scale, nullptr),
+        check_status(dh_render_heatmap_batched_16_ws(stream.stream(), heatmaps.data_ptr(), o16, nullptr, nullptr,
+                                                     centers.data_ptr<float>(), bboxes.data_ptr<float>(),
+                                                     (float)out_size_factor, sizes, tag, cw ? labels_ptr(*lab) : nullptr,
+                                                     heatmaps.size(0), centers.size(1), cw ? heatmaps.size(1) : 1,
+                                                     heatmaps.size(cw ? 2 : 1), heatmaps.size(cw ? 3 : 2),
+                                                     diameter_to_sigma_factor, k_scale, nullptr, ws.data_ptr(), wsb),
                      "render_heatmap_from_boxes (16-bit planes)");
         return;
     }
-    check_status(dh_draw_heatmap_batched_from_boxes(
+    check_status(dh_draw_heatmap_batched_from_boxes_ws(
                      stream.stream(), heatmaps.data_ptr<float>(), centers.data_ptr<float>(), bboxes.data_ptr<float>(),
                      (float)out_size_factor, sizes, tag, cw ? labels_ptr(*lab) : nullptr, heatmaps.size(0),
                      centers.size(1), cw ? heatmaps.size(1) : 1, heatmaps.size(cw ? 2 : 1), heatmaps.size(cw ? 3 : 2),
                      diameter_to_sigma_factor, k_scale, fresh ? DH_MODE_FRESH : DH_MODE_ACCUMULATE, nullptr, nullptr,
-                     nullptr),
+                     nullptr, ws.data_ptr(), wsb),
                  "render_heatmap_from_boxes");
 }
 

@@ -87,6 +87,9 @@ int dh_radius_center(void* stream, const float* centers_xy, const float* bboxes_
                      int64_t n, int32_t* centers_out, int32_t* radii_out);
 
 /* ---- batched entry (RaggedBatch layout) ----------------------------------------------
+ * Alignment: `centers` (and `centers_xy` below) should be 8-byte and `bboxes_xyxy` 16-byte aligned — each slot is then
+ * read with one vector load; arrays that are only 4-byte aligned (a contiguous torch view at an odd storage offset)
+ * are accepted and read with scalar loads, as the reference does (cuh:57-58,86-87).
  * Replaces draw_heatmap_batched_cuda(cudaStream_t, float*, const int*, const int*, const int*,
  *   int H, int W, int T, float factor, float k, int B, int C = 0, const int* labels = nullptr)
  * (DH/accvlab/draw_heatmap/csrc/draw_heatmap_cuda.cu:43-60; kernel cuh:76-109).
@@ -129,6 +132,37 @@ int dh_draw_heatmap_batched_from_boxes_digest(void* stream, float* heatmap, cons
                                               float k_scale, int64_t index_base, uint64_t* digest_out3,
                                               dh_status* status);
 
+/* ---- the same entries with a caller-provided bin-list workspace (K2 as a pre-pass) -----------------------
+ * SURVEY.md 8(b) "C-level ABI": "a caller-provided workspace pointer + size (plus a *_workspace_bytes query) for the
+ * bin lists". With a DEVICE workspace of at least dh_batched_workspace_bytes(B, T, C) bytes (16-byte aligned; contents
+ * undefined before and after) the call is TWO launches: bin_kernel reads every slot of the RaggedBatch arrays once
+ * (validity cuh:84, label, K1 for float boxes, window / sigma arithmetic cuh:61-68) and counting-sorts each sample's
+ * objects by class into compact per-plane lists; the renderer then takes a plane's list with one 8-byte load per unit
+ * and renders planes of <= 32 objects warp-autonomously (no block barrier). Results are bit-identical to the entries
+ * above; dh_status counts every skipped object exactly once. workspace == NULL (or too small, or a shape the main
+ * renderer does not serve, or num_classes > 2048) falls back to the single-launch path of the entry above — never an
+ * error. The workspace must not be shared by calls that may run concurrently. */
+size_t dh_batched_workspace_bytes(int64_t batch_size, int64_t max_num_targets, int64_t num_classes);
+int dh_draw_heatmap_batched_ws(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
+                               const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t batch_size,
+                               int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
+                               float diameter_to_sigma_factor, float k_scale, int mode, dh_status* status,
+                               void* workspace, size_t workspace_bytes);
+int dh_draw_heatmap_batched_from_boxes_ws(void* stream, float* heatmap, const float* centers_xy,
+                                          const float* bboxes_xyxy, float out_size_factor, const void* nums_targets,
+                                          int nums_dtype, const int32_t* labels, int64_t batch_size,
+                                          int64_t max_num_targets, int64_t num_classes, int64_t height,
+                                          int64_t width, float diameter_to_sigma_factor, float k_scale, int mode,
+                                          int32_t* centers_out, int32_t* radii_out, dh_status* status,
+                                          void* workspace, size_t workspace_bytes);
+int dh_draw_heatmap_batched_from_boxes_digest_ws(void* stream, float* heatmap, const float* centers_xy,
+                                                 const float* bboxes_xyxy, float out_size_factor,
+                                                 const void* nums_targets, int nums_dtype, const int32_t* labels,
+                                                 int64_t batch_size, int64_t max_num_targets, int64_t num_classes,
+                                                 int64_t height, int64_t width, float diameter_to_sigma_factor,
+                                                 float k_scale, int64_t index_base, uint64_t* digest_out3,
+                                                 dh_status* status, void* workspace, size_t workspace_bytes);
+
 /* ---- 16-bit heatmap planes (not in the reference, whose heatmaps are float32 only:
  * draw_heatmap_cuda.cu:84,117,160 `data_ptr<float>()`) -------------------------------------
  * DH_MODE_FRESH render into fp16 or bf16 planes: every value is computed in fp32 exactly as by the fp32 entries and
@@ -145,6 +179,13 @@ int dh_render_heatmap_batched_16(void* stream, void* heatmap, int out_dtype, con
                                  const int32_t* labels, int64_t batch_size, int64_t max_num_targets,
                                  int64_t num_classes, int64_t height, int64_t width, float diameter_to_sigma_factor,
                                  float k_scale, dh_status* status);
+/* ... with the bin-list workspace of dh_batched_workspace_bytes (see above) */
+int dh_render_heatmap_batched_16_ws(void* stream, void* heatmap, int out_dtype, const int32_t* centers,
+                                    const int32_t* radii, const float* centers_xy, const float* bboxes_xyxy,
+                                    float out_size_factor, const void* nums_targets, int nums_dtype,
+                                    const int32_t* labels, int64_t batch_size, int64_t max_num_targets,
+                                    int64_t num_classes, int64_t height, int64_t width, float diameter_to_sigma_factor,
+                                    float k_scale, dh_status* status, void* workspace, size_t workspace_bytes);
 
 /* ---- flat entry (concatenated objects + per-object plane index) ----------------------
  * Replaces draw_heatmap_cuda(cudaStream_t, float*, const int*, const int*, const int*, int H, int W,

@@ -38,6 +38,14 @@ SIGNATURES = {
                                                        _f, _i64, _p, _p]),
     "dh_render_heatmap_batched_16": (_i, [_p, _p, _i, _p, _p, _p, _p, _f, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f,
                                           _p]),
+    "dh_batched_workspace_bytes": (_sz, [_i64, _i64, _i64]),
+    "dh_draw_heatmap_batched_ws": (_i, [_p, _p, _p, _p, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f, _i, _p, _p, _sz]),
+    "dh_draw_heatmap_batched_from_boxes_ws": (_i, [_p, _p, _p, _p, _f, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f,
+                                                   _i, _p, _p, _p, _p, _sz]),
+    "dh_draw_heatmap_batched_from_boxes_digest_ws": (_i, [_p, _p, _p, _p, _f, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f,
+                                                          _f, _i64, _p, _p, _p, _sz]),
+    "dh_render_heatmap_batched_16_ws": (_i, [_p, _p, _i, _p, _p, _p, _p, _f, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f,
+                                             _f, _p, _p, _sz]),
     "dh_draw_heatmap_workspace_bytes": (_sz, [_i64, _i64]),
     "dh_draw_heatmap": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _i, _p, _sz, _p]),
     "dh_checksum": (_i, [_p, _p, _i64, _i64, _p]),
@@ -103,7 +111,26 @@ def stream_ptr():
 
 
 # ---- convenience wrappers over torch CUDA tensors (still only raw pointers cross the ABI) -------------
-def draw_batched(lib, heat, centers, radii, sizes, labels=None, factor=6.0, k=1.0, mode=DH_MODE_ACCUMULATE, status=None):
+# `ws`: True  = the *_ws entry with a bin-list workspace (K2 pre-pass + warp-autonomous renderer: the product's main path,
+#               what the torch binding, bench.py and the host entry use);
+#       False = the workspace-less entry (single-launch renderer);  None = USE_WS (env DH_TEST_WS, default 1).
+USE_WS = os.environ.get("DH_TEST_WS", "1") != "0"
+
+
+def _workspace(lib, B, T, C, device, ws):
+    """(workspace tensor or None, bytes) for the batched entries."""
+    import torch
+
+    if ws is None:
+        ws = USE_WS
+    if not ws:
+        return None, 0
+    n = int(lib.dh_batched_workspace_bytes(B, T, C))
+    return torch.empty(max(n, 16), dtype=torch.uint8, device=device), n
+
+
+def draw_batched(lib, heat, centers, radii, sizes, labels=None, factor=6.0, k=1.0, mode=DH_MODE_ACCUMULATE, status=None,
+                 ws=None):
     import torch
 
     B, T = radii.shape
@@ -112,14 +139,19 @@ def draw_batched(lib, heat, centers, radii, sizes, labels=None, factor=6.0, k=1.
     else:
         C, (H, W) = 1, heat.shape[1:]
     tag = DH_SIZES_I64 if sizes.dtype == torch.int64 else DH_SIZES_I32
-    st = lib.dh_draw_heatmap_batched(stream_ptr(), ptr(heat), ptr(centers), ptr(radii), ptr(sizes), tag, ptr(labels), B, T,
-                                     C, H, W, factor, k, mode, ptr(status))
+    wt, wn = _workspace(lib, B, T, C, heat.device, ws)
+    if wt is None:
+        st = lib.dh_draw_heatmap_batched(stream_ptr(), ptr(heat), ptr(centers), ptr(radii), ptr(sizes), tag, ptr(labels), B,
+                                         T, C, H, W, factor, k, mode, ptr(status))
+    else:
+        st = lib.dh_draw_heatmap_batched_ws(stream_ptr(), ptr(heat), ptr(centers), ptr(radii), ptr(sizes), tag, ptr(labels),
+                                            B, T, C, H, W, factor, k, mode, ptr(status), ptr(wt), wn)
     check(lib, st, "dh_draw_heatmap_batched")
     return heat
 
 
 def draw_from_boxes(lib, heat, centers_f, bboxes_f, osf, sizes, labels=None, factor=6.0, k=1.0, mode=DH_MODE_FRESH,
-                    centers_out=None, radii_out=None):
+                    centers_out=None, radii_out=None, ws=None, status=None):
     import torch
 
     B, T = centers_f.shape[:2]
@@ -128,9 +160,15 @@ def draw_from_boxes(lib, heat, centers_f, bboxes_f, osf, sizes, labels=None, fac
     else:
         C, (H, W) = 1, heat.shape[1:]
     tag = DH_SIZES_I64 if sizes.dtype == torch.int64 else DH_SIZES_I32
-    st = lib.dh_draw_heatmap_batched_from_boxes(stream_ptr(), ptr(heat), ptr(centers_f), ptr(bboxes_f), osf, ptr(sizes),
-                                                tag, ptr(labels), B, T, C, H, W, factor, k, mode, ptr(centers_out),
-                                                ptr(radii_out), None)
+    wt, wn = _workspace(lib, B, T, C, heat.device, ws)
+    if wt is None:
+        st = lib.dh_draw_heatmap_batched_from_boxes(stream_ptr(), ptr(heat), ptr(centers_f), ptr(bboxes_f), osf, ptr(sizes),
+                                                    tag, ptr(labels), B, T, C, H, W, factor, k, mode, ptr(centers_out),
+                                                    ptr(radii_out), ptr(status))
+    else:
+        st = lib.dh_draw_heatmap_batched_from_boxes_ws(stream_ptr(), ptr(heat), ptr(centers_f), ptr(bboxes_f), osf,
+                                                       ptr(sizes), tag, ptr(labels), B, T, C, H, W, factor, k, mode,
+                                                       ptr(centers_out), ptr(radii_out), ptr(status), ptr(wt), wn)
     check(lib, st, "dh_draw_heatmap_batched_from_boxes")
     return heat
 
@@ -139,7 +177,7 @@ DH_OUT_F16, DH_OUT_BF16 = 1, 2
 
 
 def render16(lib, heat, sizes, labels=None, centers=None, radii=None, centers_f=None, bboxes_f=None, osf=1.0, factor=6.0,
-             k=1.0, status=None, check_status=True):
+             k=1.0, status=None, check_status=True, ws=None):
     """dh_render_heatmap_batched_16 into a float16 / bfloat16 CUDA tensor (FRESH)."""
     import torch
 
@@ -151,16 +189,22 @@ def render16(lib, heat, sizes, labels=None, centers=None, radii=None, centers_f=
         C, (H, W) = 1, heat.shape[1:]
     tag = DH_SIZES_I64 if sizes.dtype == torch.int64 else DH_SIZES_I32
     out = DH_OUT_F16 if heat.dtype == torch.float16 else DH_OUT_BF16
-    st = lib.dh_render_heatmap_batched_16(stream_ptr(), ptr(heat), out, ptr(centers), ptr(radii), ptr(centers_f),
-                                          ptr(bboxes_f), osf, ptr(sizes), tag, ptr(labels), B, T, C, H, W, factor, k,
-                                          ptr(status))
+    wt, wn = _workspace(lib, B, T, C, heat.device, ws)
+    if wt is None:
+        st = lib.dh_render_heatmap_batched_16(stream_ptr(), ptr(heat), out, ptr(centers), ptr(radii), ptr(centers_f),
+                                              ptr(bboxes_f), osf, ptr(sizes), tag, ptr(labels), B, T, C, H, W, factor, k,
+                                              ptr(status))
+    else:
+        st = lib.dh_render_heatmap_batched_16_ws(stream_ptr(), ptr(heat), out, ptr(centers), ptr(radii), ptr(centers_f),
+                                                 ptr(bboxes_f), osf, ptr(sizes), tag, ptr(labels), B, T, C, H, W, factor, k,
+                                                 ptr(status), ptr(wt), wn)
     if check_status:
         check(lib, st, "dh_render_heatmap_batched_16")
     return st
 
 
 def draw_from_boxes_digest(lib, heat, centers_f, bboxes_f, osf, sizes, labels=None, factor=6.0, k=1.0, index_base=0,
-                           digest=None):
+                           digest=None, ws=None):
     """FRESH render with the digest fused into the launch; returns the int64[3] device digest (wrapping uint64)."""
     import torch
 
@@ -172,9 +216,15 @@ def draw_from_boxes_digest(lib, heat, centers_f, bboxes_f, osf, sizes, labels=No
     if digest is None:
         digest = torch.zeros(3, dtype=torch.int64, device=heat.device)
     tag = DH_SIZES_I64 if sizes.dtype == torch.int64 else DH_SIZES_I32
-    st = lib.dh_draw_heatmap_batched_from_boxes_digest(stream_ptr(), ptr(heat), ptr(centers_f), ptr(bboxes_f), osf,
-                                                       ptr(sizes), tag, ptr(labels), B, T, C, H, W, factor, k, index_base,
-                                                       ptr(digest), None)
+    wt, wn = _workspace(lib, B, T, C, heat.device, ws)
+    if wt is None:
+        st = lib.dh_draw_heatmap_batched_from_boxes_digest(stream_ptr(), ptr(heat), ptr(centers_f), ptr(bboxes_f), osf,
+                                                           ptr(sizes), tag, ptr(labels), B, T, C, H, W, factor, k,
+                                                           index_base, ptr(digest), None)
+    else:
+        st = lib.dh_draw_heatmap_batched_from_boxes_digest_ws(stream_ptr(), ptr(heat), ptr(centers_f), ptr(bboxes_f), osf,
+                                                              ptr(sizes), tag, ptr(labels), B, T, C, H, W, factor, k,
+                                                              index_base, ptr(digest), None, ptr(wt), wn)
     check(lib, st, "dh_draw_heatmap_batched_from_boxes_digest")
     return digest
 
