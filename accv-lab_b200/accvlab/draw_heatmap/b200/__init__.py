@@ -91,7 +91,7 @@ def _tensor_and_sizes(x):
 def render_heatmap_batched(centers, radii, height: Optional[int] = None, width: Optional[int] = None,
                            num_classes: Optional[int] = None, labels=None, diameter_to_sigma_factor: float = 6.0,
                            k_scale: float = 1.0, out: Optional[torch.Tensor] = None,
-                           dtype: torch.dtype = torch.float32) -> torch.Tensor:
+                           dtype: torch.dtype = torch.float32, use_workspace: bool = False) -> torch.Tensor:
     """Render a fresh heatmap (every pixel written once; zeros where nothing is drawn). Returns the heatmap.
 
     ``centers``/``radii``/``labels`` are RaggedBatches (or anything with ``.tensor`` and ``.sample_sizes``).
@@ -105,7 +105,9 @@ def render_heatmap_batched(centers, radii, height: Optional[int] = None, width: 
     if out is None:
         shape = (ct.shape[0], height, width) if lt is None else (ct.shape[0], num_classes, height, width)
         out = torch.empty(shape, dtype=dtype, device=ct.device)
-    _ext.render_heatmap_batched(out, ct, rt, sizes, lt, diameter_to_sigma_factor, k_scale, True)
+    # use_workspace=True: the two-launch path of the *_ws C-ABI entries (K2 pre-pass into a bin-list workspace from the
+    # caching allocator, then the list-fed renderer); bit-identical results, measured slower on the BASELINE configs
+    _ext.render_heatmap_batched(out, ct, rt, sizes, lt, diameter_to_sigma_factor, k_scale, True, use_workspace)
     return out
 
 
@@ -114,7 +116,7 @@ def render_heatmap_from_boxes(centers: torch.Tensor, bboxes: torch.Tensor, out_s
                               num_classes: Optional[int] = None, labels: Optional[torch.Tensor] = None,
                               diameter_to_sigma_factor: float = 6.0, k_scale: float = 1.0,
                               out: Optional[torch.Tensor] = None, fresh: bool = True,
-                              dtype: torch.dtype = torch.float32) -> torch.Tensor:
+                              dtype: torch.dtype = torch.float32, use_workspace: bool = False) -> torch.Tensor:
     """Float centres ``[B,T,2]`` + boxes ``[B,T,4]`` -> heatmap, radius/centre computation fused (one launch).
     float16 / bfloat16 heatmaps (``dtype`` or ``out``) are served in fresh mode only."""
     if out is None:
@@ -122,7 +124,7 @@ def render_heatmap_from_boxes(centers: torch.Tensor, bboxes: torch.Tensor, out_s
         out = torch.empty(shape, dtype=dtype, device=centers.device)
         fresh = True
     _ext.render_heatmap_from_boxes(out, centers, bboxes, float(out_size_factor), sample_sizes, labels,
-                                   diameter_to_sigma_factor, k_scale, fresh)
+                                   diameter_to_sigma_factor, k_scale, fresh, use_workspace)
     return out
 
 

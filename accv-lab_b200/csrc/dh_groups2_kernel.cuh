@@ -189,6 +189,12 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups2_kernel(const Ren
         clc_try_cancel(&s_clc[1], &s_full[1]);
     }
     for (;;) {
+        // ONE block barrier per unit keeps the eight warps on the same unit. Letting them drift (no barrier, the ring below
+        // alone) was measured SLOWER: 231-237 against 212 us on the 8-GPU slice of cfg5 — with two units in flight per CTA
+        // the set of addresses being written doubles (444 x 2 x 186 KB > the 126 MB L2) and the write rate falls, the same
+        // effect the write-only microbenchmarks show for larger spans per CTA (profiles/r01/experiments.md section 1,
+        // profiles/r02/call4, call6).
+        __syncthreads();
         long long plane;
         int uy0, uy1;
         unit_rows(p, u, G, plane, uy0, uy1);
@@ -281,8 +287,9 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups2_kernel(const Ren
                 }
             }
         }
-        if constexpr (!ACCUM) {  // K4a: untouched runs, by one warp per unit (rotating, so no warp is the designated laggard)
-            if (warp == (int)((k + kGWarps - 1u) % kGWarps)) zero_runs(~mask & valid, lane, plane_b, uy0, uy1, W, G, ES, zero_tile);
+        if constexpr (!ACCUM) {
+            // K4a: the untouched runs, by warp 7 (it gets the fewest striped groups in a short unit)
+            if (warp == kGWarps - 1) zero_runs(~mask & valid, lane, plane_b, uy0, uy1, W, G, ES, zero_tile);
         }
         unsigned long long gm = mask & (0x0101010101010101ull << warp);
         if (gm != 0ull && !stage_clean) {  // first touched group of this warp: establish the all-zero staging invariant

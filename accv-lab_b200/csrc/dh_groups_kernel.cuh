@@ -89,6 +89,10 @@ struct Digest {
 };
 
 // Dense path, one object into the rows [y0, y0+nrows) held in `buf` (row stride W). Warp-collective.
+// (Round 2 tried columns outer / rows inner — the x-only terms computed once per pixel and reused for the rows of the
+// group: 27 instead of 40 instructions in the inner body, but more instructions overall (ncu on cfg4: 228 M against
+// 201 M warp instructions in this function, 353 against 314 us; profiles/r02/call5/) because with two rows per group the
+// second loop nest and its prologue cost more than the shared terms save. Rows outer stays.)
 __device__ __forceinline__ void sweep_obj(unsigned* __restrict__ buf, int y0, int nrows, int W, const ObjI& o, bool kneg,
                                           int lane, int& ux0, int& ux1) {
     const int x0 = max(o.x - o.r, 0), x1 = min(o.x + o.r, W - 1);

@@ -160,7 +160,7 @@ static const void* pinned_alias(const void* h) {
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct HostLayout {
-    size_t off_centers, off_bboxes, off_sizes, off_labels, off_cksum, off_bin, bin_bytes, bin_stride, off_stage[2], total;
+    size_t off_centers, off_bboxes, off_sizes, off_labels, off_cksum, off_stage[2], total;
     int64_t chunk;
 };
 
@@ -181,11 +181,6 @@ static HostLayout host_layout(int64_t B, int64_t T, int64_t C, int64_t H, int64_
     L.off_sizes = o;   o += align256((size_t)B * 8);
     L.off_labels = o;  o += has_labels ? align256((size_t)B * T * 4) : 0;
     L.off_cksum = o;   o += 256;
-    // bin lists of the K2 pre-pass: a fixed stride per sample, so that sample ranges rendered concurrently (input
-    // pipelining, chunked copy-back) bin into disjoint slices of the one region
-    L.bin_stride = (size_t)T * 16 + (((size_t)planes_per_sample * 8 + 15) & ~(size_t)15);
-    L.bin_bytes = (size_t)B * L.bin_stride;
-    L.off_bin = o;     o += align256(L.bin_bytes);
     for (int i = 0; i < 2; ++i) {
         L.off_stage[i] = o;
         if (staging) o += align256((size_t)chunk * sample_bytes);
@@ -258,17 +253,14 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
     auto render_range = [&](cudaStream_t cs, float* dst, int64_t s0, int64_t nb) -> int {
         int r = DH_ERR_UNSUPPORTED_SHAPE;
         const int32_t* lab = has_labels ? d_labels + s0 * T : nullptr;
-        // each sample range bins into its own slice of the workspace (ranges render concurrently on two streams):
-        void* const bw = ws + L.off_bin + (size_t)s0 * L.bin_stride;
-        const size_t bin_need = (size_t)nb * L.bin_stride;  // >= dh_batched_workspace_bytes(nb, T, C) - 16 (its slack)
         if (checksum_host)  // digest fused into the render launch: the heatmap is never re-read
-            r = dh_draw_heatmap_batched_from_boxes_digest_ws(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
-                                                             d_sizes + s0, DH_SIZES_I64, lab, nb, T, C, H, W, factor, k,
-                                                             s0 * sample_elems, d_ck, nullptr, bw, bin_need);
+            r = dh_draw_heatmap_batched_from_boxes_digest(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
+                                                          d_sizes + s0, DH_SIZES_I64, lab, nb, T, C, H, W, factor, k,
+                                                          s0 * sample_elems, d_ck, nullptr);
         if (r == DH_ERR_UNSUPPORTED_SHAPE) {
-            r = dh_draw_heatmap_batched_from_boxes_ws(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
-                                                      d_sizes + s0, DH_SIZES_I64, lab, nb, T, C, H, W, factor, k,
-                                                      DH_MODE_FRESH, nullptr, nullptr, nullptr, bw, bin_need);
+            r = dh_draw_heatmap_batched_from_boxes(cs, dst, d_centers + s0 * T * 2, d_bboxes + s0 * T * 4, osf,
+                                                   d_sizes + s0, DH_SIZES_I64, lab, nb, T, C, H, W, factor, k,
+                                                   DH_MODE_FRESH, nullptr, nullptr, nullptr);
             if (r == DH_OK && checksum_host) r = dh_checksum(cs, dst, nb * sample_elems, s0 * sample_elems, d_ck);
         }
         return r;

@@ -133,7 +133,7 @@ void batched_checks(const at::Tensor& heatmap, const at::Tensor& centers, const 
 }
 
 void batched_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tensor& radii, const at::Tensor& nums_targets,
-                  const at::Tensor* labels, float factor, float k, int mode) {
+                  const at::Tensor* labels, float factor, float k, int mode, bool use_workspace = false) {
     batched_checks(heatmap, centers, radii, nums_targets, labels, mode == DH_MODE_FRESH);
     CHECK_DTYPE(centers, at::kInt);
     CHECK_DTYPE(radii, at::kInt);
@@ -142,14 +142,19 @@ void batched_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tens
     int tag = 0;
     const void* sizes = sizes_ptr(nums_targets, tag);
     const bool cw = labels != nullptr;
+    // workspace-less entries = the single-launch renderer, which measured faster than the two-launch (K2 pre-pass) path
+    // of the *_ws entries on every BASELINE config (profiles/r02/experiments.md); pass `use_workspace` through
+    // b200.render_* to try the other one
     size_t wsb = 0;
-    at::Tensor ws = bin_workspace(heatmap, heatmap.size(0), radii.size(1), cw ? heatmap.size(1) : 1, wsb);
+    at::Tensor ws;
+    if (use_workspace) ws = bin_workspace(heatmap, heatmap.size(0), radii.size(1), cw ? heatmap.size(1) : 1, wsb);
+    void* const wsp = use_workspace ? ws.data_ptr() : nullptr;
     if (const int o16 = out16_tag(heatmap)) {  // fp16 / bf16 planes: FRESH only
         check_status(dh_render_heatmap_batched_16_ws(stream.stream(), heatmap.data_ptr(), o16, centers.data_ptr<int>(),
                                                      radii.data_ptr<int>(), nullptr, nullptr, 1.0f, sizes, tag,
                                                      cw ? labels_ptr(*labels) : nullptr, heatmap.size(0), radii.size(1),
                                                      cw ? heatmap.size(1) : 1, heatmap.size(cw ? 2 : 1),
-                                                     heatmap.size(cw ? 3 : 2), factor, k, nullptr, ws.data_ptr(), wsb),
+                                                     heatmap.size(cw ? 3 : 2), factor, k, nullptr, wsp, wsb),
                      "render_heatmap_batched (16-bit planes)");
         return;
     }
@@ -157,7 +162,7 @@ void batched_mode(at::Tensor& heatmap, const at::Tensor& centers, const at::Tens
                                             radii.data_ptr<int>(), sizes, tag, cw ? labels_ptr(*labels) : nullptr,
                                             heatmap.size(0), radii.size(1), cw ? heatmap.size(1) : 1,
                                             heatmap.size(cw ? 2 : 1), heatmap.size(cw ? 3 : 2), factor, k, mode, nullptr,
-                                            ws.data_ptr(), wsb),
+                                            wsp, wsb),
                  "draw_heatmap_batched");
 }
 
@@ -180,9 +185,9 @@ void draw_heatmap_batched_classwise(at::Tensor& heatmaps, const at::Tensor& cent
 // ---- additions -----------------------------------------------------------------------------------------------
 void render_heatmap_batched(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
                             const at::Tensor& nums_targets, const c10::optional<at::Tensor>& labels,
-                            float diameter_to_sigma_factor, float k_scale, bool fresh) {
+                            float diameter_to_sigma_factor, float k_scale, bool fresh, bool use_workspace) {
     batched_mode(heatmaps, centers, radii, nums_targets, labels.has_value() ? &labels.value() : nullptr,
-                 diameter_to_sigma_factor, k_scale, fresh ? DH_MODE_FRESH : DH_MODE_ACCUMULATE);
+                 diameter_to_sigma_factor, k_scale, fresh ? DH_MODE_FRESH : DH_MODE_ACCUMULATE, use_workspace);
 }
 
 void render_heatmap_flat(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& radii,
@@ -218,7 +223,7 @@ std::tuple<at::Tensor, at::Tensor> radius_center(const at::Tensor& centers, cons
 void render_heatmap_from_boxes(at::Tensor& heatmaps, const at::Tensor& centers, const at::Tensor& bboxes,
                                double out_size_factor, const at::Tensor& nums_targets,
                                const c10::optional<at::Tensor>& labels, float diameter_to_sigma_factor, float k_scale,
-                               bool fresh) {
+                               bool fresh, bool use_workspace) {
     CHECK_INPUT(bboxes);
     CHECK_DTYPE(centers, at::kFloat);
     CHECK_DTYPE(bboxes, at::kFloat);
@@ -254,14 +259,16 @@ void render_heatmap_from_boxes(at::Tensor& heatmaps, const at::Tensor& centers, 
     int tag = 0;
     const void* sizes = sizes_ptr(nums_targets, tag);
     size_t wsb = 0;
-    at::Tensor ws = bin_workspace(heatmaps, heatmaps.size(0), centers.size(1), cw ? heatmaps.size(1) : 1, wsb);
+    at::Tensor ws;
+    if (use_workspace) ws = bin_workspace(heatmaps, heatmaps.size(0), centers.size(1), cw ? heatmaps.size(1) : 1, wsb);
+    void* const wsp = use_workspace ? ws.data_ptr() : nullptr;
     if (o16 != 0) {  // fp16 / bf16 planes: FRESH only
         check_status(dh_render_heatmap_batched_16_ws(stream.stream(), heatmaps.data_ptr(), o16, nullptr, nullptr,
                                                      centers.data_ptr<float>(), bboxes.data_ptr<float>(),
                                                      (float)out_size_factor, sizes, tag, cw ? labels_ptr(*lab) : nullptr,
                                                      heatmaps.size(0), centers.size(1), cw ? heatmaps.size(1) : 1,
                                                      heatmaps.size(cw ? 2 : 1), heatmaps.size(cw ? 3 : 2),
-                                                     diameter_to_sigma_factor, k_scale, nullptr, ws.data_ptr(), wsb),
+                                                     diameter_to_sigma_factor, k_scale, nullptr, wsp, wsb),
                      "render_heatmap_from_boxes (16-bit planes)");
         return;
     }
@@ -270,7 +277,7 @@ void render_heatmap_from_boxes(at::Tensor& heatmaps, const at::Tensor& centers, 
                      (float)out_size_factor, sizes, tag, cw ? labels_ptr(*lab) : nullptr, heatmaps.size(0),
                      centers.size(1), cw ? heatmaps.size(1) : 1, heatmaps.size(cw ? 2 : 1), heatmaps.size(cw ? 3 : 2),
                      diameter_to_sigma_factor, k_scale, fresh ? DH_MODE_FRESH : DH_MODE_ACCUMULATE, nullptr, nullptr,
-                     nullptr, ws.data_ptr(), wsb),
+                     nullptr, wsp, wsb),
                  "render_heatmap_from_boxes");
 }
 
@@ -697,7 +704,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           "Batched drawing with explicit mode: fresh=True overwrites every pixel (zero-init fused, nothing read).",
           pybind11::arg("heatmaps"), pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"),
           pybind11::arg("labels") = pybind11::none(), pybind11::arg("diameter_to_sigma_factor") = 6.f,
-          pybind11::arg("k_scale") = 1.f, pybind11::arg("fresh") = false);
+          pybind11::arg("k_scale") = 1.f, pybind11::arg("fresh") = false, pybind11::arg("use_workspace") = false);
     m.def("render_heatmap_flat", &render_heatmap_flat, "Flat drawing with explicit mode.", pybind11::arg("heatmaps"),
           pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("heatmap_idxes"),
           pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f, pybind11::arg("fresh") = false);
@@ -707,7 +714,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           "radius_center fused into the batched renderer (float boxes in, one launch).", pybind11::arg("heatmaps"),
           pybind11::arg("centers"), pybind11::arg("bboxes"), pybind11::arg("out_size_factor"),
           pybind11::arg("nums_targets"), pybind11::arg("labels") = pybind11::none(),
-          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f, pybind11::arg("fresh") = false);
+          pybind11::arg("diameter_to_sigma_factor") = 6.f, pybind11::arg("k_scale") = 1.f, pybind11::arg("fresh") = false,
+          pybind11::arg("use_workspace") = false);
     m.def("fill_probe", &fill_probe, "Zero-fill a tensor with the renderer's store path (write-only ceiling).",
           pybind11::arg("tensor"));
     m.def("checksum_", &checksum_, "digest[3] (int64, CUDA) += order-independent digest of a float32 CUDA tensor.",

@@ -24,9 +24,6 @@ import sys
 import threading
 import time
 
-if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":  # at this level NCCL prints its banner on STDOUT, and the
-    os.environ["NCCL_DEBUG"] = "WARN"                       # contract is ONE JSON line there (set before torch loads)
-
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -51,6 +48,8 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=8.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--two-launch", action="store_true", help="A/B: K2 pre-pass + list-fed renderer (the *_ws entries)")
+    ap.add_argument("--no-side-legs", action="store_true", help="skip cfg1-4 / accumulate / reference-GPU side records")
     return ap.parse_args()
 
 
@@ -251,9 +250,10 @@ def run_ours(args):
     stream = torch.cuda.current_stream()
     sp = ctypes.c_void_p(stream.cuda_stream)
 
-    # bin-list workspace of the K2 pre-pass (include/dh_b200.h dh_batched_workspace_bytes): held by the caller
-    ws_bytes = int(lib.dh_batched_workspace_bytes(nb, T, C))
-    ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=dev)
+    # --two-launch: the *_ws entry with a caller-held bin-list workspace (K2 pre-pass + list-fed renderer) instead of the
+    # single-launch renderer; A/B measurements only (profiles/r02/experiments.md)
+    ws_bytes = int(lib.dh_batched_workspace_bytes(nb, T, C)) if args.two_launch else 0
+    ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=dev) if args.two_launch else None
 
     def step(i, sp=sp):
         st = lib.dh_draw_heatmap_batched_from_boxes_ws(sp, _cabi.ptr(heats[i % nbuf]), _cabi.ptr(d_cf), _cabi.ptr(d_bf),
@@ -261,7 +261,7 @@ def run_ours(args):
                                                        _cabi.ptr(d_lab), nb, T, C, H, W, FACTOR, K_SCALE,
                                                        _cabi.DH_MODE_FRESH, None, None, None, _cabi.ptr(ws), ws_bytes)
         if st != 0:
-            raise RuntimeError(f"dh_draw_heatmap_batched_from_boxes_ws: {lib.dh_status_string(st).decode()}")
+            raise RuntimeError(f"dh_draw_heatmap_batched_from_boxes: {lib.dh_status_string(st).decode()}")
 
     def barrier():
         torch.cuda.synchronize()
@@ -337,9 +337,8 @@ def run_ours(args):
     # ---- roofline of the (only) kernel of the step, from this rank's own launch durations ----
     peak, peak_src, _ = load_peaks()
     algo_bytes = out_bytes + nb * T * (8 + 16 + 4) + nb * 8  # one fp32 store per pixel + the padded input slots
-    # a step = bin_kernel (K2 pre-pass, microseconds) + groups2_kernel (the dominant one) back to back on one stream;
-    # CUDA events bracket steps, so the renderer's launch duration is bounded from above by the step time: `achieved` is
-    # conservative (the ncu launch list under profiles/ gives the split)
+    # one launch per step (groups_kernel, K1 fused); with --two-launch the step is bin_kernel + groups2_kernel and the
+    # step time bounds the renderer's duration from above
     launch_ms = ms_total / max(args.steps, 1)
     achieved = algo_bytes / (launch_ms * 1e-3) / 1e9
     traffic = None
@@ -348,7 +347,8 @@ def run_ours(args):
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "dh::groups2_kernel<false,false,0> (+ dh::bin_kernel<SRC_BOXES> in the same step)",
+                "traffic": traffic, "kernel": ("dh::groups_kernel<false,SRC_BOXES,false,OUT_F32>" if not args.two_launch else
+                           "dh::groups2_kernel<false,false,OUT_F32> (+ dh::bin_kernel<SRC_BOXES> in the same step)"),
                 "peak_source": peak_src, "launches_per_step": launches / max(args.steps, 1),
                 "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": launch_ms,
                 "frac_of_nominal_8TBs": achieved / 8000.0, "cuda_graph_replay_ms_per_step": graph_ms,
@@ -376,6 +376,168 @@ def run_ours(args):
     return dict(torch=torch, lib=lib, _cabi=_cabi, dist=dist, dev=dev, rank=rank, world=world, w=w, w_all=w_all, lo=lo,
                 host=(h_cf, h_bf, h_sz, h_lab), heats=heats, value=value, ms_step=ms_step, launches=launches,
                 roofline=roofline, digest=digest, sampler=sampler, warm=warm, barrier=barrier)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Side legs (rank 0, N=1 only; each bounded to about a second): the other BASELINE configs, the drop-in accumulate path
+# and the unmodified reference CUDA extension, so that these numbers are driver-visible and not only builder records.
+def _ev_ms(torch, fn, reps, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+def _fresh_call(lib, _cabi, sp, heat, d, cfg, nb, T, ws, ws_bytes):
+    st = lib.dh_draw_heatmap_batched_from_boxes_ws(sp, _cabi.ptr(heat), _cabi.ptr(d[0]), _cabi.ptr(d[1]), float(cfg.osf),
+                                                   _cabi.ptr(d[2]), _cabi.DH_SIZES_I64, _cabi.ptr(d[3]), nb, T, cfg.C, cfg.H,
+                                                   cfg.W, FACTOR, K_SCALE, _cabi.DH_MODE_FRESH, None, None, None,
+                                                   _cabi.ptr(ws), ws_bytes)
+    if st != 0:
+        raise RuntimeError(lib.dh_status_string(st).decode())
+
+
+def side_configs_leg(ctx, peak):
+    """cfg1-cfg4: FRESH render with K1 fused, CUDA events over back-to-back steps on buffers rotated
+    over > 512 MB, plus the same steps replayed from a CUDA graph (launch-bound configs)."""
+    torch, lib, _cabi, dev = (ctx[k] for k in ("torch", "lib", "_cabi", "dev"))
+    sp = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    out = {}
+    for name in ("cfg1", "cfg2", "cfg3", "cfg4"):
+        w = workloads.make(name)
+        cfg = w.cfg
+        d = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (w.centers_f, w.bboxes_f, w.sizes, w.labels)]
+        nbuf = int(min(64, -(-(512 << 20) // w.out_bytes)))
+        heats = [torch.empty((w.B, cfg.C, cfg.H, cfg.W), dtype=torch.float32, device=dev) for _ in range(nbuf)]
+        wsb, ws = 0, None  # single-launch renderer
+        it = [0]
+
+        def step(sp_=sp):
+            it[0] += 1
+            _fresh_call(lib, _cabi, sp_, heats[it[0] % nbuf], d, cfg, w.B, w.T, ws, wsb)
+
+        reps = 400 if name != "cfg4" else 100
+        ms = _ev_ms(torch, step, reps, warm=20)
+        graph_ms = None
+        try:
+            g = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.graph(g, stream=side):
+                csp = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+                for _ in range(nbuf):
+                    step(csp)
+            graph_ms = _ev_ms(torch, g.replay, max(3, reps // nbuf), warm=3) / nbuf
+        except Exception as e:
+            print(f"[bench] {name}: CUDA-graph replay skipped: {e!r}", file=sys.stderr)
+        algo = w.out_bytes + w.B * w.T * 28 + w.B * 8
+        r = {"planes": w.planes, "output_bytes": w.out_bytes, "ms_per_step": ms, "heatmaps_per_s": w.planes / (ms * 1e-3),
+             "GBps": algo / (ms * 1e-3) / 1e9, "frac": algo / (ms * 1e-3) / 1e9 / peak, "cuda_graph_replay_ms": graph_ms,
+             "steps": reps, "rotating_buffers": nbuf}
+        if name == "cfg4":  # not an HBM config: 1024 boxes of r 16..64 on every 512x512 plane -> pixel-object pairs
+            ci, ri = _cabi.radius_center(lib, d[0], d[1], float(cfg.osf))
+            x, y, rr = ci[..., 0].long(), ci[..., 1].long(), ri.long()
+            pairs = int((((x + rr).clamp(max=cfg.W - 1) - (x - rr).clamp(min=0) + 1).clamp(min=0) *
+                         ((y + rr).clamp(max=cfg.H - 1) - (y - rr).clamp(min=0) + 1).clamp(min=0)).sum())
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            issue_peak = sms * 4 * 1.965e9  # warp instructions / s: 4 schedulers per SM at the 1965 MHz the clocks record shows
+            r.update({"bound": "instruction issue (not HBM)", "pixel_object_pairs": pairs,
+                      "pairs_per_s": pairs / (ms * 1e-3), "issue_peak_warp_inst_per_s": issue_peak,
+                      "pairs_per_issue_slot": pairs / (ms * 1e-3) / issue_peak,
+                      "note": "one warp instruction handles <= 32 pixels (128 in the 4-pixel-per-lane sweep); "
+                              "profiles/r02 holds the ncu instruction count"})
+        out[name] = r
+        del heats
+    return out
+
+
+def accumulate_leg(ctx, peak):
+    """The drop-in path a reference user calls (max-blend into the caller's tensor, DH_MODE_ACCUMULATE) on the first
+    1536 samples of cfg5: accumulate alone into an already zeroed heatmap, and zero_() + accumulate (what a fresh heatmap
+    costs through the reference-named API). Roofline of this mode: 8 B per TOUCHED pixel (read + write)."""
+    torch, lib, _cabi, dev, w_all = (ctx[k] for k in ("torch", "lib", "_cabi", "dev", "w_all"))
+    nb = min(w_all.B, 1536)
+    w = w_all.slice(0, nb)
+    cfg = w.cfg
+    d = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (w.centers_f, w.bboxes_f, w.sizes, w.labels)]
+    ci, ri = _cabi.radius_center(lib, d[0], d[1], float(cfg.osf))
+    heat = ctx["heats"][0][:nb]
+    wsb, ws = 0, None  # single-launch renderer
+    sp = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def acc():
+        st = lib.dh_draw_heatmap_batched_ws(sp, _cabi.ptr(heat), _cabi.ptr(ci), _cabi.ptr(ri), _cabi.ptr(d[2]),
+                                            _cabi.DH_SIZES_I64, _cabi.ptr(d[3]), nb, w.T, cfg.C, cfg.H, cfg.W, FACTOR, K_SCALE,
+                                            _cabi.DH_MODE_ACCUMULATE, None, _cabi.ptr(ws), wsb)
+        if st != 0:
+            raise RuntimeError(lib.dh_status_string(st).decode())
+
+    def zero_acc():
+        heat.zero_()
+        acc()
+
+    def fresh():
+        _fresh_call(lib, _cabi, sp, heat, d, cfg, nb, w.T, ws, wsb)
+
+    heat.zero_()
+    acc()
+    touched = int(_cabi.checksum(lib, heat)[2])
+    reps = 20
+    ms_acc, ms_zero_acc, ms_fresh = _ev_ms(torch, acc, reps), _ev_ms(torch, zero_acc, reps), _ev_ms(torch, fresh, reps)
+    algo = 8 * touched
+    return {"samples": nb, "planes": nb * cfg.C, "touched_pixels": touched, "accumulate_ms": ms_acc,
+            "zero_plus_accumulate_ms": ms_zero_acc, "fresh_fused_ms": ms_fresh,
+            "roofline": {"bound": "hbm", "algorithmic_bytes": algo, "achieved": algo / (ms_acc * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": algo / (ms_acc * 1e-3) / 1e9 / peak,
+                         "note": "8 B per touched pixel; the launch is bound by per-unit latency, not by bytes"},
+            "heatmaps_per_s_zero_plus_accumulate": nb * cfg.C / (ms_zero_acc * 1e-3)}
+
+
+def reference_gpu_leg(ctx):
+    """The UNMODIFIED reference CUDA extension (oracle/_ref/dh_ref_fast.so: the reference's own sources compiled for
+    sm_100a with its default --use_fast_math, oracle/build_oracle.py) on the same device and inputs — a BASELINE that is
+    measured, like the CPU arm; the product never loads it. Reference cost of a fresh heatmap = zero_() + its draw call
+    (its API max-blends into a caller-zeroed tensor). First 1536 samples of cfg5: the reference indexes pixels with
+    int32 and overflows on the whole."""
+    import importlib.util
+
+    torch, lib, _cabi, dev, w_all = (ctx[k] for k in ("torch", "lib", "_cabi", "dev", "w_all"))
+    path = os.path.join(ROOT, "oracle", "_ref", "dh_ref_fast.so")
+    if not os.path.exists(path):
+        return {"unavailable": "oracle/_ref/dh_ref_fast.so not built (needs /root/reference at build time)"}
+    spec = importlib.util.spec_from_file_location("dh_ref_fast", path)
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    nb = min(w_all.B, 1536)
+    w = w_all.slice(0, nb)
+    cfg = w.cfg
+    d = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (w.centers_f, w.bboxes_f, w.sizes, w.labels)]
+    ci, ri = _cabi.radius_center(lib, d[0], d[1], float(cfg.osf))
+    s32 = d[2].int()
+    heat = ctx["heats"][0][:nb]
+
+    def f_ref():
+        heat.zero_()
+        ref.draw_heatmap_batched_classwise_impl(heat, ci, ri, s32, d[3], FACTOR, K_SCALE)
+
+    ms_ref = _ev_ms(torch, f_ref, 5, warm=2)
+    ref_digest = [int(x) for x in _cabi.checksum(lib, heat).cpu().tolist()]
+    wsb, ws = 0, None  # single-launch renderer
+    sp = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    ms_fresh = _ev_ms(torch, lambda: _fresh_call(lib, _cabi, sp, heat, d, cfg, nb, w.T, ws, wsb), 20)
+    our_digest = [int(x) for x in _cabi.checksum(lib, heat).cpu().tolist()]
+    return {"samples": nb, "planes": nb * cfg.C, "reference_zero_plus_draw_ms": ms_ref,
+            "reference_heatmaps_per_s": nb * cfg.C / (ms_ref * 1e-3), "ours_fresh_fused_ms": ms_fresh,
+            "ours_heatmaps_per_s": nb * cfg.C / (ms_fresh * 1e-3), "speedup_fresh": ms_ref / ms_fresh,
+            "touched_mask_identical": ref_digest[1:] == our_digest[1:],
+            "kind": "unmodified reference extension, --use_fast_math (its default), sm_100a"}
+
 
 
 def e2e_leg(ctx, steps, warm):
@@ -490,6 +652,15 @@ def main():
             cpu = cpu_reference_leg(ctx["w_all"], args.cpu_seconds, threads)
             one = cpu_reference_leg(ctx["w_all"], min(args.cpu_seconds, 4.0), 1, max_samples=48)
             cpu["single_thread_value"] = one["value"]
+    side = {}
+    if rank == 0 and world == 1 and not args.no_side_legs and args.workload == "cfg5" and args.batch is None:
+        peak = ctx["roofline"]["peak"]
+        for key, fn in (("configs", lambda: side_configs_leg(ctx, peak)), ("accumulate", lambda: accumulate_leg(ctx, peak)),
+                        ("reference_gpu", lambda: reference_gpu_leg(ctx))):
+            try:
+                side[key] = fn()
+            except Exception as e:  # side records never take the headline down
+                side[key] = {"error": repr(e)}
     if ctx["dist"] is not None:
         ctx["dist"].barrier()
     if rank == 0:
@@ -503,6 +674,7 @@ def main():
             "digest": ctx["digest"], "hbm_write_GBps_aggregate": ctx["w_all"].out_bytes / (ctx["ms_step"] * 1e-3) / 1e9,
             "build": ctx["lib"].dh_build_info().decode(),
         }
+        line.update(side)
         print(json.dumps(line), flush=True)
     if ctx["dist"] is not None:
         ctx["dist"].destroy_process_group()

@@ -20,9 +20,13 @@ NU = 1 << 20
 trace = torch.zeros(NU * 4, dtype=torch.int64, device=dev)
 sp = _cabi.stream_ptr()
 
+WSB = int(lib.dh_batched_workspace_bytes(w.B, w.T, cfg.C))
+WS = torch.empty(max(WSB, 16), dtype=torch.uint8, device=dev)
+
 def run(i):
-    st = lib.dh_draw_heatmap_batched_from_boxes(sp, _cabi.ptr(heat[i % 2]), _cabi.ptr(d[0]), _cabi.ptr(d[1]), float(cfg.osf),
-        _cabi.ptr(d[2]), _cabi.DH_SIZES_I64, _cabi.ptr(d[3]), w.B, w.T, cfg.C, cfg.H, cfg.W, 6.0, 1.0, MODE, None, None, None)
+    st = lib.dh_draw_heatmap_batched_from_boxes_ws(sp, _cabi.ptr(heat[i % 2]), _cabi.ptr(d[0]), _cabi.ptr(d[1]), float(cfg.osf),
+        _cabi.ptr(d[2]), _cabi.DH_SIZES_I64, _cabi.ptr(d[3]), w.B, w.T, cfg.C, cfg.H, cfg.W, 6.0, 1.0, MODE, None, None, None,
+        _cabi.ptr(WS), WSB)  # DH_G_NOBIN=1 in the environment selects the single-launch renderer
     assert st == 0
 
 for h in heat: h.zero_()

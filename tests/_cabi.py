@@ -111,10 +111,11 @@ def stream_ptr():
 
 
 # ---- convenience wrappers over torch CUDA tensors (still only raw pointers cross the ABI) -------------
-# `ws`: True  = the *_ws entry with a bin-list workspace (K2 pre-pass + warp-autonomous renderer: the product's main path,
-#               what the torch binding, bench.py and the host entry use);
-#       False = the workspace-less entry (single-launch renderer);  None = USE_WS (env DH_TEST_WS, default 1).
-USE_WS = os.environ.get("DH_TEST_WS", "1") != "0"
+# `ws`: False = the workspace-less entry (single-launch renderer: the product's main path — what the torch binding, bench.py
+#               and the host entry call);
+#       True  = the *_ws entry with a bin-list workspace (K2 pre-pass + groups2 renderer, two launches);
+#       None  = USE_WS (env DH_TEST_WS, default 0). tests/test_two_render_paths.py covers both explicitly.
+USE_WS = os.environ.get("DH_TEST_WS", "0") != "0"
 
 
 def _workspace(lib, B, T, C, device, ws):

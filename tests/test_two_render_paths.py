@@ -1,9 +1,11 @@
-"""GPU: the workspace-less entries (single-launch renderer, groups_kernel) keep their own parity coverage.
+"""GPU: both render paths of the batched entries, on every BASELINE config, against the oracle and against each other.
 
-Since round 2 the product's main path is the K2 pre-pass + warp-autonomous renderer (the *_ws entries of
-include/dh_b200.h; tests/_cabi.py passes a workspace by default, and so do the torch binding, bench.py and the host
-entry). The entries without a workspace remain part of the ABI — and are what a *_ws call falls back to — so every
-BASELINE config is also rendered through them and compared with the oracle and with the two-launch path, bit for bit.
+  ws=False  the workspace-less entries: ONE launch (groups_kernel: in-kernel slot scan, K1 fused) — the product's main
+            path (torch binding, bench.py, host entry);
+  ws=True   the *_ws entries of include/dh_b200.h with a caller workspace: TWO launches (bin_kernel = K2 as a pre-pass
+            that counting-sorts every sample's objects by class into compact per-plane lists, then groups2_kernel, whose
+            unit header is one 8-byte load). Bit-identical by contract; round 2 measured it slower on the BASELINE
+            configs (profiles/r02/experiments.md), so nothing in the product selects it by default.
 """
 import numpy as np
 import pytest
