@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups2_kernel(const Ren
             // K4a: the untouched runs, by warp 7 (it gets the fewest striped groups in a short unit)
             if (warp == kGWarps - 1) zero_runs(~mask & valid, lane, plane_b, uy0, uy1, W, G, ES, zero_tile);
         }
-        unsigned long long gm = mask & (0x0101010101010101ull << warp);
+        unsigned long long gm = mask & (kGStripe << warp);
         if (gm != 0ull && !stage_clean) {  // first touched group of this warp: establish the all-zero staging invariant
             uint4* const b4 = reinterpret_cast<uint4*>(ws.buf0);
             for (int i = lane; i < (2 * stage) / 16; i += 32) b4[i] = make_uint4(0u, 0u, 0u, 0u);

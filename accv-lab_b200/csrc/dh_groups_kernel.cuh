@@ -31,19 +31,28 @@
 
 namespace dh {
 
+#ifndef DH_G_THREADS
+#define DH_G_THREADS 256  // 256 (8 warps, 3 CTAs per SM) or 128 (4 warps, 6 CTAs per SM: A/B builds)
+#endif
 #ifndef DH_G_MINB
-#define DH_G_MINB 3  // resident CTAs per SM the register budget is cut for
+#define DH_G_MINB (768 / DH_G_THREADS)  // resident CTAs per SM the register budget is cut for (24 warps per SM)
 #endif
 #ifndef DH_G_STAGE_CAP
 #define DH_G_STAGE_CAP 4096
 #endif
-constexpr int kGThreads = 256;
+constexpr int kGThreads = DH_G_THREADS;
 constexpr int kGWarps = kGThreads / 32;
+static_assert(kGWarps == 8 || kGWarps == 4, "groups kernels: 8 or 4 warps per CTA");
+constexpr unsigned long long kGStripe = kGWarps == 8 ? 0x0101010101010101ull : 0x1111111111111111ull;  // groups of warp 0
 constexpr int kGStageCap = DH_G_STAGE_CAP;  // bytes of one staging buffer (one row group)
 constexpr int kGMaxW = kGStageCap / 4;      // widest map served by this kernel
-constexpr int kGZeroBytes = 8192;           // constant zero tile
-constexpr int kGCap = 512;                  // unit list capacity
+constexpr int kGZeroBytes = kGWarps == 8 ? 8192 : 4096;  // constant zero tile
+constexpr int kGCap = kGWarps == 8 ? 512 : 256;           // unit list capacity
 constexpr int kGMaxGroups = 64;             // groups per unit (bits of the occupancy mask)
+constexpr int kGPermCap = 2048;             // samples whose hand-out order is rearranged (heaviest first)
+constexpr int kGPermBins = 256;             // counting-sort bins of that rearrangement
+constexpr int kGPermSmem = kGPermCap * 2;   // static shared memory it takes (bytes)
+constexpr int kGPermScratch = kGWarps * kGPermBins * 2 + 64;  // bytes of the staging area build_perm borrows
 
 // dynamic shared memory: zero tile | 8 warps x 2 staging buffers of `stage` bytes | unit list
 __host__ __device__ constexpr size_t groups_smem_bytes(int stage) {
@@ -415,9 +424,104 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
 }
 
 // Unit -> plane, rows, source range. Returns the number of slots to scan (`nscan`, independent of any load).
+// Heaviest-first hand-out. Units are handed out in index order by the block scheduler, and a unit with many objects
+// takes 3-5 x an empty one, so a launch used to end with a long tail of half-idle SMs while the last heavy units
+// finished (unit timelines, profiles/r02/call4: the last ~8 us of 37 on cfg3, ~11 us of 211 on the 8-GPU slice of cfg5
+// run at half occupancy or less). Every CTA therefore sorts the samples by their object count, descending (counting
+// sort over kGPermBins bins in shared memory: `sizes` is all it reads, about a microsecond), and unit index -> sample
+// goes through that permutation: the samples with the most objects are rendered first, the launch ends on the cheap ones. Only the last
+// kGPermCap samples of the hand-out order are rearranged (what comes before them cannot be in the tail).
+// The permutation must be THE SAME in every CTA (each one maps unit indices through its own copy), so the counting sort
+// is a stable, atomics-free one: the samples are cut into one contiguous block per warp; every warp histograms its block
+// (chunks of 32, __match_any_sync groups equal keys, the lowest lane of a group adds its size), the per-(warp, bin)
+// counts are turned into start offsets (bins in order, warps in order inside a bin), and every warp scatters its block
+// in the same chunk order. Scratch (keys, 8 x 256 counters) lives in the staging area, which nothing uses yet.
+__device__ __forceinline__ void build_perm(const RenderParams& p, unsigned char* __restrict__ scratch,
+                                           unsigned short* __restrict__ s_perm, int tid, int lane, int warp) {
+    constexpr int PERW = kGPermCap / kGWarps / 32;  // chunks of 32 samples per warp, at most
+    const int M = p.perm_n;
+    unsigned short* const H = reinterpret_cast<unsigned short*>(scratch);  // [kGWarps][kGPermBins]
+    int* const wsum = reinterpret_cast<int*>(scratch + kGWarps * kGPermBins * 2);  // [kGWarps] block-scan scratch
+    const int blk = ((M + kGWarps - 1) / kGWarps + 31) & ~31;                 // samples per warp (multiple of 32)
+    const int i0 = warp * blk;
+    // keys of my (<= PERW) samples: every load issued before anything depends on one
+    int key[PERW];
+#pragma unroll
+    for (int c = 0; c < PERW; ++c) {
+        const int i = i0 + c * 32 + lane;
+        key[c] = -1;
+        if (c * 32 < blk && i < M) {
+            const long long s = p.perm_base + i;
+            long long ns = p.sizes_i64 ? __ldg(reinterpret_cast<const long long*>(p.sizes) + s)
+                                       : (long long)__ldg(reinterpret_cast<const int*>(p.sizes) + s);
+            ns = ns < 0 ? 0 : (ns > p.T ? p.T : ns);
+            key[c] = (kGPermBins - 1) - (int)(ns * (kGPermBins - 1) / p.T);  // most objects -> bin 0
+        }
+    }
+    for (int i = tid; i < kGWarps * kGPermBins / 2; i += kGThreads) reinterpret_cast<unsigned*>(H)[i] = 0u;
+    __syncthreads();
+    unsigned short* const myH = H + warp * kGPermBins;
+#pragma unroll
+    for (int c = 0; c < PERW; ++c) {
+        const unsigned act = __ballot_sync(0xffffffffu, key[c] >= 0);
+        if (key[c] >= 0) {
+            const unsigned peers = __match_any_sync(act, key[c]);
+            if (lane == __ffs(peers) - 1) myH[key[c]] = (unsigned short)(myH[key[c]] + __popc(peers));
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    {  // counts -> start offsets: thread b owns bin b (kGPermBins <= 2 * kGThreads: two bins per thread when 4 warps)
+        constexpr int BPT = (kGPermBins + kGThreads - 1) / kGThreads;
+        int tot[BPT], sum = 0;
+#pragma unroll
+        for (int j = 0; j < BPT; ++j) {
+            const int b = tid * BPT + j;
+            tot[j] = 0;
+            if (b < kGPermBins)
+                for (int w = 0; w < kGWarps; ++w) tot[j] += H[w * kGPermBins + b];
+            sum += tot[j];
+        }
+        int incl = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        int run = incl - sum;
+        for (int w = 0; w < warp; ++w) run += wsum[w];
+#pragma unroll
+        for (int j = 0; j < BPT; ++j) {
+            const int b = tid * BPT + j;
+            if (b < kGPermBins)
+                for (int w = 0; w < kGWarps; ++w) {
+                    const int c = H[w * kGPermBins + b];
+                    H[w * kGPermBins + b] = (unsigned short)run;
+                    run += c;
+                }
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < PERW; ++c) {
+        const unsigned act = __ballot_sync(0xffffffffu, key[c] >= 0);
+        if (key[c] >= 0) {
+            const unsigned peers = __match_any_sync(act, key[c]);
+            const int base = myH[key[c]];
+            s_perm[base + __popc(peers & ((1u << lane) - 1u))] = (unsigned short)(i0 + c * 32 + lane);
+            __syncwarp(peers);
+            if (lane == __ffs(peers) - 1) myH[key[c]] = (unsigned short)(base + __popc(peers));
+        }
+        __syncwarp();
+    }
+    __syncthreads();  // the scratch goes back to being staging memory
+}
+
 template <int SRC>
 __device__ __forceinline__ int unit_header(const RenderParams& p, long long u, int G, UnitSrc& us, int& uy0, int& uy1,
-                                           bool& count_skips) {
+                                           bool& count_skips, const unsigned short* __restrict__ s_perm = nullptr) {
     int ug, bpu;
     if (u < p.tier1_units) {
         us.plane = u / p.units_per_plane;
@@ -433,8 +537,12 @@ __device__ __forceinline__ int unit_header(const RenderParams& p, long long u, i
     uy0 = ug * bpu * G;
     uy1 = min(uy0 + bpu * G, p.H);
     if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_WEIGHTED) {
-        const long long sample = us.plane / p.C;
+        long long sample = us.plane / p.C;  // so far `plane` is the position in the hand-out order
         us.cls = (int)(us.plane - sample * p.C);
+        if (p.perm_n > 0 && sample >= p.perm_base) {
+            sample = p.perm_base + s_perm[sample - p.perm_base];
+            us.plane = sample * p.C + us.cls;
+        }
         long long ns = p.sizes_i64 ? __ldg(reinterpret_cast<const long long*>(p.sizes) + sample)
                                    : (long long)__ldg(reinterpret_cast<const int*>(p.sizes) + sample);
         ns = ns < 0 ? 0 : (ns > p.T ? p.T : ns);
@@ -591,10 +699,13 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
     float4* const zero_tile = reinterpret_cast<float4*>(smem_raw);
     const int stage = p.stage_bytes;  // G*W*4 rounded up to 128
     ObjI* const s_unit = reinterpret_cast<ObjI*>(smem_raw + kGZeroBytes + kGWarps * 2 * stage);
-    __shared__ int s_cnt;
-    __shared__ unsigned long long s_mask;
+    // list size / occupancy mask of the unit, double-buffered by unit parity: thread 0 clears the other slot while
+    // this unit is rendered, so no barrier is needed between "cleared" and "scan" (round 1 had one: three per unit)
+    __shared__ int s_cnt2[2];
+    __shared__ unsigned long long s_mask2[2];
     __shared__ __align__(16) uint4 s_clc;              // cluster-launch-control response
     __shared__ __align__(8) unsigned long long s_bar;  // its mbarrier
+    __shared__ unsigned short s_perm[kGPermCap];       // heaviest-first hand-out order (see build_perm)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool kneg0 = p.k < 0.0f;
@@ -604,7 +715,11 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
        // the first unit (the bulk of its bytes) can then leave as soon as its list is built. Every warp clears its own
        // two staging buffers later, right before it renders its first touched group (off the path to the first store).
         for (int i = tid; i < kGZeroBytes / 16; i += kGThreads) zero_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (tid == 0) mbar_init(&s_bar, 1);
+        if (tid == 0) {
+            mbar_init(&s_bar, 1);
+            s_cnt2[0] = s_cnt2[1] = 0;
+            s_mask2[0] = s_mask2[1] = 0ull;
+        }
         fence_proxy_async();  // zero tile and mbarrier -> visible to the async proxy
     }
     WarpStage ws;
@@ -619,13 +734,19 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
     // The kernel that FOLLOWS may start its own prologue as soon as every CTA of this grid is past this point.
     pdl_wait();
     pdl_launch_dependents();
+    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_WEIGHTED) {
+        if (p.perm_n > 0) build_perm(p, smem_raw + kGZeroBytes, s_perm, tid, lane, warp);
+    }
 
     long long u = blockIdx.x;
-    for (;;) {
+    unsigned par = 0;  // parity of the unit in this CTA's sequence
+    for (;; par ^= 1u) {
+        int& s_cnt = s_cnt2[par];
+        unsigned long long& s_mask = s_mask2[par];
         UnitSrc us;
         int uy0, uy1;
         bool count_skips;
-        const int nscan = unit_header<SRC>(p, u, G, us, uy0, uy1, count_skips);
+        const int nscan = unit_header<SRC>(p, u, G, us, uy0, uy1, count_skips, s_perm);
         char* const plane_b = reinterpret_cast<char*>(p.heat) + us.plane * plane_elems * ES;
         const int ngroups = (uy1 - uy0 + G - 1) / G;
         float kk = p.k;
@@ -646,16 +767,11 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
             g_trace[u * 4 + 2] = sm;
         }
 #endif
-        if (tid == 0) {
-            s_cnt = 0;
-            s_mask = 0ull;
-            if (p.use_clc) {  // ask for the next unit now; the answer lands while this one is rendered
-                fence_proxy_async();
-                mbar_expect_tx(&s_bar, 16);
-                clc_try_cancel(&s_clc, &s_bar);
-            }
+        if (tid == 0 && p.use_clc) {  // ask for the next unit now; the answer lands while this one is rendered
+            fence_proxy_async();
+            mbar_expect_tx(&s_bar, 16);
+            clc_try_cancel(&s_clc, &s_bar);
         }
-        __syncthreads();
         // K1/K2: unit list (ballot + popc-prefix compaction) and group-occupancy mask
         for (int base = 0; base < nscan; base += kGThreads) {
             ObjI o;
@@ -677,6 +793,10 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         __syncthreads();
         const int ucnt = s_cnt;
         const unsigned long long mask = s_mask;
+        if (tid == 0) {  // the other slot was last read before this unit's first barrier: clear it for the next unit
+            s_cnt2[par ^ 1u] = 0;
+            s_mask2[par ^ 1u] = 0ull;
+        }
         const bool small = ucnt <= 32;  // one list entry per lane, kept in registers for the whole unit
         ObjI mine;
         mine.x = mine.y = 0;
@@ -716,7 +836,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         }
         // K3/K4b: touched groups, striped over the warps; no block barrier in here
         const long long plane_index0 = p.digest_base + us.plane * plane_elems;
-        unsigned long long gm = mask & (0x0101010101010101ull << warp);
+        unsigned long long gm = mask & (kGStripe << warp);
         if (gm != 0ull && !stage_clean) {  // first touched group of this warp: establish the all-zero invariant
             uint4* const b4 = reinterpret_cast<uint4*>(ws.buf0);
             for (int i = lane; i < (2 * stage) / 16; i += 32) b4[i] = make_uint4(0u, 0u, 0u, 0u);

@@ -79,6 +79,10 @@ struct RenderParams {
     const float* weights;    // [B,T]
     const float* k_classes;  // [C]
     // SRC_BINNED (groups2_kernel): output of bin_kernel in the caller's workspace
+    // groups_kernel, heaviest-first hand-out: the last perm_n samples (from perm_base on) are rendered in descending order
+    // of their object count (0 = hand-out in index order)
+    int perm_n;
+    long long perm_base;
     const void* bin_list;  // int4 (x, y, r, bits(1/var)) per object, a plane's objects contiguous
     const void* bin_rec;   // int2 (first entry, count) per plane
 };
@@ -665,6 +669,7 @@ static const int g_no_clc = env_int("DH_G_NOCLC", 0);
 static const int g_single_wave = env_int("DH_G_SINGLE_WAVE", 1);
 static const int g_heavy_per_slot = env_int("DH_G_HEAVY_PER_SLOT", 8);
 static const int g_no_bin = env_int("DH_G_NOBIN", 0);  // 1: ignore the workspace, always the single-launch renderer
+static const int g_lpt = env_int("DH_G_LPT", 10);  // heaviest-first hand-out inside the last g_lpt / 2 waves (0 = off)
 static const int g_pdl = env_int("DH_G_PDL", 1);  // programmatic dependent launch of groups_kernel
 static const int g_tail_div = env_int("DH_G_TAIL_DIV", 2);            // tail-tier units are 1/this of a full unit (1 = off)
 static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail tier = this/2 waves of full-size units
@@ -677,7 +682,7 @@ static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail ti
 // Returns false when 16-bit planes cannot be cut into 16-byte aligned groups.
 static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4) {
     // rows per group: as many as a staging buffer holds while DH_G_MINB CTAs still fit the SM's shared memory
-    const long long smem_budget = (227ll * 1024) / DH_G_MINB - 1024;
+    const long long smem_budget = (227ll * 1024) / DH_G_MINB - 1024 - kGPermSmem;  // 1 KB per CTA is the system's
     const long long stage_budget = (smem_budget - (long long)groups_smem_bytes(0)) / (2 * kGWarps);
     int G = (int)((stage_budget < kGStageCap ? stage_budget : kGStageCap) / (p.W * 4));
     if (G < 1) G = 1;
@@ -784,6 +789,24 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     p.use_clc = !g_persistent && !g_no_clc && g <= 0x7fffffffll;  // a clamped grid falls back to the static stride
     if (g_persistent && g > max_ctas) g = max_ctas;
     if (g > 0x7fffffffll) g = 0x7fffffffll;
+    // heaviest-first hand-out (dh_groups_kernel.cuh build_perm): only when the launch has more than one wave — a single
+    // wave has no tail to shorten — and the source has per-sample object counts
+    p.perm_n = 0;
+    p.perm_base = 0;
+    if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_WEIGHTED) {
+        const long long B = p.num_planes / (p.C > 0 ? p.C : 1);
+        if (g_lpt && p.total_units > max_ctas && B >= 2 && p.T >= 1 &&
+            (long long)kGWarps * 2 * p.stage_bytes >= kGPermScratch) {
+            // only the samples handed out in the last g_lpt / 2 waves are rearranged: rearranging all of them was measured
+            // SLOWER on large batches (cfg5 1.576 -> 1.635 ms): it scatters the set of addresses being written over the whole
+            // buffer, and the write rate depends on that set staying compact (profiles/r02/experiments.md)
+            long long win = (g_lpt * max_ctas / 2 + (long long)p.C * p.units_per_plane - 1) / ((long long)p.C * p.units_per_plane);
+            if (win > kGPermCap) win = kGPermCap;
+            if (win > B) win = B;
+            p.perm_n = (int)win;
+            p.perm_base = B - p.perm_n;
+        }
+    }
     const cudaError_t e = launch_pdl(groups_kernel<ACCUM, SRC, DIGEST, OUT>, dim3((unsigned)g), dim3(kGThreads),
                                      groups_smem_bytes(p.stage_bytes), stream, p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
