@@ -140,7 +140,7 @@ def render_heatmap_flat(centers: torch.Tensor, radii: torch.Tensor, heatmap_idxe
 
 def draw_gaussians(heatmap: Optional[torch.Tensor], active, slice_ids, centers, radii, k_for_classes,
                    radius_to_sigma_factor: float, out: Optional[torch.Tensor] = None,
-                   shape: Optional[Tuple[int, ...]] = None) -> torch.Tensor:
+                   shape: Optional[Tuple[int, ...]] = None, fast: Optional[bool] = None) -> torch.Tensor:
     """GPU version of the reference's DALI operator ``draw_gaussians(heatmap, active, slice_ids, centers, radii,
     k_for_classes=..., radius_to_sigma_factor=...)`` (ext_impl/DrawGaussians.cc:88-157; Python call site
     processing_steps/bounding_box_to_heatmap_converter.py:321-399): returns ``max(heatmap, per-class Gaussians)``.
@@ -149,7 +149,9 @@ def draw_gaussians(heatmap: Optional[torch.Tensor], active, slice_ids, centers, 
     float32 ``[B,T]``, ``slice_ids`` int32 ``[B,T]`` (or ``None``: class 0), ``active`` bool ``[B,T]`` (or ``None``),
     each a ``RaggedBatch`` (``sample_sizes`` taken from ``radii``) or a plain tensor meaning "all T slots valid".
     ``heatmap`` float32 ``[B,C,H,W]`` / ``[B,H,W]``; ``None`` renders a fresh heatmap of ``shape`` (zero-init fused).
-    ``out`` may be ``heatmap`` itself (in place); default: a new tensor, like the operator."""
+    ``out`` may be ``heatmap`` itself (in place); default: a new tensor, like the operator.
+    ``fast`` (fresh rendering only): True / False force / forbid the three-launch path through the main renderer; None
+    takes it from 256 MiB of output on. Results are identical either way."""
     r_t, sizes = _tensor_and_sizes(radii)
     c_t, _ = _tensor_and_sizes(centers)
     a_t = None if active is None else _tensor_and_sizes(active)[0]
@@ -164,7 +166,8 @@ def draw_gaussians(heatmap: Optional[torch.Tensor], active, slice_ids, centers, 
             out = torch.empty(tuple(shape), dtype=torch.float32, device=r_t.device)
         else:
             out = torch.empty_like(heatmap)
-    return _ext.draw_gaussians(heatmap, out, a_t, s_t, c_t, r_t, sizes, k_for_classes, float(radius_to_sigma_factor))
+    return _ext.draw_gaussians(heatmap, out, a_t, s_t, c_t, r_t, sizes, k_for_classes, float(radius_to_sigma_factor),
+                               -1 if fast is None else int(bool(fast)))
 
 
 def boxes_to_gaussian_params(bboxes, scale_xy: torch.Tensor, heatmap_hw: Tuple[int, int], centers=None, classes=None,

@@ -510,7 +510,6 @@ __global__ void __launch_bounds__(1024) focal_reduce_kernel(const double* __rest
 
 namespace dh {
 
-static const bool g_gs_force_fast = getenv("DH_GS_FORCE_FAST") != nullptr;  // tests: take the fast path at any size
 
 int launch_weighted_fresh(cudaStream_t stream, float* heat, const int32_t* centers, const int32_t* radii_eff,
                           const float* weights, const int32_t* labels, const void* sizes, int sizes_i64,
@@ -608,9 +607,9 @@ extern "C" int dh_draw_gaussians(void* stream, const float* heatmap_in, float* h
     cudaStream_t s = (cudaStream_t)stream;
     // FRESH fast path (needs the caller's workspace): classify -> main renderer for the symmetric objects (bulk-store /
     // cluster-launch-control path of groups_kernel) -> exact kernel in place over the few flagged objects, if any.
-    // (three launches: only worth it when the output is large — measured break-even ~200 MB on B200)
-    const bool big = (double)B * (double)C * (double)H * (double)W * 4.0 >= (double)(256ll << 20) || dh::g_gs_force_fast;
-    if (big && heatmap_in == nullptr && vec && T > 0 && workspace != nullptr && status == nullptr &&
+    // Three launches: only worth it when the output is large (measured break-even ~200 MB on B200) — the CALLER decides by
+    // passing the workspace or not; the torch binding passes one from 256 MiB of output on.
+    if (heatmap_in == nullptr && vec && T > 0 && workspace != nullptr && status == nullptr &&
         workspace_bytes >= dh_draw_gaussians_workspace_bytes(B, T) && (reinterpret_cast<uintptr_t>(workspace) & 15u) == 0) {
         const size_t n = (size_t)B * (size_t)T, a4 = (n * 4 + 15) & ~(size_t)15, a1 = (n + 15) & ~(size_t)15;
         char* ws = (char*)workspace;

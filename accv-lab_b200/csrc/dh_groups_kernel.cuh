@@ -37,6 +37,12 @@ namespace dh {
 #ifndef DH_G_MINB
 #define DH_G_MINB (768 / DH_G_THREADS)  // resident CTAs per SM the register budget is cut for (24 warps per SM)
 #endif
+#ifndef DH_G_MINB_ACCUM
+// ACCUMULATE (the reference's in-place semantics) reads before it writes and is bound by memory latency, not by stores
+// (ncu, profiles/r02/ncu_groups_kernel_accum_b1536.txt: `long_scoreboard` is the top stall, DRAM at 14 %). It needs
+// neither the zero tile nor a second staging buffer per warp, so one more CTA fits an SM: 32 resident warps, not 24.
+#define DH_G_MINB_ACCUM (1024 / DH_G_THREADS)
+#endif
 #ifndef DH_G_STAGE_CAP
 #define DH_G_STAGE_CAP 4096
 #endif
@@ -55,8 +61,10 @@ constexpr int kGPermSmem = kGPermCap * 2;   // static shared memory it takes (by
 constexpr int kGPermScratch = kGWarps * kGPermBins * 2 + 64;  // bytes of the staging area build_perm borrows
 
 // dynamic shared memory: zero tile | 8 warps x 2 staging buffers of `stage` bytes | unit list
-__host__ __device__ constexpr size_t groups_smem_bytes(int stage) {
-    return (size_t)kGZeroBytes + (size_t)kGWarps * 2 * (size_t)stage + (size_t)kGCap * sizeof(ObjI);
+// dynamic shared memory: [zero tile] | kGWarps x (2 | 1) staging buffers of `stage` bytes | unit list.
+// ACCUMULATE has no zero tile and one staging buffer per warp (scratch of the dense path; nothing leaves from it).
+__host__ __device__ constexpr size_t groups_smem_bytes(int stage, bool accum = false) {
+    return (size_t)(accum ? 0 : kGZeroBytes) + (size_t)kGWarps * (accum ? 1 : 2) * (size_t)stage + (size_t)kGCap * sizeof(ObjI);
 }
 
 __device__ __forceinline__ unsigned enc_m(float m, bool kneg) {
@@ -693,12 +701,14 @@ __device__ long long g_trace_units = 0;
 #endif
 
 template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32>
-__global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const RenderParams p) {
+__global__ void __launch_bounds__(kGThreads, ACCUM ? DH_G_MINB_ACCUM : DH_G_MINB) groups_kernel(const RenderParams p) {
+    constexpr int ZB = ACCUM ? 0 : kGZeroBytes;  // bytes of the zero tile
+    constexpr int NB = ACCUM ? 1 : 2;            // staging buffers per warp
     constexpr int ES = (OUT == OUT_F32) ? 4 : 2;  // bytes per heatmap element
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float4* const zero_tile = reinterpret_cast<float4*>(smem_raw);
     const int stage = p.stage_bytes;  // G*W*4 rounded up to 128
-    ObjI* const s_unit = reinterpret_cast<ObjI*>(smem_raw + kGZeroBytes + kGWarps * 2 * stage);
+    ObjI* const s_unit = reinterpret_cast<ObjI*>(smem_raw + ZB + kGWarps * NB * stage);
     // list size / occupancy mask of the unit, double-buffered by unit parity: thread 0 clears the other slot while
     // this unit is rendered, so no barrier is needed between "cleared" and "scan" (round 1 had one: three per unit)
     __shared__ int s_cnt2[2];
@@ -714,7 +724,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
     {  // Prologue. Only the 8 KB zero tile is cleared by the whole block before the first unit: the untouched runs of
        // the first unit (the bulk of its bytes) can then leave as soon as its list is built. Every warp clears its own
        // two staging buffers later, right before it renders its first touched group (off the path to the first store).
-        for (int i = tid; i < kGZeroBytes / 16; i += kGThreads) zero_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = tid; i < ZB / 16; i += kGThreads) zero_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (tid == 0) {
             mbar_init(&s_bar, 1);
             s_cnt2[0] = s_cnt2[1] = 0;
@@ -723,8 +733,8 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         fence_proxy_async();  // zero tile and mbarrier -> visible to the async proxy
     }
     WarpStage ws;
-    ws.buf0 = reinterpret_cast<unsigned*>(smem_raw + kGZeroBytes + warp * 2 * stage);
-    ws.buf1 = ws.buf0 + stage / 4;
+    ws.buf0 = reinterpret_cast<unsigned*>(smem_raw + ZB + warp * NB * stage);
+    ws.buf1 = ws.buf0 + (NB - 1) * (stage / 4);  // ACCUMULATE: one buffer (ws.cur never flips there)
     bool stage_clean = false;  // my staging buffers are all-zero (established before my first render_group)
     unsigned clc_phase = 0;
     Digest dg;
@@ -735,7 +745,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
     pdl_wait();
     pdl_launch_dependents();
     if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_WEIGHTED) {
-        if (p.perm_n > 0) build_perm(p, smem_raw + kGZeroBytes, s_perm, tid, lane, warp);
+        if (p.perm_n > 0) build_perm(p, smem_raw + ZB, s_perm, tid, lane, warp);
     }
 
     long long u = blockIdx.x;
@@ -839,7 +849,7 @@ __global__ void __launch_bounds__(kGThreads, DH_G_MINB) groups_kernel(const Rend
         unsigned long long gm = mask & (kGStripe << warp);
         if (gm != 0ull && !stage_clean) {  // first touched group of this warp: establish the all-zero invariant
             uint4* const b4 = reinterpret_cast<uint4*>(ws.buf0);
-            for (int i = lane; i < (2 * stage) / 16; i += 32) b4[i] = make_uint4(0u, 0u, 0u, 0u);
+            for (int i = lane; i < (NB * stage) / 16; i += 32) b4[i] = make_uint4(0u, 0u, 0u, 0u);
             __syncwarp();
             stage_clean = true;
         }

@@ -81,13 +81,19 @@ __global__ void __launch_bounds__(256) checksum_kernel(const float* __restrict__
 }
 
 // ---- helper streams of the host entry (per device, created once) ------------------------------------
+// growth factor of the input chunks, smallest input size that is pipelined (KiB); environment-tunable in measurement
+// builds only (-DDH_TUNING)
+#ifdef DH_TUNING
 static int host_env_int(const char* name, int dflt) {
     const char* v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
 }
-// measurement hooks (read once): growth factor of the input chunks, smallest input size that is pipelined (KiB)
-static const int g_host_growth = host_env_int("DH_HOST_GROWTH", 4);
-static const int g_host_pipeline_kib = host_env_int("DH_HOST_PIPELINE_KIB", 1536);
+#define DH_HOST_KNOB(name, dflt) host_env_int(name, dflt)
+#else
+#define DH_HOST_KNOB(name, dflt) (dflt)
+#endif
+static const int g_host_growth = DH_HOST_KNOB("DH_HOST_GROWTH", 4);
+static const int g_host_pipeline_kib = DH_HOST_KNOB("DH_HOST_PIPELINE_KIB", 1536);
 constexpr int kHostMaxChunks = 16;  // input chunks of the pipelined device-output path
 struct HostCtx {
     bool ready = false;
@@ -96,14 +102,20 @@ struct HostCtx {
     cudaEvent_t fork = nullptr, join[2] = {nullptr, nullptr};
     cudaEvent_t arrived[kHostMaxChunks] = {};
 };
+// One context (helper streams + events) and one lock PER DEVICE: calls on different GPUs of one process never serialise
+// on each other; two calls on the same GPU share its helper streams and are serialised while they enqueue.
 static HostCtx g_ctx[64];
-static std::mutex g_ctx_mu;
+static std::mutex g_ctx_mu[64];
 
-static int host_ctx(HostCtx*& out) {
-    int dev = 0;
+static int host_device(int& dev) {
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return (int)e;
-    if (dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
+    return (dev < 0 || dev >= 64) ? DH_ERR_NO_DEVICE : DH_OK;
+}
+
+// caller holds g_ctx_mu[dev]
+static int host_ctx(int dev, HostCtx*& out) {
+    cudaError_t e;
     HostCtx& c = g_ctx[dev];
     if (!c.ready) {
         for (int i = 0; i < 2; ++i) {
@@ -145,7 +157,7 @@ __global__ void __launch_bounds__(256) gather_host_kernel(const GatherArgs a) {
         }
     }
 }
-static const int g_host_gather = host_env_int("DH_HOST_GATHER", 1);
+static const int g_host_gather = DH_HOST_KNOB("DH_HOST_GATHER", 1);
 // device-visible alias of a pinned host pointer, or nullptr when the memory is pageable / unknown to the driver
 static const void* pinned_alias(const void* h) {
     if (!h) return nullptr;
@@ -302,9 +314,11 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
             }
             if (bounds[1] < 1) bounds[1] = 1;  // B >= 2: the first chunk is never empty
         }
-        std::lock_guard<std::mutex> lock(dh::g_ctx_mu);
+        int dev = 0;
+        if ((st = dh::host_device(dev)) != DH_OK) return st;
+        std::lock_guard<std::mutex> lock(dh::g_ctx_mu[dev]);
         dh::HostCtx* ctx = nullptr;
-        st = dh::host_ctx(ctx);
+        st = dh::host_ctx(dev, ctx);
         if (st != DH_OK) return st;
         DH_TRY(cudaMemcpyAsync(d_sizes, nums_targets_host, (size_t)B * 8, cudaMemcpyHostToDevice, stream));
         if (checksum_host) DH_TRY(cudaMemsetAsync(d_ck, 0, 24, stream));
@@ -312,26 +326,30 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
         DH_TRY(cudaStreamWaitEvent(ctx->copy, ctx->fork, 0));
         DH_TRY(cudaStreamWaitEvent(ctx->s[0], ctx->fork, 0));
         DH_TRY(cudaStreamWaitEvent(ctx->s[1], ctx->fork, 0));
-        for (int64_t c = 0; c < nch; ++c) {
+        // From here on work may be queued on the helper streams: an error must not return before they are joined to
+        // the caller's stream again (a later synchronisation of `stream` has to cover everything this call enqueued).
+        st = DH_OK;
+#define DH_TRY_J(x) do { if (st == DH_OK && (e = (x)) != cudaSuccess) st = (int)e; } while (0)
+        for (int64_t c = 0; c < nch && st == DH_OK; ++c) {
             const int64_t s0 = bounds[c], s1 = bounds[c + 1] > s0 ? bounds[c + 1] : s0, nb = s1 - s0;
             if (nb <= 0) continue;
-            DH_TRY(cudaMemcpyAsync(d_centers + s0 * T * 2, centers_xy_host + s0 * T * 2, (size_t)nb * T * 8,
-                                   cudaMemcpyHostToDevice, ctx->copy));
-            DH_TRY(cudaMemcpyAsync(d_bboxes + s0 * T * 4, bboxes_xyxy_host + s0 * T * 4, (size_t)nb * T * 16,
-                                   cudaMemcpyHostToDevice, ctx->copy));
+            DH_TRY_J(cudaMemcpyAsync(d_centers + s0 * T * 2, centers_xy_host + s0 * T * 2, (size_t)nb * T * 8,
+                                     cudaMemcpyHostToDevice, ctx->copy));
+            DH_TRY_J(cudaMemcpyAsync(d_bboxes + s0 * T * 4, bboxes_xyxy_host + s0 * T * 4, (size_t)nb * T * 16,
+                                     cudaMemcpyHostToDevice, ctx->copy));
             if (has_labels)
-                DH_TRY(cudaMemcpyAsync(d_labels + s0 * T, labels_host + s0 * T, (size_t)nb * T * 4,
-                                       cudaMemcpyHostToDevice, ctx->copy));
-            DH_TRY(cudaEventRecord(ctx->arrived[c], ctx->copy));
+                DH_TRY_J(cudaMemcpyAsync(d_labels + s0 * T, labels_host + s0 * T, (size_t)nb * T * 4,
+                                         cudaMemcpyHostToDevice, ctx->copy));
+            DH_TRY_J(cudaEventRecord(ctx->arrived[c], ctx->copy));
             cudaStream_t rs = ctx->s[c & 1];
-            DH_TRY(cudaStreamWaitEvent(rs, ctx->arrived[c], 0));
-            st = render_range(rs, heatmap_device + s0 * sample_elems, s0, nb);
-            if (st != DH_OK) return st;
+            DH_TRY_J(cudaStreamWaitEvent(rs, ctx->arrived[c], 0));
+            if (st == DH_OK) st = render_range(rs, heatmap_device + s0 * sample_elems, s0, nb);
         }
-        for (int j = 0; j < 2; ++j) {
-            DH_TRY(cudaEventRecord(ctx->join[j], ctx->s[j]));
-            DH_TRY(cudaStreamWaitEvent(stream, ctx->join[j], 0));
+        for (int j = 0; j < 2; ++j) {  // always: join what was queued
+            if (cudaEventRecord(ctx->join[j], ctx->s[j]) == cudaSuccess) cudaStreamWaitEvent(stream, ctx->join[j], 0);
         }
+        if (cudaEventRecord(ctx->join[0], ctx->copy) == cudaSuccess) cudaStreamWaitEvent(stream, ctx->join[0], 0);
+        if (st != DH_OK) return st;
         if (checksum_host) DH_TRY(cudaMemcpyAsync(checksum_host, d_ck, 24, cudaMemcpyDeviceToHost, stream));
         return DH_OK;
     }
@@ -381,27 +399,30 @@ int dh_draw_heatmap_batched_from_boxes_host(void* stream_, float* heatmap_host, 
     }
 
     // ---- chunked render + copy back, double-buffered over two helper streams ----
-    std::lock_guard<std::mutex> lock(dh::g_ctx_mu);
+    int dev = 0;
+    if ((st = dh::host_device(dev)) != DH_OK) return st;
+    std::lock_guard<std::mutex> lock(dh::g_ctx_mu[dev]);
     dh::HostCtx* ctx = nullptr;
-    st = dh::host_ctx(ctx);
+    st = dh::host_ctx(dev, ctx);
     if (st != DH_OK) return st;
     DH_TRY(cudaEventRecord(ctx->fork, stream));
     DH_TRY(cudaStreamWaitEvent(ctx->s[0], ctx->fork, 0));
     DH_TRY(cudaStreamWaitEvent(ctx->s[1], ctx->fork, 0));
     int64_t i = 0;
-    for (int64_t s0 = 0; s0 < B; s0 += L.chunk, ++i) {
+    st = DH_OK;
+    for (int64_t s0 = 0; s0 < B && st == DH_OK; s0 += L.chunk, ++i) {
         const int64_t nb = (B - s0 < L.chunk) ? (B - s0) : L.chunk;
         cudaStream_t cs = ctx->s[i & 1];
         float* dst = staging ? (float*)(ws + L.off_stage[i & 1]) : heatmap_device + s0 * sample_elems;
         st = render_range(cs, dst, s0, nb);
-        if (st != DH_OK) return st;
-        DH_TRY(cudaMemcpyAsync(heatmap_host + s0 * sample_elems, dst, (size_t)nb * sample_elems * 4,
-                               cudaMemcpyDeviceToHost, cs));
+        DH_TRY_J(cudaMemcpyAsync(heatmap_host + s0 * sample_elems, dst, (size_t)nb * sample_elems * 4,
+                                 cudaMemcpyDeviceToHost, cs));
     }
-    for (int j = 0; j < 2; ++j) {
-        DH_TRY(cudaEventRecord(ctx->join[j], ctx->s[j]));
-        DH_TRY(cudaStreamWaitEvent(stream, ctx->join[j], 0));
+    for (int j = 0; j < 2; ++j) {  // always: join what was queued, also after an error
+        if (cudaEventRecord(ctx->join[j], ctx->s[j]) == cudaSuccess) cudaStreamWaitEvent(stream, ctx->join[j], 0);
     }
+    if (st != DH_OK) return st;
+#undef DH_TRY_J
     if (checksum_host) DH_TRY(cudaMemcpyAsync(checksum_host, d_ck, 24, cudaMemcpyDeviceToHost, stream));
 #undef DH_TRY
     return DH_OK;

@@ -14,7 +14,8 @@
 //   K3  max-blend       : pixel-owner threads keep max_o(-(i^2+j^2)*vinv_o) in registers (no atomics on
 //                         the heatmap, shared or global) and evaluate ONE expf per touched pixel:
 //                         max_o k*exp(a_o) == k*exp(max_o a_o) bit-for-bit because expf is monotone
-//                         (verified exhaustively on the GPU by tests/test_gpu_expf_monotone.py).
+//                         (verified exhaustively on the GPU by
+//                         tests/test_gpu_properties.py::test_expf_is_monotone_and_close_to_correctly_rounded).
 //   K4  write           : every pixel is stored exactly once with 128-bit coalesced stores; zero-init is
 //                         fused (FRESH mode writes zeros where nothing was drawn and never reads).
 // No tensor cores: this is HBM-write-bound byte work, not a contraction.
@@ -544,25 +545,29 @@ static int device_info(DeviceInfo& di) {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return (int)e;
-    static int cached_sms[64] = {0};
+    // per-device caches are std::atomic: several host threads may make their first call at once; a duplicated query is
+    // harmless (same value), a torn or unsynchronised write would not be
+    static std::atomic<int> cached_sms[64];
     if (dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
-    if (cached_sms[dev] == 0) {
-        int sms = 0;
+    int sms = cached_sms[dev].load(std::memory_order_relaxed);
+    if (sms == 0) {
         e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (e != cudaSuccess) return (int)e;
-        cached_sms[dev] = sms;
+        cached_sms[dev].store(sms, std::memory_order_relaxed);
     }
-    di.sms = cached_sms[dev];
+    di.sms = sms;
     return DH_OK;
 }
 
 template <typename K>
-static int blocks_per_sm(K kernel, int& cached) {
-    if (cached == 0) {
+static int blocks_per_sm(K kernel, std::atomic<int>& cached, int& out) {
+    out = cached.load(std::memory_order_relaxed);
+    if (out == 0) {
         int nb = 0;
         cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kThreads, 0);
         if (e != cudaSuccess) return (int)e;
-        cached = nb > 0 ? nb : 1;
+        out = nb > 0 ? nb : 1;
+        cached.store(out, std::memory_order_relaxed);
     }
     return DH_OK;
 }
@@ -635,10 +640,10 @@ static void make_rows_plan(RenderParams& p, long long max_ctas) {
 
 template <bool ACCUM, int SRC>
 static int launch_rows(cudaStream_t stream, RenderParams& p, int sms) {
-    static int occ_dev[64] = {0};  // per instantiation and device (function attributes are per device); also "attribute set"
+    static std::atomic<int> occ_dev[64];  // per instantiation and device (function attributes are per device); also "attribute set"
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
-    int& occ = occ_dev[dev];
+    int occ = occ_dev[dev].load(std::memory_order_relaxed);
     if (occ == 0) {
         cudaError_t e = cudaFuncSetAttribute(rows_kernel<ACCUM, SRC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)kRowsSmemBytes);
@@ -647,6 +652,7 @@ static int launch_rows(cudaStream_t stream, RenderParams& p, int sms) {
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, rows_kernel<ACCUM, SRC>, kRowsThreads, kRowsSmemBytes);
         if (e != cudaSuccess) return (int)e;
         occ = nb > 0 ? nb : 1;
+        occ_dev[dev].store(occ, std::memory_order_relaxed);
     }
     const long long max_ctas = (long long)sms * occ;
     make_rows_plan(p, max_ctas);
@@ -657,22 +663,28 @@ static int launch_rows(cudaStream_t stream, RenderParams& p, int sms) {
     return (int)cudaGetLastError();
 }
 
-// Tuning hooks (environment, read once): DH_G_UNIT_BYTES = target bytes per unit, DH_G_PERSISTENT=1 = static
-// grid-stride launch (kept for A/B measurements of the block-scheduler effect).
+// Tuning constants. Product builds compile them in; measurement builds (-DDH_TUNING, profiles/scripts/build_variants.sh)
+// read the environment once at load time instead, for A/B runs of one binary. The defaults are the measured optima
+// (profiles/r01/experiments.md, profiles/r02/experiments.md).
+#ifdef DH_TUNING
 static int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
 }
-static const int g_unit_bytes = env_int("DH_G_UNIT_BYTES", 196608);
-static const int g_persistent = env_int("DH_G_PERSISTENT", 0);
-static const int g_no_clc = env_int("DH_G_NOCLC", 0);
-static const int g_single_wave = env_int("DH_G_SINGLE_WAVE", 1);
-static const int g_heavy_per_slot = env_int("DH_G_HEAVY_PER_SLOT", 8);
-static const int g_no_bin = env_int("DH_G_NOBIN", 0);  // 1: ignore the workspace, always the single-launch renderer
-static const int g_lpt = env_int("DH_G_LPT", 10);  // heaviest-first hand-out inside the last g_lpt / 2 waves (0 = off)
-static const int g_pdl = env_int("DH_G_PDL", 1);  // programmatic dependent launch of groups_kernel
-static const int g_tail_div = env_int("DH_G_TAIL_DIV", 2);            // tail-tier units are 1/this of a full unit (1 = off)
-static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail tier = this/2 waves of full-size units
+#define DH_KNOB(name, dflt) env_int(name, dflt)
+#else
+#define DH_KNOB(name, dflt) (dflt)
+#endif
+static const int g_unit_bytes = DH_KNOB("DH_G_UNIT_BYTES", 196608);    // target bytes per unit
+static const int g_persistent = DH_KNOB("DH_G_PERSISTENT", 0);         // 1: static grid-stride launch (block-scheduler A/B)
+static const int g_no_clc = DH_KNOB("DH_G_NOCLC", 0);                  // 1: no cluster launch control
+static const int g_single_wave = DH_KNOB("DH_G_SINGLE_WAVE", 1);       // small problems: one wave of larger units
+static const int g_heavy_per_slot = DH_KNOB("DH_G_HEAVY_PER_SLOT", 8); // units per resident CTA slot when T >= 256
+static const int g_no_bin = DH_KNOB("DH_G_NOBIN", 0);                  // 1: ignore the workspace of the *_ws entries
+static const int g_lpt = DH_KNOB("DH_G_LPT", 10);                      // heaviest-first hand-out inside the last g_lpt / 2 waves (0 = off)
+static const int g_pdl = DH_KNOB("DH_G_PDL", 1);                       // programmatic dependent launch of the groups kernels
+static const int g_tail_div = DH_KNOB("DH_G_TAIL_DIV", 2);             // tail-tier units are 1/this of a full unit (1 = off)
+static const int g_tail_waves_x2 = DH_KNOB("DH_G_TAIL_WAVES_X2", 2);   // tail tier = this/2 waves of full-size units
 
 // Plan of the groups kernels: row group = G whole rows (<= kGStageCap bytes), unit = up to 64 groups of one plane,
 // ~192 KB when the problem is large (amortises the per-unit list build; with the tail tier of half-size units the measured
@@ -680,10 +692,10 @@ static const int g_tail_waves_x2 = env_int("DH_G_TAIL_WAVES_X2", 2);  // tail ti
 // is not, so that every resident CTA slot still sees several units.
 // `es` = bytes per heatmap element (4, or 2 for the 16-bit planes: rows per group still follow the fp32 scratch).
 // Returns false when 16-bit planes cannot be cut into 16-byte aligned groups.
-static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4) {
-    // rows per group: as many as a staging buffer holds while DH_G_MINB CTAs still fit the SM's shared memory
-    const long long smem_budget = (227ll * 1024) / DH_G_MINB - 1024 - kGPermSmem;  // 1 KB per CTA is the system's
-    const long long stage_budget = (smem_budget - (long long)groups_smem_bytes(0)) / (2 * kGWarps);
+static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4, bool accum = false) {
+    // rows per group: as many as a staging buffer holds while DH_G_MINB(_ACCUM) CTAs still fit the SM's shared memory
+    const long long smem_budget = (227ll * 1024) / (accum ? DH_G_MINB_ACCUM : DH_G_MINB) - 1024 - kGPermSmem;  // 1 KB: the system's
+    const long long stage_budget = (smem_budget - (long long)groups_smem_bytes(0, accum)) / ((accum ? 1 : 2) * kGWarps);
     int G = (int)((stage_budget < kGStageCap ? stage_budget : kGStageCap) / (p.W * 4));
     if (G < 1) G = 1;
     if (G > p.H) G = p.H;
@@ -767,19 +779,18 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 
 template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32>
 static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
-    static bool attr_set_dev[64] = {false};  // function attributes are per device: one process may drive several GPUs
+    static std::atomic<bool> attr_set_dev[64];  // function attributes are per device: one process may drive several GPUs
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
-    bool& attr_set = attr_set_dev[dev];
-    if (!attr_set) {
-        const int cap = (int)groups_smem_bytes(kGStageCap);  // widest map: fewer CTAs per SM then
+    if (!attr_set_dev[dev].load(std::memory_order_acquire)) {
+        const int cap = (int)groups_smem_bytes(kGStageCap, ACCUM);  // widest map: fewer CTAs per SM then
         cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST, OUT>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+        attr_set_dev[dev].store(true, std::memory_order_release);
     }
-    const long long max_ctas = (long long)sms * DH_G_MINB;
-    if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2)) return DH_ERR_UNSUPPORTED_SHAPE;
+    const long long max_ctas = (long long)sms * (ACCUM ? DH_G_MINB_ACCUM : DH_G_MINB);
+    if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2, ACCUM)) return DH_ERR_UNSUPPORTED_SHAPE;
     if (p.total_units == 0) return DH_OK;
     // Flat grid, one CTA per unit: the block scheduler hands units out dynamically and in address order, which
     // balances SMs that see different effective store bandwidth; a static grid-stride loop runs at the pace of the
@@ -796,7 +807,7 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_WEIGHTED) {
         const long long B = p.num_planes / (p.C > 0 ? p.C : 1);
         if (g_lpt && p.total_units > max_ctas && B >= 2 && p.T >= 1 &&
-            (long long)kGWarps * 2 * p.stage_bytes >= kGPermScratch) {
+            (long long)kGWarps * (ACCUM ? 1 : 2) * p.stage_bytes >= kGPermScratch) {
             // only the samples handed out in the last g_lpt / 2 waves are rearranged: rearranging all of them was measured
             // SLOWER on large batches (cfg5 1.576 -> 1.635 ms): it scatters the set of addresses being written over the whole
             // buffer, and the write rate depends on that set staying compact (profiles/r02/experiments.md)
@@ -808,7 +819,7 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
         }
     }
     const cudaError_t e = launch_pdl(groups_kernel<ACCUM, SRC, DIGEST, OUT>, dim3((unsigned)g), dim3(kGThreads),
-                                     groups_smem_bytes(p.stage_bytes), stream, p);
+                                     groups_smem_bytes(p.stage_bytes, ACCUM), stream, p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
@@ -817,14 +828,14 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
 // dependent on the first (its prologue overlaps bin_kernel; it waits before it reads the lists).
 template <bool ACCUM, bool DIGEST, int OUT = OUT_F32>
 static int launch_groups2(cudaStream_t stream, RenderParams& p, int sms, long long B, void* workspace) {
-    static bool attr_set_dev[64] = {false};
+    static std::atomic<bool> attr_set_dev[64];
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
-    if (!attr_set_dev[dev]) {
+    if (!attr_set_dev[dev].load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(groups2_kernel<ACCUM, DIGEST, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)groups_smem_bytes(kGStageCap));
         if (e != cudaSuccess) return (int)e;
-        attr_set_dev[dev] = true;
+        attr_set_dev[dev].store(true, std::memory_order_release);
     }
     const long long max_ctas = (long long)sms * DH_G_MINB;
     if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2)) return DH_ERR_UNSUPPORTED_SHAPE;
@@ -890,12 +901,14 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode, long lo
         return accum ? launch_rows<true, SRC>(stream, p, di.sms) : launch_rows<false, SRC>(stream, p, di.sms);
     }
     // generic path (W not a multiple of 4, misaligned base, or rows wider than a tile): pixel-owner threads
-    static int occ[2][2] = {{0, 0}, {0, 0}};
-    int& o = occ[vec][accum];
-    if (vec && accum) st = blocks_per_sm(render_kernel<4, true, SRC>, o);
-    else if (vec) st = blocks_per_sm(render_kernel<4, false, SRC>, o);
-    else if (accum) st = blocks_per_sm(render_kernel<1, true, SRC>, o);
-    else st = blocks_per_sm(render_kernel<1, false, SRC>, o);
+    static std::atomic<int> occ[64][2][2];  // per device (occupancy is a per-device property)
+    int dev = 0, o = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
+    std::atomic<int>& oc = occ[dev][vec][accum];
+    if (vec && accum) st = blocks_per_sm(render_kernel<4, true, SRC>, oc, o);
+    else if (vec) st = blocks_per_sm(render_kernel<4, false, SRC>, oc, o);
+    else if (accum) st = blocks_per_sm(render_kernel<1, true, SRC>, oc, o);
+    else st = blocks_per_sm(render_kernel<1, false, SRC>, oc, o);
     if (st != DH_OK) return st;
     const long long max_ctas = (long long)di.sms * o;
     make_plan(p, vec ? 4 : 1, max_ctas);

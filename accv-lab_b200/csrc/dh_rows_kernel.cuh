@@ -1,4 +1,6 @@
-// dh_rows_kernel.cuh — the main renderer: row-owner warps + shared-memory tiles + bulk (TMA) stores.
+// dh_rows_kernel.cuh — renderer for WIDE maps (1024 < W <= 4096; everything narrower goes to dh_groups_kernel.cuh):
+// row-owner warps + shared-memory tiles + bulk (TMA) stores. Also home of the pieces the other renderers share (ObjI,
+// the slot loaders, make_obji).
 // Included by dh_kernels.cu after RenderParams / radius_center_one are defined.
 //
 // Replaces draw_gaussian + atomicMax of the reference

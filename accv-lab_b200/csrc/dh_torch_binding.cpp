@@ -475,7 +475,7 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> pack_radius_center(const std::vec
 at::Tensor draw_gaussians(const c10::optional<at::Tensor>& heatmap_in, at::Tensor& heatmap_out,
                           const c10::optional<at::Tensor>& active, const c10::optional<at::Tensor>& slice_ids,
                           const at::Tensor& centers, const at::Tensor& radii, const at::Tensor& nums_targets,
-                          const at::Tensor& k_for_classes, double radius_to_sigma_factor) {
+                          const at::Tensor& k_for_classes, double radius_to_sigma_factor, int64_t fast) {
     CHECK_INPUT(heatmap_out);
     CHECK_INPUT(centers);
     CHECK_INPUT(radii);
@@ -528,9 +528,13 @@ at::Tensor draw_gaussians(const c10::optional<at::Tensor>& heatmap_in, at::Tenso
     int tag = 0;
     const void* sizes = sizes_ptr(nums_targets, tag);
     c10::cuda::CUDAGuard guard(heatmap_out.device());
-    at::Tensor ws;  // FRESH fast path (classify -> main renderer -> exact fix-up)
+    // FRESH fast path (classify -> main renderer -> exact fix-up): three launches instead of one, selected by handing the C
+    // ABI a workspace. fast = 1 / 0 forces / forbids it; -1 (default) takes it from 256 MiB of output on (measured
+    // break-even ~200 MB on B200).
+    at::Tensor ws;
     size_t wsb = 0;
-    if (!heatmap_in.has_value() && T > 0) {
+    const bool want_fast = fast > 0 || (fast < 0 && heatmap_out.numel() * 4 >= ((int64_t)256 << 20));
+    if (!heatmap_in.has_value() && T > 0 && want_fast) {
         wsb = dh_draw_gaussians_workspace_bytes(B, T);
         ws = at::empty({(int64_t)wsb}, heatmap_out.options().dtype(at::kByte));
     }
@@ -734,7 +738,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           "DALI draw_gaussians semantics (float radii, per-class k, active flags) on RaggedBatch-layout inputs; one launch.",
           pybind11::arg("heatmap_in"), pybind11::arg("heatmap_out"), pybind11::arg("active"), pybind11::arg("slice_ids"),
           pybind11::arg("centers"), pybind11::arg("radii"), pybind11::arg("nums_targets"), pybind11::arg("k_for_classes"),
-          pybind11::arg("radius_to_sigma_factor"));
+          pybind11::arg("radius_to_sigma_factor"), pybind11::arg("fast") = -1);
     m.def("boxes_to_gaussian_params", &boxes_to_gaussian_params,
           "Boxes -> (clipped boxes, int centres, offsets, float radii, is_active, clipped hw, area fraction): the front half of the DALI heatmap converter, one launch.",
           pybind11::arg("bboxes"), pybind11::arg("centers"), pybind11::arg("classes"), pybind11::arg("is_valid"),

@@ -1,9 +1,5 @@
 """pytest configuration: markers, import paths, build-on-demand of the oracle (gcc) — never of CUDA code."""
 import os
-
-# The FRESH fast path of dh_draw_gaussians normally needs >= 256 MiB of output; the library reads this once when it is
-# loaded, so it is set before anything can load it: the parity tests then exercise the fast path at test sizes.
-os.environ.setdefault("DH_GS_FORCE_FAST", "1")
 import sys
 
 import pytest

@@ -14,7 +14,6 @@ import pytest
 
 import _cabi
 
-FORCED_FAST = os.environ.get("DH_GS_FORCE_FAST") is not None  # set in conftest.py before the library loads
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_dali.npz")
 CASES = ("typical", "integer_r", "tiny_r", "two_d", "neg_k", "near_int")
 
@@ -109,9 +108,9 @@ def test_gpu_fresh_fast_path_on_the_golden_objects(cuda_dev, oracle, name):
     oracle.draw_gaussians(want, c["centers"], c["radii"], c["sizes"], c["k"], float(c["factor"]), c["slice_ids"], c["active"])
     l0 = b200.launch_count()
     fast = b200.draw_gaussians(None, rb(c["active"]), rb(c["slice_ids"]), rb(c["centers"]), rb(c["radii"]), dev(c["k"]),
-                               float(c["factor"]), shape=shape)
+                               float(c["factor"]), shape=shape, fast=True)
     W = shape[-1]
-    assert b200.launch_count() - l0 == (3 if (W % 4 == 0 and W <= 1024 and FORCED_FAST) else 1)
+    assert b200.launch_count() - l0 == (3 if (W % 4 == 0 and W <= 1024) else 1)
     _check(fast.cpu().numpy(), want, name + " fresh fast")
     zeros = torch.zeros(shape, device=cuda_dev)
     exact = b200.draw_gaussians(zeros, rb(c["active"]), rb(c["slice_ids"]), rb(c["centers"]), rb(c["radii"]), dev(c["k"]),
@@ -160,7 +159,7 @@ def test_gpu_vs_oracle_shapes(cabi, cuda_dev, oracle, H, W, T, C):
     out_f = torch.full((B, C, H, W), 9.0, device=cuda_dev)
     l0 = cabi.dh_launch_count()
     run(None, out_f, fast=True)  # fresh, classify -> main renderer -> exact fix-up (when the map qualifies)
-    assert cabi.dh_launch_count() - l0 == (3 if (W % 4 == 0 and W <= 1024 and FORCED_FAST) else 1)
+    assert cabi.dh_launch_count() - l0 == (3 if (W % 4 == 0 and W <= 1024) else 1)
     _check(out_f.cpu().numpy(), want, "fresh fast path")
     assert torch.equal(out_f, out), "fast path and exact kernel must agree bit for bit"
     bg = (rng.random((B, C, H, W), dtype=np.float32) * 0.6 * (rng.random((B, C, H, W)) < 0.3)).astype(np.float32)
@@ -267,3 +266,31 @@ def test_gpu_converter_front_half_matches_reference_bit_for_bit(cuda_dev, name):
     orc.draw_gaussians(want, c["center_int"], c["radii"], c["sizes"], kcls, 1.0 / 3.0,
                        np.clip(c["classes"], 0, C - 1).astype(np.int32) if c["use_classes"] else None, c["is_active"])
     _check(heat.cpu().numpy(), want, name + " render")
+
+
+@pytest.mark.gpu
+def test_gpu_fast_path_is_automatic_from_256_mib(cuda_dev):
+    """The product's own rule, no forcing: below 256 MiB of output b200.draw_gaussians is ONE launch (the exact kernel),
+    from 256 MiB on THREE (classify -> main renderer -> exact fix-up), and both give the same bits as the exact kernel."""
+    import torch
+    from accvlab.draw_heatmap import b200
+
+    C, H, W, T = 10, 232, 400, 100
+    for B, launches in ((8, 1), (80, 3)):  # 29.7 MB / 297 MB of output
+        g = torch.Generator().manual_seed(B)
+        sizes = torch.randint(0, T + 1, (B,), generator=g, dtype=torch.int64)
+        centers = torch.stack([torch.randint(-5, W + 5, (B, T), generator=g), torch.randint(-5, H + 5, (B, T), generator=g)],
+                              2).int()
+        radii = (torch.rand(B, T, generator=g) * 30 + 0.4).float()
+        radii[torch.rand(B, T, generator=g) < 0.3] = 7.0  # integer radii: the symmetric-window class of the fast path
+        slice_ids = torch.randint(0, C, (B, T), generator=g).int()
+        k = (0.5 + 0.5 * torch.rand(C, generator=g)).float().to(cuda_dev)
+        d = [t.to(cuda_dev) for t in (centers, radii, slice_ids, sizes)]
+        rb = lambda t: b200.RaggedBatch(t, sample_sizes=d[3])
+        l0 = b200.launch_count()
+        auto = b200.draw_gaussians(None, None, rb(d[2]), rb(d[0]), rb(d[1]), k, 0.35, shape=(B, C, H, W))
+        assert b200.launch_count() - l0 == launches
+        exact = b200.draw_gaussians(None, None, rb(d[2]), rb(d[0]), rb(d[1]), k, 0.35, shape=(B, C, H, W), fast=False)
+        torch.cuda.synchronize()
+        assert torch.equal(auto, exact)
+        del auto, exact
