@@ -63,8 +63,12 @@ constexpr int kGPermScratch = kGWarps * kGPermBins * 2 + 64;  // bytes of the st
 // dynamic shared memory: zero tile | 8 warps x 2 staging buffers of `stage` bytes | unit list
 // dynamic shared memory: [zero tile] | kGWarps x (2 | 1) staging buffers of `stage` bytes | unit list.
 // ACCUMULATE has no zero tile and one staging buffer per warp (scratch of the dense path; nothing leaves from it).
-__host__ __device__ constexpr size_t groups_smem_bytes(int stage, bool accum = false) {
-    return (size_t)(accum ? 0 : kGZeroBytes) + (size_t)kGWarps * (accum ? 1 : 2) * (size_t)stage + (size_t)kGCap * sizeof(ObjI);
+// LEAN (object-heavy FRESH renders, T >= 256): the zero tile stays, but one staging buffer per warp — the render of a
+// group takes far longer than the bulk read of the previous one, so there is nothing to double-buffer — which buys twice
+// the rows per group (the per-object set-up is paid per group) and the fourth CTA per SM.
+__host__ __device__ constexpr size_t groups_smem_bytes(int stage, bool accum = false, bool lean = false) {
+    return (size_t)(accum ? 0 : kGZeroBytes) + (size_t)kGWarps * ((accum || lean) ? 1 : 2) * (size_t)stage +
+           (size_t)kGCap * sizeof(ObjI);
 }
 
 __device__ __forceinline__ unsigned enc_m(float m, bool kneg) {
@@ -286,6 +290,7 @@ __device__ __forceinline__ ObjI shfl_obj(const ObjI& o, int src) {
 struct WarpStage {
     unsigned* buf0;
     unsigned* buf1;
+    bool single = false;  // LEAN layout: one buffer, re-used once the copy engine has read it
     int cur = 0;
     int c0x0 = 1, c0x1 = 0, c1x0 = 1, c1x1 = 0;
 };
@@ -317,7 +322,10 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
                                                                           (ws.cur ? (p.stage_bytes >> 1) : 0));
     unsigned* const buf = (OUT == OUT_F32) ? obuf : ws.buf0;
     if constexpr (!ACCUM) {
-        if (lane == 0) bulk_wait_read<1>();  // the store that last read `obuf` is older than my latest one
+        if (lane == 0) {
+            if (ws.single) bulk_wait_read<0>();  // one buffer: every store of mine has been read
+            else bulk_wait_read<1>();            // the store that last read `obuf` is older than my latest one
+        }
         __syncwarp();
         const int cx0 = ws.cur ? ws.c1x0 : ws.c0x0, cx1 = ws.cur ? ws.c1x1 : ws.c0x1;
         if (cx1 >= cx0) {  // back to all-zero: clear only what its last use wrote (4 pixels per store, W % 4 == 0)
@@ -425,7 +433,7 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
             ws.c0x0 = ux0;
             ws.c0x1 = ux1;
         }
-        ws.cur ^= 1;
+        if (!ws.single) ws.cur ^= 1;
     } else {
         __syncwarp();
     }
@@ -700,10 +708,11 @@ __device__ unsigned long long* g_trace = nullptr;
 __device__ long long g_trace_units = 0;
 #endif
 
-template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32>
-__global__ void __launch_bounds__(kGThreads, ACCUM ? DH_G_MINB_ACCUM : DH_G_MINB) groups_kernel(const RenderParams p) {
-    constexpr int ZB = ACCUM ? 0 : kGZeroBytes;  // bytes of the zero tile
-    constexpr int NB = ACCUM ? 1 : 2;            // staging buffers per warp
+template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32, bool LEAN = false>
+__global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM : DH_G_MINB) groups_kernel(const RenderParams p) {
+    static_assert(!LEAN || (!ACCUM && OUT == OUT_F32), "the lean layout is a FRESH fp32 variant");
+    constexpr int ZB = ACCUM ? 0 : kGZeroBytes;    // bytes of the zero tile
+    constexpr int NB = (ACCUM || LEAN) ? 1 : 2;    // staging buffers per warp
     constexpr int ES = (OUT == OUT_F32) ? 4 : 2;  // bytes per heatmap element
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float4* const zero_tile = reinterpret_cast<float4*>(smem_raw);
@@ -734,7 +743,8 @@ __global__ void __launch_bounds__(kGThreads, ACCUM ? DH_G_MINB_ACCUM : DH_G_MINB
     }
     WarpStage ws;
     ws.buf0 = reinterpret_cast<unsigned*>(smem_raw + ZB + warp * NB * stage);
-    ws.buf1 = ws.buf0 + (NB - 1) * (stage / 4);  // ACCUMULATE: one buffer (ws.cur never flips there)
+    ws.buf1 = ws.buf0 + (NB - 1) * (stage / 4);  // ACCUMULATE / LEAN: one buffer (ws.cur never flips there)
+    ws.single = LEAN;
     bool stage_clean = false;  // my staging buffers are all-zero (established before my first render_group)
     unsigned clc_phase = 0;
     Digest dg;

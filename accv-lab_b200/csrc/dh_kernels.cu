@@ -680,6 +680,7 @@ static const int g_persistent = DH_KNOB("DH_G_PERSISTENT", 0);         // 1: sta
 static const int g_no_clc = DH_KNOB("DH_G_NOCLC", 0);                  // 1: no cluster launch control
 static const int g_single_wave = DH_KNOB("DH_G_SINGLE_WAVE", 1);       // small problems: one wave of larger units
 static const int g_heavy_per_slot = DH_KNOB("DH_G_HEAVY_PER_SLOT", 8); // units per resident CTA slot when T >= 256
+static const int g_lean = DH_KNOB("DH_G_LEAN", 1);                     // object-heavy FRESH renders: lean shared-memory layout
 static const int g_no_bin = DH_KNOB("DH_G_NOBIN", 0);                  // 1: ignore the workspace of the *_ws entries
 static const int g_lpt = DH_KNOB("DH_G_LPT", 10);                      // heaviest-first hand-out inside the last g_lpt / 2 waves (0 = off)
 static const int g_pdl = DH_KNOB("DH_G_PDL", 1);                       // programmatic dependent launch of the groups kernels
@@ -692,10 +693,11 @@ static const int g_tail_waves_x2 = DH_KNOB("DH_G_TAIL_WAVES_X2", 2);   // tail t
 // is not, so that every resident CTA slot still sees several units.
 // `es` = bytes per heatmap element (4, or 2 for the 16-bit planes: rows per group still follow the fp32 scratch).
 // Returns false when 16-bit planes cannot be cut into 16-byte aligned groups.
-static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4, bool accum = false) {
+static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4, bool accum = false, bool lean = false) {
     // rows per group: as many as a staging buffer holds while DH_G_MINB(_ACCUM) CTAs still fit the SM's shared memory
-    const long long smem_budget = (227ll * 1024) / (accum ? DH_G_MINB_ACCUM : DH_G_MINB) - 1024 - kGPermSmem;  // 1 KB: the system's
-    const long long stage_budget = (smem_budget - (long long)groups_smem_bytes(0, accum)) / ((accum ? 1 : 2) * kGWarps);
+    const bool one = accum || lean;  // one staging buffer per warp, four CTAs per SM
+    const long long smem_budget = (227ll * 1024) / (one ? DH_G_MINB_ACCUM : DH_G_MINB) - 1024 - kGPermSmem;  // 1 KB: the system's
+    const long long stage_budget = (smem_budget - (long long)groups_smem_bytes(0, accum, lean)) / ((one ? 1 : 2) * kGWarps);
     int G = (int)((stage_budget < kGStageCap ? stage_budget : kGStageCap) / (p.W * 4));
     if (G < 1) G = 1;
     if (G > p.H) G = p.H;
@@ -777,20 +779,20 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 
-template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32>
+template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32, bool LEAN = false>
 static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     static std::atomic<bool> attr_set_dev[64];  // function attributes are per device: one process may drive several GPUs
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
     if (!attr_set_dev[dev].load(std::memory_order_acquire)) {
-        const int cap = (int)groups_smem_bytes(kGStageCap, ACCUM);  // widest map: fewer CTAs per SM then
-        cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST, OUT>,
+        const int cap = (int)groups_smem_bytes(kGStageCap, ACCUM, LEAN);  // widest map: fewer CTAs per SM then
+        cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST, OUT, LEAN>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
         if (e != cudaSuccess) return (int)e;
         attr_set_dev[dev].store(true, std::memory_order_release);
     }
-    const long long max_ctas = (long long)sms * (ACCUM ? DH_G_MINB_ACCUM : DH_G_MINB);
-    if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2, ACCUM)) return DH_ERR_UNSUPPORTED_SHAPE;
+    const long long max_ctas = (long long)sms * ((ACCUM || LEAN) ? DH_G_MINB_ACCUM : DH_G_MINB);
+    if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2, ACCUM, LEAN)) return DH_ERR_UNSUPPORTED_SHAPE;
     if (p.total_units == 0) return DH_OK;
     // Flat grid, one CTA per unit: the block scheduler hands units out dynamically and in address order, which
     // balances SMs that see different effective store bandwidth; a static grid-stride loop runs at the pace of the
@@ -807,7 +809,7 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_WEIGHTED) {
         const long long B = p.num_planes / (p.C > 0 ? p.C : 1);
         if (g_lpt && p.total_units > max_ctas && B >= 2 && p.T >= 1 &&
-            (long long)kGWarps * (ACCUM ? 1 : 2) * p.stage_bytes >= kGPermScratch) {
+            (long long)kGWarps * ((ACCUM || LEAN) ? 1 : 2) * p.stage_bytes >= kGPermScratch) {
             // only the samples handed out in the last g_lpt / 2 waves are rearranged: rearranging all of them was measured
             // SLOWER on large batches (cfg5 1.576 -> 1.635 ms): it scatters the set of addresses being written over the whole
             // buffer, and the write rate depends on that set staying compact (profiles/r02/experiments.md)
@@ -818,8 +820,8 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
             p.perm_base = B - p.perm_n;
         }
     }
-    const cudaError_t e = launch_pdl(groups_kernel<ACCUM, SRC, DIGEST, OUT>, dim3((unsigned)g), dim3(kGThreads),
-                                     groups_smem_bytes(p.stage_bytes, ACCUM), stream, p);
+    const cudaError_t e = launch_pdl(groups_kernel<ACCUM, SRC, DIGEST, OUT, LEAN>, dim3((unsigned)g), dim3(kGThreads),
+                                     groups_smem_bytes(p.stage_bytes, ACCUM, LEAN), stream, p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
@@ -893,6 +895,14 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode, long lo
     }
     if (vec && p.W <= kGMaxW) {  // main path: row groups striped over warps, per-warp staging + bulk stores
         if (accum) return launch_groups<true, SRC, false>(stream, p, di.sms);
+        if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+            // object-heavy FRESH renders (hundreds of objects per plane: instruction-issue bound, not store bound): the
+            // lean layout — one staging buffer per warp, twice the rows per group, four CTAs per SM
+            if (g_lean && p.T >= 256) {
+                if (p.digest != nullptr) return launch_groups<false, SRC, true, OUT_F32, true>(stream, p, di.sms);
+                return launch_groups<false, SRC, false, OUT_F32, true>(stream, p, di.sms);
+            }
+        }
         if (p.digest != nullptr) return launch_groups<false, SRC, true>(stream, p, di.sms);
         return launch_groups<false, SRC, false>(stream, p, di.sms);
     }
