@@ -55,6 +55,10 @@ constexpr int kGMaxW = kGStageCap / 4;      // widest map served by this kernel
 constexpr int kGZeroBytes = kGWarps == 8 ? 8192 : 4096;  // constant zero tile
 constexpr int kGCap = kGWarps == 8 ? 512 : 256;           // unit list capacity
 constexpr int kGMaxGroups = 64;             // groups per unit (bits of the occupancy mask)
+#ifndef DH_SPARSE_MAX
+#define DH_SPARSE_MAX 2  // 3 and 4 were measured: registers spill, cfg5 1.57 -> 1.70 / 1.85 ms (profiles/r02/experiments.md section 8)
+#endif
+constexpr int kSparseMax = DH_SPARSE_MAX;   // objects on a group that are still evaluated in registers (no staging sweep)
 constexpr int kGPermCap = 2048;             // samples whose hand-out order is rearranged (heaviest first)
 constexpr int kGPermBins = 256;             // counting-sort bins of that rearrangement
 constexpr int kGPermSmem = kGPermCap * 2;   // static shared memory it takes (bytes)
@@ -185,45 +189,80 @@ __device__ __forceinline__ void finish_row(unsigned* __restrict__ rowp, float* _
 //   k >= 0: max_o k*expf(-m_o) = k*expf(-min_o m_o);  k < 0: the max picks max_o m_o = -min_o(-m_o)
 // (expf is monotone: verified exhaustively on the device by tests/test_gpu_properties.py), so `ws` = +-1/var and one
 // fminf cover both signs; negation is exact, so every rounding is the reference's.
-template <bool ACCUM, bool DIGEST, int OUT>
-__device__ __forceinline__ void sparse_group(unsigned* __restrict__ buf, float* __restrict__ gdst, long long gindex, int y0,
-                                             int nrows, int W, const ObjI& A, const ObjI& B, bool hasB, bool kneg, float k,
-                                             int lane, int& ux0, int& ux1, Digest& dg) {
-    const int ax0 = max(A.x - A.r, 0), ax1 = min(A.x + A.r, W - 1);
-    const int bx0 = max(B.x - B.r, 0), bx1 = min(B.x + B.r, W - 1);
-    const float aw = kneg ? -A.w : A.w, bw = kneg ? -B.w : B.w;
-    const float fra = (float)A.r, frb = (float)B.r;
-    for (int rr = 0; rr < nrows; ++rr) {
-        const int dya = y0 + rr - A.y, dyb = y0 + rr - B.y;
-        const bool inA = abs(dya) <= A.r, inB = hasB && abs(dyb) <= B.r;  // warp-uniform
-        if (!(inA || inB)) continue;
-        const float fa = (float)dya, fb = (float)dyb;
-        const float fia = __fmul_rn(fa, fa), fib = __fmul_rn(fb, fb);
-        const int rx0 = inA ? (inB ? min(ax0, bx0) : ax0) : bx0;
-        const int rx1 = inA ? (inB ? max(ax1, bx1) : ax1) : bx1;
+// Round 2: rows are taken TWO AT A TIME and a group hit by ONE object (the common case) has its own instantiation. What
+// depends on x alone (dx, dx^2 — shared by both rows —, the |dx| <= r test) is computed once per 32-pixel chunk, the two
+// rows are two independent dependency chains through expf (a heavy unit is bound by the latency of that chain, not by
+// issue slots: unit timelines, profiles/r02/experiments.md section 8), and a single object skips the second candidate
+// altogether: ~22 instead of ~45 instructions per (row, chunk). The arithmetic per pixel is unchanged (cuh:45).
+template <bool ACCUM, bool DIGEST, int OUT, int N>
+__device__ __forceinline__ void sparse_rows(unsigned* __restrict__ buf, float* __restrict__ gdst, long long gindex, int y0,
+                                            int nrows, int W, const ObjI (&O)[N], bool kneg, float k, int lane, int& ux0,
+                                            int& ux1, Digest& dg) {
+    int ox0[N], ox1[N];
+    float ow[N], fr[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+        ox0[j] = max(O[j].x - O[j].r, 0);
+        ox1[j] = min(O[j].x + O[j].r, W - 1);
+        ow[j] = kneg ? -O[j].w : O[j].w;
+        fr[j] = (float)O[j].r;
+    }
+    // one finished pixel of row `rr` (v = expf(-m) * k already formed)
+    auto emit = [&](int rr, int x, float v) {
+        if constexpr (ACCUM) {
+            float* const gp = gdst + (long long)rr * W + x;
+            const float g = *gp;
+            if (!(g >= v)) *gp = v;  // cuh:30
+        } else {
+            const float f = (0.0f >= v) ? 0.0f : v;
+            if constexpr (OUT == OUT_F32) buf[rr * W + x] = __float_as_uint(f);
+            else reinterpret_cast<unsigned short*>(buf)[rr * W + x] = cvt16<OUT>(f);  // `buf` = the 16-bit buffer
+            if constexpr (DIGEST) dg.add(f, gindex + (long long)rr * W + x);
+        }
+    };
+    for (int rr = 0; rr < nrows; rr += 2) {
+        const bool has1 = rr + 1 < nrows;
+        bool in0[N], in1[N];  // object j covers row rr / row rr + 1 (warp-uniform)
+        float fi0[N], fi1[N];
+        int rx0 = W, rx1 = -1;
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+            const int dy = y0 + rr - O[j].y;
+            in0[j] = abs(dy) <= O[j].r;
+            in1[j] = has1 && abs(dy + 1) <= O[j].r;
+            const float f0 = (float)dy, f1 = (float)(dy + 1);
+            fi0[j] = __fmul_rn(f0, f0);
+            fi1[j] = __fmul_rn(f1, f1);
+            if (in0[j] || in1[j]) {
+                rx0 = min(rx0, ox0[j]);
+                rx1 = max(rx1, ox1[j]);
+            }
+        }
+        if (rx1 < rx0) continue;
         ux0 = min(ux0, rx0);
         ux1 = max(ux1, rx1);
         for (int xb = rx0; xb <= rx1; xb += 32) {
-            // branch-free: both candidates are evaluated (B is a copy of A when there is one object), then selected
             const int x = xb + lane;
-            const float fdxa = (float)(x - A.x), fdxb = (float)(x - B.x);  // exact (|dx| < 2^24)
-            const float ma = __fmul_rn(__fadd_rn(fia, __fmul_rn(fdxa, fdxa)), aw);
-            const float mb = __fmul_rn(__fadd_rn(fib, __fmul_rn(fdxb, fdxb)), bw);
-            const bool ta = inA && fabsf(fdxa) <= fra, tb = inB && fabsf(fdxb) <= frb;
-            const float acc = ta ? (tb ? fminf(ma, mb) : ma) : mb;
-            const bool touched = ta || tb;
-            if (touched && x <= rx1) {
-                const float v = __fmul_rn(expf(kneg ? acc : -acc), k);  // = expf(-m) * k
-                if constexpr (ACCUM) {
-                    float* const gp = gdst + (long long)rr * W + x;
-                    const float g = *gp;
-                    if (!(g >= v)) *gp = v;  // cuh:30
-                } else {
-                    const float f = (0.0f >= v) ? 0.0f : v;
-                    if constexpr (OUT == OUT_F32) buf[rr * W + x] = __float_as_uint(f);
-                    else reinterpret_cast<unsigned short*>(buf)[rr * W + x] = cvt16<OUT>(f);  // `buf` = the 16-bit buffer
-                    if constexpr (DIGEST) dg.add(f, gindex + (long long)rr * W + x);
+            float dx2[N];
+            bool tx[N];
+#pragma unroll
+            for (int j = 0; j < N; ++j) {
+                const float fdx = (float)(x - O[j].x);  // exact (|dx| < 2^24)
+                dx2[j] = __fmul_rn(fdx, fdx);
+                tx[j] = fabsf(fdx) <= fr[j] && x <= rx1;
+            }
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {  // row rr, row rr + 1
+                float acc = 0.0f;
+                bool touched = false;
+#pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    const bool t = (h ? in1[j] : in0[j]) && tx[j];
+                    const float m = __fmul_rn(__fadd_rn(h ? fi1[j] : fi0[j], dx2[j]), ow[j]);
+                    acc = t ? (touched ? fminf(acc, m) : m) : acc;
+                    touched = touched || t;
                 }
+                if (touched) emit(rr + h, x, __fmul_rn(expf(kneg ? acc : -acc), k));  // = expf(-m) * k
             }
         }
     }
@@ -358,14 +397,25 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
         const bool hit = (mine.r >= 0) && (mine.y + mine.r >= y0) && (mine.y - mine.r <= y1);
         unsigned bal = __ballot_sync(0xffffffffu, hit);
         const int nh = __popc(bal);
-        if (nh <= 2) {
+        if (nh <= kSparseMax) {  // register path: every hit object is evaluated per pixel, nothing goes through staging
             if (nh > 0) {
-                const int sa = __ffs(bal) - 1;
-                const unsigned rest = bal & (bal - 1u);
-                const int sb = rest ? __ffs(rest) - 1 : sa;
-                const ObjI A = shfl_obj(mine, sa), B = shfl_obj(mine, sb);
-                sparse_group<ACCUM, DIGEST, OUT>(obuf, gdst, gindex, y0, nrows, W, A, B, rest != 0u, kneg, k, lane, ux0, ux1,
-                                                 dg);
+                ObjI O[kSparseMax];
+                unsigned rest = bal;
+#pragma unroll
+                for (int j = 0; j < kSparseMax; ++j) {
+                    const int src = rest ? __ffs(rest) - 1 : 0;
+                    rest &= rest - 1u;
+                    O[j] = shfl_obj(mine, src);
+                }
+                if (nh == 1) {
+                    const ObjI O1[1] = {O[0]};
+                    sparse_rows<ACCUM, DIGEST, OUT, 1>(obuf, gdst, gindex, y0, nrows, W, O1, kneg, k, lane, ux0, ux1, dg);
+                } else if (nh == 2) {
+                    const ObjI O2[2] = {O[0], O[1]};
+                    sparse_rows<ACCUM, DIGEST, OUT, 2>(obuf, gdst, gindex, y0, nrows, W, O2, kneg, k, lane, ux0, ux1, dg);
+                } else {
+                    sparse_rows<ACCUM, DIGEST, OUT, kSparseMax>(obuf, gdst, gindex, y0, nrows, W, O, kneg, k, lane, ux0, ux1, dg);
+                }
             }
         } else {
             finish = true;
