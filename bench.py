@@ -341,13 +341,17 @@ def run_ours(args):
     # step time bounds the renderer's duration from above
     launch_ms = ms_total / max(args.steps, 1)
     achieved = algo_bytes / (launch_ms * 1e-3) / 1e9
-    traffic = None
+    # `traffic` is an OFFLINE figure (one ncu --set full capture per kernel change, profiles/roofline_traffic.json names
+    # the capture and the commit it was taken at); everything else in this object is measured in this run
+    traffic, traffic_source = None, None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get(f"{cfg.name}_n{world}")
+        tj = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))
+        traffic = tj.get(f"{cfg.name}_n{world}")
+        traffic_source = tj.get("source") if traffic is not None else None
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": ("dh::groups_kernel<false,SRC_BOXES,false,OUT_F32>" if not args.two_launch else
+                "traffic": traffic, "traffic_source": traffic_source, "kernel": ("dh::groups_kernel<false,SRC_BOXES,false,OUT_F32>" if not args.two_launch else
                            "dh::groups2_kernel<false,false,OUT_F32> (+ dh::bin_kernel<SRC_BOXES> in the same step)"),
                 "peak_source": peak_src, "launches_per_step": launches / max(args.steps, 1),
                 "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": launch_ms,
@@ -373,6 +377,8 @@ def run_ours(args):
         step(0)  # restore a rendered result in buffer 0
         torch.cuda.synchronize()
     roofline["write_only_ceilings"] = ceil
+    if ceil.get("torch_zero__GBps"):  # the copy peak is a read+write figure; a write-only kernel is better judged against this
+        roofline["frac_of_torch_zero_"] = achieved / ceil["torch_zero__GBps"]
     return dict(torch=torch, lib=lib, _cabi=_cabi, dist=dist, dev=dev, rank=rank, world=world, w=w, w_all=w_all, lo=lo,
                 host=(h_cf, h_bf, h_sz, h_lab), heats=heats, value=value, ms_step=ms_step, launches=launches,
                 roofline=roofline, digest=digest, sampler=sampler, warm=warm, barrier=barrier)
