@@ -681,6 +681,7 @@ static const int g_no_clc = DH_KNOB("DH_G_NOCLC", 0);                  // 1: no 
 static const int g_single_wave = DH_KNOB("DH_G_SINGLE_WAVE", 1);       // small problems: one wave of larger units
 static const int g_heavy_per_slot = DH_KNOB("DH_G_HEAVY_PER_SLOT", 8); // units per resident CTA slot when T >= 256
 static const int g_lean = DH_KNOB("DH_G_LEAN", 1);                     // object-heavy FRESH renders: lean shared-memory layout
+static const int g_lean_t = DH_KNOB("DH_G_LEAN_T", 256);                // ... from this many padded targets per sample on
 static const int g_no_bin = DH_KNOB("DH_G_NOBIN", 0);                  // 1: ignore the workspace of the *_ws entries
 static const int g_lpt = DH_KNOB("DH_G_LPT", 10);                      // heaviest-first hand-out inside the last g_lpt / 2 waves (0 = off)
 static const int g_pdl = DH_KNOB("DH_G_PDL", 1);                       // programmatic dependent launch of the groups kernels
@@ -898,7 +899,7 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode, long lo
         if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
             // object-heavy FRESH renders (hundreds of objects per plane: instruction-issue bound, not store bound): the
             // lean layout — one staging buffer per warp, twice the rows per group, four CTAs per SM
-            if (g_lean && p.T >= 256) {
+            if (g_lean && p.T >= g_lean_t) {
                 if (p.digest != nullptr) return launch_groups<false, SRC, true, OUT_F32, true>(stream, p, di.sms);
                 return launch_groups<false, SRC, false, OUT_F32, true>(stream, p, di.sms);
             }
