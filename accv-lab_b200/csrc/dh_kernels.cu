@@ -1000,6 +1000,9 @@ const char* dh_status_string(int status) {
         case DH_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
         case DH_ERR_UNSUPPORTED_SHAPE: return "unsupported shape (need 1 <= H,W <= 2^23 and H*W < 2^31)";
         case DH_ERR_NO_DEVICE: return "no usable CUDA device";
+        case DH_ERR_STATIC_SCRATCH_EXCEEDED:
+            return "problem needs more scratch than the built-in static array holds (DH_NOALLOC_MAX_SCRATCH_BYTES): use the "
+                   "*_ws entry with a caller workspace";
         default: break;
     }
     if (status > 0) return cudaGetErrorString((cudaError_t)status);
@@ -1089,6 +1092,53 @@ int dh_draw_heatmap_batched(void* stream, float* heatmap, const int32_t* centers
     return dh_draw_heatmap_batched_ws(stream, heatmap, centers, radii, nums_targets, nums_dtype, labels, batch_size,
                                       max_num_targets, num_classes, height, width, diameter_to_sigma_factor, k_scale, mode,
                                       status, nullptr, 0);
+}
+
+// ---- allocation-free entry: the bin-list scratch of the two-launch path lives in the library image ---------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). Every GPU that loads the library holds
+// DH_NOALLOC_MAX_SCRATCH_BYTES of device memory for it until exit. ONE array per device, shared by every call: calls
+// that overlap on the GPU (two streams, two threads) race on it. bin_kernel rewrites every (start, count) record and
+// every list entry a record can reach before groups2_kernel reads them, so nothing has to start at zero and the last
+// call's contents are harmless.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[DH_NOALLOC_MAX_SCRATCH_BYTES];
+
+// `g_noalloc_scratch` in HOST code is a host-side stand-in, not a device address: the device address is looked up once
+// per device, with that device current, and cached.
+static int noalloc_scratch_ptr(void** out) {
+    static std::atomic<void*> cache[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
+    void* ptr = cache[dev].load(std::memory_order_acquire);
+    if (ptr == nullptr) {
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (ptr == nullptr) return DH_ERR_NO_DEVICE;
+        cache[dev].store(ptr, std::memory_order_release);  // racing first calls store the same value
+    }
+    *out = ptr;
+    return DH_OK;
+}
+
+size_t dh_noalloc_max_scratch_bytes(void) { return (size_t)DH_NOALLOC_MAX_SCRATCH_BYTES; }
+
+int dh_draw_heatmap_batched_noalloc(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
+                                    const void* nums_targets, int nums_dtype, const int32_t* labels, int64_t batch_size,
+                                    int64_t max_num_targets, int64_t num_classes, int64_t height, int64_t width,
+                                    float diameter_to_sigma_factor, float k_scale, int mode, dh_status* status) {
+    if (batch_size < 0 || max_num_targets < 0 || num_classes < 0) return DH_ERR_INVALID_ARGUMENT;
+    // size check first, without touching a device: beyond the built-in array is an error, never a silent other path
+    const int64_t cap = (int64_t)DH_NOALLOC_MAX_SCRATCH_BYTES;
+    const int64_t C1 = (labels && num_classes > 1) ? num_classes : 1;
+    if (batch_size > 0 && (C1 > cap || max_num_targets > cap || 8 * C1 + 16 * max_num_targets > cap / batch_size))
+        return DH_ERR_STATIC_SCRATCH_EXCEEDED;  // (overflow-free bound on B * (8 C + 16 T))
+    if (dh_batched_workspace_bytes(batch_size, max_num_targets, C1) > (size_t)cap) return DH_ERR_STATIC_SCRATCH_EXCEEDED;
+    void* scratch = nullptr;
+    const int st = noalloc_scratch_ptr(&scratch);
+    if (st != DH_OK) return st;
+    return batched_common(stream, heatmap, centers, radii, nullptr, nullptr, 1.0f, nums_targets, nums_dtype, labels,
+                          batch_size, max_num_targets, num_classes, height, width, diameter_to_sigma_factor, k_scale,
+                          mode, status, nullptr, 0, scratch, (size_t)DH_NOALLOC_MAX_SCRATCH_BYTES);
 }
 
 int dh_draw_heatmap_batched_from_boxes(void* stream, float* heatmap, const float* centers_xy, const float* bboxes_xyxy,

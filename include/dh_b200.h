@@ -41,6 +41,7 @@ extern "C" {
 #define DH_ERR_WORKSPACE_TOO_SMALL (-2)
 #define DH_ERR_UNSUPPORTED_SHAPE (-3)
 #define DH_ERR_NO_DEVICE (-4)
+#define DH_ERR_STATIC_SCRATCH_EXCEEDED (-5) /* dh_draw_heatmap_batched_noalloc: problem beyond DH_NOALLOC_MAX_SCRATCH_BYTES */
 
 /* blend mode */
 #define DH_MODE_ACCUMULATE 0 /* reference semantics: max-blend into existing contents (read+write touched pixels) */
@@ -162,6 +163,29 @@ int dh_draw_heatmap_batched_from_boxes_digest_ws(void* stream, float* heatmap, c
                                                  int64_t height, int64_t width, float diameter_to_sigma_factor,
                                                  float k_scale, int64_t index_base, uint64_t* digest_out3,
                                                  dh_status* status, void* workspace, size_t workspace_bytes);
+
+/* ---- allocation-free variant of dh_draw_heatmap_batched_ws ------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation). Same arguments,
+ * same results (bit for bit) as dh_draw_heatmap_batched / dh_draw_heatmap_batched_ws; the bin-list workspace of the
+ * two-launch path is a file-scope static __device__ array inside the library (DH_NOALLOC_MAX_SCRATCH_BYTES = 8 MiB;
+ * every GPU that loads the library holds that much device memory until the process exits). The call allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine); the caller passes inputs and outputs only.
+ *   limit:   dh_batched_workspace_bytes(B, T, C) <= DH_NOALLOC_MAX_SCRATCH_BYTES (e.g. B*T <= ~520 k slots at C = 10;
+ *            cfg5, B = 3072 x T = 100 x C = 10, needs 5.2 MB), else DH_ERR_STATIC_SCRATCH_EXCEEDED — never a silent
+ *            change of path. Shapes the two-launch path does not serve (see the *_ws entries) run the single-launch
+ *            renderer, which needs no scratch at all.
+ *   sharing: ONE array per device, shared by every call in the process, keeping the last call's contents; nothing in
+ *            it has to start at zero (every record and reachable list entry is rewritten by the call's first launch
+ *            before its second reads it). Calls that may OVERLAP on the GPU (different streams or threads) race on it:
+ *            serialise them, or use the *_ws entry with one workspace each. */
+#define DH_NOALLOC_MAX_SCRATCH_BYTES (8u << 20)
+size_t dh_noalloc_max_scratch_bytes(void);
+int dh_draw_heatmap_batched_noalloc(void* stream, float* heatmap, const int32_t* centers, const int32_t* radii,
+                                    const void* nums_targets, int nums_dtype, const int32_t* labels,
+                                    int64_t batch_size, int64_t max_num_targets, int64_t num_classes, int64_t height,
+                                    int64_t width, float diameter_to_sigma_factor, float k_scale, int mode,
+                                    dh_status* status);
 
 /* ---- 16-bit heatmap planes (not in the reference, whose heatmaps are float32 only:
  * draw_heatmap_cuda.cu:84,117,160 `data_ptr<float>()`) -------------------------------------

@@ -46,6 +46,8 @@ SIGNATURES = {
                                                           _f, _i64, _p, _p, _p, _sz]),
     "dh_render_heatmap_batched_16_ws": (_i, [_p, _p, _i, _p, _p, _p, _p, _f, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f,
                                              _f, _p, _p, _sz]),
+    "dh_noalloc_max_scratch_bytes": (_sz, []),
+    "dh_draw_heatmap_batched_noalloc": (_i, [_p, _p, _p, _p, _p, _i, _p, _i64, _i64, _i64, _i64, _i64, _f, _f, _i, _p]),
     "dh_draw_heatmap_workspace_bytes": (_sz, [_i64, _i64]),
     "dh_draw_heatmap": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _i, _p, _sz, _p]),
     "dh_checksum": (_i, [_p, _p, _i64, _i64, _p]),
