@@ -441,6 +441,7 @@ __global__ void __launch_bounds__(kThreads) render_kernel(const RenderParams p) 
 #include "dh_rows_kernel.cuh"
 #include "dh_groups_kernel.cuh"
 #include "dh_groups2_kernel.cuh"
+#include "dh_tiles_kernel.cuh"
 namespace dh {
 
 // ------------------------------------------------------------------------------------------------
@@ -682,6 +683,8 @@ static const int g_single_wave = DH_KNOB("DH_G_SINGLE_WAVE", 1);       // small 
 static const int g_heavy_per_slot = DH_KNOB("DH_G_HEAVY_PER_SLOT", 8); // units per resident CTA slot when T >= 256
 static const int g_lean = DH_KNOB("DH_G_LEAN", 1);                     // object-heavy FRESH renders: lean shared-memory layout
 static const int g_lean_t = DH_KNOB("DH_G_LEAN_T", 256);                // ... from this many padded targets per sample on
+static const int g_tiles = DH_KNOB("DH_G_TILES", 1);                   // object-heavy renders (k >= 0): register-tile renderer
+static const int g_tiles_t = DH_KNOB("DH_G_TILES_T", 256);              // ... from this many padded targets per sample on
 static const int g_no_bin = DH_KNOB("DH_G_NOBIN", 0);                  // 1: ignore the workspace of the *_ws entries
 static const int g_lpt = DH_KNOB("DH_G_LPT", 10);                      // heaviest-first hand-out inside the last g_lpt / 2 waves (0 = off)
 static const int g_pdl = DH_KNOB("DH_G_PDL", 1);                       // programmatic dependent launch of the groups kernels
@@ -827,6 +830,30 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
 
+// Object-heavy renders (dh_tiles_kernel.cuh): one CTA per strip of kTRows rows, register tiles, flat grid + launch control.
+template <bool ACCUM, int SRC, bool DIGEST>
+static int launch_tiles(cudaStream_t stream, RenderParams& p) {
+    const int upp = (p.H + kTRows - 1) / kTRows;
+    p.band_cols = p.band_rows = kTRows;
+    p.bands_y = p.bands_per_plane = upp;
+    p.bands_x = 1;
+    p.units_per_plane = p.units_per_plane2 = upp;
+    p.bands_per_unit = p.bands_per_unit2 = 1;
+    p.tier1_planes = p.num_planes;
+    p.tier1_units = p.total_units = p.num_planes * upp;
+    p.perm_n = 0;
+    p.perm_base = 0;
+    p.stage_bytes = 0;
+    if (p.total_units == 0) return DH_OK;
+    long long g = p.total_units;
+    p.use_clc = !g_no_clc && g <= 0x7fffffffll;  // a clamped grid falls back to the static stride
+    if (g > 0x7fffffffll) g = 0x7fffffffll;
+    const cudaError_t e = launch_pdl(tiles_kernel<ACCUM, SRC, DIGEST>, dim3((unsigned)g), dim3(kGThreads),
+                                     tiles_smem_bytes(ACCUM), stream, p);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
+}
+
 // K2 pre-pass + warp-autonomous renderer (dh_groups2_kernel.cuh): two launches, the second one programmatically
 // dependent on the first (its prologue overlaps bin_kernel; it waits before it reads the lists).
 template <bool ACCUM, bool DIGEST, int OUT = OUT_F32>
@@ -895,6 +922,15 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode, long lo
         }
     }
     if (vec && p.W <= kGMaxW) {  // main path: row groups striped over warps, per-warp staging + bulk stores
+        if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
+            // object-heavy renders (hundreds of objects per plane: instruction-issue bound, not store bound): register
+            // tiles. k < 0 stays with the staged renderer (its order-preserving encode covers that sign).
+            if (g_tiles && p.T >= g_tiles_t && !(p.k < 0.0f)) {
+                if (accum) return launch_tiles<true, SRC, false>(stream, p);
+                if (p.digest != nullptr) return launch_tiles<false, SRC, true>(stream, p);
+                return launch_tiles<false, SRC, false>(stream, p);
+            }
+        }
         if (accum) return launch_groups<true, SRC, false>(stream, p, di.sms);
         if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
             // object-heavy FRESH renders (hundreds of objects per plane: instruction-issue bound, not store bound): the

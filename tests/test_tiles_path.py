@@ -1,0 +1,141 @@
+"""GPU: the object-heavy renderer (csrc/dh_tiles_kernel.cuh, selected for T >= 256 padded slots and k >= 0) against the
+oracle and against the staged renderer on THE SAME objects: padding the slot arrays from T = 255 to T >= 256 changes
+the kernel, never the result. Shapes chosen to hit every edge of the tile geometry: H not a multiple of the 8-row
+strip, W not a multiple of the 64-column tile, W > 512 (more tiles than warps: two rounds), T > 1024 (several list
+passes), empty strips / samples (bulk zero path), objects centred off the map, negative and oversize radii, both
+sizes dtypes, both modes, K1 fused (float boxes) with the fused digest, skip counters counted once.
+"""
+import numpy as np
+import pytest
+import torch
+
+import _cabi
+import workloads
+
+pytestmark = pytest.mark.gpu
+
+
+def _objects(seed, B, n_max, C, H, W, r_hi, empty_every=0):
+    rng = np.random.default_rng(seed)
+    sizes = rng.integers(0, n_max + 1, size=B)
+    if empty_every:
+        sizes[::empty_every] = 0
+    sizes[-1] = n_max
+    centers = np.stack([rng.integers(-r_hi, W + r_hi, (B, n_max)), rng.integers(-r_hi, H + r_hi, (B, n_max))], 2).astype(np.int32)
+    radii = rng.integers(-1, r_hi + 1, (B, n_max)).astype(np.int32)  # -1: draws nothing (reference: empty loops)
+    labels = rng.integers(0, C, (B, n_max)).astype(np.int32)
+    return centers, radii, labels, sizes.astype(np.int64)
+
+
+def _pad(a, T, fill):
+    """[B, n, ...] -> [B, T, ...]; padded slots hold a drawable decoy that must never be drawn (t >= size)."""
+    out = np.full((a.shape[0], T) + a.shape[2:], fill, a.dtype)
+    out[:, :a.shape[1]] = a
+    return out
+
+
+CASES = [
+    # B, n_max, C, H,  W,    r_hi, T_small, T_big, sizes dtype
+    (3, 255, 4, 70, 200, 40, 255, 256, torch.int64),   # H % 8 = 6, W % 64 = 8: partial strip and partial tile
+    (2, 200, 1, 19, 1024, 90, 200, 300, torch.int32),  # 16 tiles per strip: two rounds; objects wider than a tile
+    (2, 255, 2, 64, 128, 12, 255, 2500, torch.int64),  # small objects, hugely padded T: three list passes
+    (5, 120, 3, 33, 64, 70, 120, 512, torch.int64),    # objects larger than the map; one tile per strip
+    (4, 250, 2, 8, 512, 5, 250, 256, torch.int32),     # a single strip per plane
+]
+
+
+@pytest.mark.parametrize("B,n_max,C,H,W,r_hi,T_small,T_big,sdtype", CASES)
+def test_tile_renderer_equals_staged_renderer_and_oracle(cabi, cuda_dev, oracle, B, n_max, C, H, W, r_hi, T_small, T_big,
+                                                         sdtype):
+    centers, radii, labels, sizes = _objects(1000 + H + W, B, n_max, C, H, W, r_hi, empty_every=3)
+    dev = cuda_dev
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    sz = d(sizes).to(sdtype)
+    want = np.zeros((B, C, H, W), np.float32)
+    oracle.draw_batched(want, centers, radii, sizes, 6.0, 0.8, labels)
+    want_t = torch.from_numpy(want).to(dev)
+    rng = np.random.default_rng(5)
+    prefill = torch.from_numpy(rng.uniform(-0.5, 0.9, (B, C, H, W)).astype(np.float32)).to(dev)
+    res = {}
+    for T in (T_small, T_big):
+        assert (T >= 256) == (T == T_big)
+        ci, ri, lab = d(_pad(centers, T, 2)), d(_pad(radii, T, 1)), d(_pad(labels, T, 0))
+        fresh = _cabi.draw_batched(cabi, torch.full((B, C, H, W), 3.0, device=dev), ci, ri, sz, lab, 6.0, 0.8,
+                                   mode=_cabi.DH_MODE_FRESH)
+        acc0 = _cabi.draw_batched(cabi, torch.zeros((B, C, H, W), device=dev), ci, ri, sz, lab, 6.0, 0.8)
+        accp = _cabi.draw_batched(cabi, prefill.clone(), ci, ri, sz, lab, 6.0, 0.8)
+        one = _cabi.draw_batched(cabi, torch.full((B, H, W), 3.0, device=dev), ci, ri, sz, None, 6.0, 0.8,
+                                 mode=_cabi.DH_MODE_FRESH)
+        torch.cuda.synchronize()
+        assert torch.equal(fresh, acc0), f"T={T}: FRESH vs ACCUMULATE into zeros"
+        assert torch.equal(fresh > 0, want_t > 0), f"T={T}: touched mask"
+        assert float((fresh - want_t).abs().max()) <= 1e-6, f"T={T}"
+        res[T] = (fresh, accp, one)
+    for a, b, what in zip(res[T_small], res[T_big], ("fresh", "accumulate into a prefilled map", "one plane per sample")):
+        assert torch.equal(a, b), f"{what}: staged renderer (T={T_small}) != tile renderer (T={T_big})"
+    # accumulate into a prefilled map (negative values included) == elementwise reference blend of cuh:30
+    fresh, accp, one = res[T_big]
+    touched = want_t > 0
+    # where nothing was drawn the map is untouched; where something was drawn: keep old iff old >= v
+    # (pixels drawn with a value that underflowed to 0 are not in `touched`; they follow the same rule: max(old, 0))
+    blend = torch.where(prefill >= fresh, prefill, fresh)
+    assert torch.equal(accp[touched], blend[touched])
+    assert torch.equal(accp[~touched & (prefill >= 0)], prefill[~touched & (prefill >= 0)])
+    want1 = np.zeros((B, H, W), np.float32)
+    oracle.draw_batched(want1, centers, radii, sizes, 6.0, 0.8, None)
+    w1 = torch.from_numpy(want1).to(dev)
+    assert torch.equal(one > 0, w1 > 0) and float((one - w1).abs().max()) <= 1e-6
+
+
+def test_tile_renderer_cfg4_boxes_digest_and_status(cabi, cuda_dev, oracle):
+    """BASELINE cfg4 (2 samples of it): K1 fused, fused digest == dh_checksum of the output == oracle values; negative k
+    (served by the staged renderer) and k = 0 on the same inputs."""
+    dev = cuda_dev
+    w = workloads.make("cfg4", B=2)
+    c = w.cfg
+    cf, bf = torch.from_numpy(w.centers_f).to(dev), torch.from_numpy(w.bboxes_f).to(dev)
+    sizes, labels = torch.from_numpy(w.sizes).to(dev), torch.from_numpy(w.labels).to(dev)
+    shape = (w.B, c.C, c.H, c.W)
+    oci, ori = oracle.radius_center(w.centers_f, w.bboxes_f, c.osf)
+    for k in (1.0, 0.0, -0.7):
+        want = np.zeros(shape, np.float32)
+        oracle.draw_batched(want, oci, ori, w.sizes, 6.0, k, w.labels)
+        want_t = torch.from_numpy(want).to(dev)
+        heat = torch.full(shape, 5.0, device=dev)
+        dg = _cabi.draw_from_boxes_digest(cabi, heat, cf, bf, float(c.osf), sizes, labels, 6.0, k)
+        plain = _cabi.draw_from_boxes(cabi, torch.full(shape, 5.0, device=dev), cf, bf, float(c.osf), sizes, labels, 6.0, k)
+        acc = _cabi.draw_batched(cabi, torch.zeros(shape, device=dev), torch.from_numpy(oci).to(dev),
+                                 torch.from_numpy(ori).to(dev), sizes, labels, 6.0, k)
+        torch.cuda.synchronize()
+        assert torch.equal(heat, plain) and torch.equal(heat, acc), f"k={k}"
+        assert torch.equal(dg, _cabi.checksum(cabi, heat)), f"k={k}"
+        assert torch.equal(heat > 0, want_t > 0), f"k={k}"
+        assert float((heat - want_t).abs().max()) <= 1e-6, f"k={k}"
+
+
+@pytest.mark.parametrize("W", [96, 640])
+def test_tile_renderer_counts_skips_once(cabi, cuda_dev, W):
+    """Oversize radii and bad labels are counted once per object, whatever the number of strips, passes and rounds."""
+    dev = cuda_dev
+    B, T, C, H = 2, 1300, 3, 40
+    big = 4194304 + 9
+    centers = torch.full((B, T, 2), 10, dtype=torch.int32)
+    radii = torch.full((B, T), 1, dtype=torch.int32)
+    labels = (torch.arange(T, dtype=torch.int32) % C).repeat(B, 1)
+    sizes = torch.tensor([T, 1100], dtype=torch.int64)
+    for t in (0, 5, 1024, 1299):
+        radii[0, t] = big
+    radii[1, 1030] = big
+    radii[1, 1200] = big  # padded slot of sample 1: not counted
+    labels[0, 7] = -1
+    labels[1, 1050] = C
+    labels[1, 1250] = C + 3  # padded
+    centers, radii, labels, sizes = (t.to(dev) for t in (centers, radii, labels, sizes))
+    for mode in (_cabi.DH_MODE_FRESH, _cabi.DH_MODE_ACCUMULATE):
+        status = torch.zeros(4, dtype=torch.int32, device=dev)
+        heat = torch.zeros((B, C, H, W), device=dev)
+        _cabi.draw_batched(cabi, heat, centers, radii, sizes, labels, mode=mode, status=status)
+        torch.cuda.synchronize()
+        s = status.cpu().numpy().view(np.uint32)
+        assert int(s[0]) == 2 and int(s[2]) == 5, f"mode {mode}: {s}"
+        assert float(heat.max()) == 1.0 and int((heat > 0).sum()) == 9 * B * C
