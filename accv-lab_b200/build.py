@@ -42,14 +42,38 @@ def cuda_sources():
     return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
 
 
+def _includes(src):
+    """Quoted includes of a source file (csrc headers + the public header): its rebuild dependencies."""
+    import re
+
+    out = [src]
+    for name in re.findall(r'^\s*#\s*include\s+"([^"]+)"', open(src).read(), flags=re.M):
+        for d in (CSRC, INCLUDE):
+            q = os.path.join(d, name)
+            if os.path.exists(q):
+                out.append(q)
+    return out
+
+
 def build_cuda_lib(force=False, verbose_ptxas=False):
+    """One object per .cu (compiled in parallel, rebuilt only when the file or a header it includes changed), then one
+    link. Objects live in accv-lab_b200/_obj/ (git- and gpurun-ignored)."""
+    from concurrent.futures import ThreadPoolExecutor
+
     srcs = cuda_sources()
-    deps = srcs + [os.path.join(INCLUDE, "dh_b200.h")] + sorted(
-        os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh"))  # headers the .cu files include
-    if force or not _fresh(LIB_PATH, deps):
-        cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose_ptxas else []) + ["-shared", f"-I{INCLUDE}"] + srcs + [
-            "-o", LIB_PATH, "-lcudart"]
-        _run(cmd)
+    objdir = os.path.join(HERE, "_obj")
+    os.makedirs(objdir, exist_ok=True)
+    objs, todo = [], []
+    for s in srcs:
+        o = os.path.join(objdir, os.path.basename(s) + ".o")
+        objs.append(o)
+        if force or not _fresh(o, _includes(s)):
+            todo.append(["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose_ptxas else []) + [f"-I{INCLUDE}", "-c", s, "-o", o])
+    if todo:
+        with ThreadPoolExecutor(max_workers=min(len(todo), os.cpu_count() or 1)) as ex:
+            list(ex.map(_run, todo))
+    if todo or not _fresh(LIB_PATH, objs):
+        _run(["nvcc"] + NVCC_FLAGS + ["-shared"] + objs + ["-o", LIB_PATH, "-lcudart"])
     return LIB_PATH
 
 
