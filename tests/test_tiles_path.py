@@ -139,3 +139,50 @@ def test_tile_renderer_counts_skips_once(cabi, cuda_dev, W):
         s = status.cpu().numpy().view(np.uint32)
         assert int(s[0]) == 2 and int(s[2]) == 5, f"mode {mode}: {s}"
         assert float(heat.max()) == 1.0 and int((heat > 0).sum()) == 9 * B * C
+
+
+def _bits(t):
+    return t.contiguous().view(torch.int32)
+
+
+@pytest.mark.parametrize("factor,odd_slots", [
+    (6.0, ()),                  # every object plain: arithmetic sweep only (odd and even hit counts per tile)
+    (6.0, (3, 77)),             # r > 2896 in the first list pass: predicated sweep from the start
+    (6.0, (1100, 1490)),        # ... only in the SECOND pass: the tile switches sweeps with accumulators in flight
+    (1e21, ()),                 # var underflows to 0, 1/var = inf: m = inf off centre, NaN at the centre (cuh:45)
+    (1e-21, ()),                # var = inf, 1/var = 0: m = 0 over the whole window
+    (3e16, ()),                 # 1/var ~ 1e31 > 1e30 but finite: m overflows for distant pixels only
+])
+def test_tile_renderer_unusual_objects_bit_equal_staged(cabi, cuda_dev, oracle, factor, odd_slots):
+    """The tile renderer's two sweeps (packed-fp32 arithmetic masking for plain objects, per-pixel predication for the
+    rest) against the staged renderer on the same T (the *_ws entry never selects the tile renderer): same bits, NaNs
+    included, FRESH and ACCUMULATE into a prefilled map; against the oracle where the values are ordinary."""
+    dev = cuda_dev
+    B, C, H, W, T = 2, 2, 44, 200, 1500
+    rng = np.random.default_rng(77)
+    centers = np.stack([rng.integers(-20, W + 20, (B, T)), rng.integers(-20, H + 20, (B, T))], 2).astype(np.int32)
+    radii = rng.integers(0, 31, (B, T)).astype(np.int32)
+    labels = rng.integers(0, C, (B, T)).astype(np.int32)
+    for i, t in enumerate(odd_slots):
+        radii[:, t] = (2897, 5000)[i % 2]
+        centers[:, t] = (W // 2 + 2900 * (i % 2), H // 2)  # 2897 covers the map; 5000 from 2900 px to the right too
+        labels[:, t] = i % C
+    sizes = np.array([T, 1499 if odd_slots else 1201], np.int64)
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    ci, ri, lab, sz = d(centers), d(radii), d(labels), d(sizes)
+    prefill = torch.from_numpy(rng.uniform(-0.5, 0.9, (B, C, H, W)).astype(np.float32)).to(dev)
+    out = {}
+    for ws in (False, True):
+        fresh = _cabi.draw_batched(cabi, torch.full((B, C, H, W), 3.0, device=dev), ci, ri, sz, lab, factor, 0.8,
+                                   mode=_cabi.DH_MODE_FRESH, ws=ws)
+        accp = _cabi.draw_batched(cabi, prefill.clone(), ci, ri, sz, lab, factor, 0.8, ws=ws)
+        torch.cuda.synchronize()
+        out[ws] = (fresh, accp)
+    assert torch.equal(_bits(out[False][0]), _bits(out[True][0])), "fresh: tile renderer != staged renderer"
+    assert torch.equal(_bits(out[False][1]), _bits(out[True][1])), "accumulate: tile renderer != staged renderer"
+    if factor == 6.0:
+        want = np.zeros((B, C, H, W), np.float32)
+        oracle.draw_batched(want, centers, radii, sizes, factor, 0.8, labels)
+        want_t = torch.from_numpy(want).to(dev)
+        assert torch.equal(out[False][0] > 0, want_t > 0)
+        assert float((out[False][0] - want_t).abs().max()) <= 1e-6
