@@ -251,18 +251,52 @@ __device__ __forceinline__ void sparse_rows(unsigned* __restrict__ buf, float* _
                 dx2[j] = __fmul_rn(fdx, fdx);
                 tx[j] = fabsf(fdx) <= fr[j] && x <= rx1;
             }
+            if constexpr (ACCUM) {
+                // The old pixels of BOTH rows are requested first, by the lanes that will blend only, so the two loads
+                // are in flight together and the arithmetic runs under them. (Written pixel by pixel — load, blend,
+                // store, next load — the second load waits for the first store: the compiler must assume they alias.)
+                bool th[2];
+                float g[2] = {0.0f, 0.0f};
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {  // row rr, row rr + 1
-                float acc = 0.0f;
-                bool touched = false;
+                for (int h = 0; h < 2; ++h) {
+                    th[h] = false;
 #pragma unroll
-                for (int j = 0; j < N; ++j) {
-                    const bool t = (h ? in1[j] : in0[j]) && tx[j];
-                    const float m = __fmul_rn(__fadd_rn(h ? fi1[j] : fi0[j], dx2[j]), ow[j]);
-                    acc = t ? (touched ? fminf(acc, m) : m) : acc;
-                    touched = touched || t;
+                    for (int j = 0; j < N; ++j) th[h] = th[h] || ((h ? in1[j] : in0[j]) && tx[j]);
                 }
-                if (touched) emit(rr + h, x, __fmul_rn(expf(kneg ? acc : -acc), k));  // = expf(-m) * k
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                    if (th[h]) g[h] = gdst[(long long)(rr + h) * W + x];
+                float v[2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float acc = 0.0f;
+                    bool touched = false;
+#pragma unroll
+                    for (int j = 0; j < N; ++j) {
+                        const bool t = (h ? in1[j] : in0[j]) && tx[j];
+                        const float m = __fmul_rn(__fadd_rn(h ? fi1[j] : fi0[j], dx2[j]), ow[j]);
+                        acc = t ? (touched ? fminf(acc, m) : m) : acc;
+                        touched = touched || t;
+                    }
+                    v[h] = __fmul_rn(expf(kneg ? acc : -acc), k);  // = expf(-m) * k
+                }
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                    if (th[h] && !(g[h] >= v[h])) gdst[(long long)(rr + h) * W + x] = v[h];  // cuh:30
+            } else {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {  // row rr, row rr + 1
+                    float acc = 0.0f;
+                    bool touched = false;
+#pragma unroll
+                    for (int j = 0; j < N; ++j) {
+                        const bool t = (h ? in1[j] : in0[j]) && tx[j];
+                        const float m = __fmul_rn(__fadd_rn(h ? fi1[j] : fi0[j], dx2[j]), ow[j]);
+                        acc = t ? (touched ? fminf(acc, m) : m) : acc;
+                        touched = touched || t;
+                    }
+                    if (touched) emit(rr + h, x, __fmul_rn(expf(kneg ? acc : -acc), k));  // = expf(-m) * k
+                }
             }
         }
     }
