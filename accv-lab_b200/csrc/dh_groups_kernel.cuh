@@ -792,9 +792,18 @@ __device__ unsigned long long* g_trace = nullptr;
 __device__ long long g_trace_units = 0;
 #endif
 
-template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32, bool LEAN = false>
+}  // namespace dh
+#include "dh_tiles_kernel.cuh"  // render_unit_dense: what a DENSE instantiation does with a unit that many objects land on
+namespace dh {
+
+// DENSE (selected by the host for T >= 256 padded slots and k >= 0, fp32 planes, RaggedBatch sources): the instantiation
+// also contains the register-tile renderer of dh_tiles_kernel.cuh, and each CTA decides PER UNIT, from the list it has
+// just built, which renderer the unit gets (see that file's header). Everything else is the plain kernel.
+template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32, bool LEAN = false, bool DENSE = false>
 __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM : DH_G_MINB) groups_kernel(const RenderParams p) {
     static_assert(!LEAN || (!ACCUM && OUT == OUT_F32), "the lean layout is a FRESH fp32 variant");
+    static_assert(!DENSE || (OUT == OUT_F32 && !LEAN && (SRC == SRC_BATCHED || SRC == SRC_BOXES)),
+                  "the per-unit dense renderer serves fp32 planes from the RaggedBatch sources");
     constexpr int ZB = ACCUM ? 0 : kGZeroBytes;    // bytes of the zero tile
     constexpr int NB = (ACCUM || LEAN) ? 1 : 2;    // staging buffers per warp
     constexpr int ES = (OUT == OUT_F32) ? 4 : 2;  // bytes per heatmap element
@@ -901,6 +910,23 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
             s_cnt2[par ^ 1u] = 0;
             s_mask2[par ^ 1u] = 0ull;
         }
+        bool dense_done = false;
+        if constexpr (DENSE) {
+            // Many objects on this unit (block-uniform test): register tiles. The list is rewritten in place into the
+            // float form the sweeps consume; the barrier that publishes it also tells whether every object is plain.
+            if (ucnt >= p.dense_min && stage >= kTQueueBytes) {
+                if constexpr (!ACCUM) {  // the copy engine may still be reading my staging buffer (an earlier unit's group)
+                    if (lane == 0) bulk_wait_read<0>();
+                    __syncwarp();
+                }
+                stage_clean = false;  // the queue lives in the staging buffer: all-zero again before the next staged group
+                render_unit_dense<ACCUM, SRC, DIGEST>(p, us, nscan, ucnt, uy0, uy1, W, p.k, reinterpret_cast<float*>(plane_b),
+                                                      p.digest_base + us.plane * plane_elems, s_unit,
+                                                      reinterpret_cast<unsigned short*>(ws.buf0), tid, lane, warp, dg);
+                dense_done = true;
+            }
+        }
+        if (!dense_done) {
         const bool small = ucnt <= 32;  // one list entry per lane, kept in registers for the whole unit
         ObjI mine;
         mine.x = mine.y = 0;
@@ -954,6 +980,7 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
             render_group<ACCUM, SRC, DIGEST, OUT>(p, ws, plane_b, plane_index0, y0, min(G, uy1 - y0), W, G, kneg, kk, lane, small,
                                                   mine, s_unit, ucnt, us, dg);
         }
+        }  // !dense_done
 #ifdef DH_TRACE_UNITS
         if (lane == 0 && g_trace && u < g_trace_units) {
             unsigned long long t;

@@ -84,6 +84,7 @@ struct RenderParams {
     // of their object count (0 = hand-out in index order)
     int perm_n;
     long long perm_base;
+    int dense_min;  // groups_kernel<..., DENSE>: units with at least this many list entries are rendered as register tiles
     const void* bin_list;  // int4 (x, y, r, bits(1/var)) per object, a plane's objects contiguous
     const void* bin_rec;   // int2 (first entry, count) per plane
 };
@@ -441,7 +442,6 @@ __global__ void __launch_bounds__(kThreads) render_kernel(const RenderParams p) 
 #include "dh_rows_kernel.cuh"
 #include "dh_groups_kernel.cuh"
 #include "dh_groups2_kernel.cuh"
-#include "dh_tiles_kernel.cuh"
 namespace dh {
 
 // ------------------------------------------------------------------------------------------------
@@ -683,8 +683,9 @@ static const int g_single_wave = DH_KNOB("DH_G_SINGLE_WAVE", 1);       // small 
 static const int g_heavy_per_slot = DH_KNOB("DH_G_HEAVY_PER_SLOT", 8); // units per resident CTA slot when T >= 256
 static const int g_lean = DH_KNOB("DH_G_LEAN", 1);                     // object-heavy FRESH renders: lean shared-memory layout
 static const int g_lean_t = DH_KNOB("DH_G_LEAN_T", 256);                // ... from this many padded targets per sample on
-static const int g_tiles = DH_KNOB("DH_G_TILES", 1);                   // object-heavy renders (k >= 0): register-tile renderer
+static const int g_tiles = DH_KNOB("DH_G_TILES", 1);                   // T >= g_tiles_t, k >= 0: the instantiation with the per-unit register-tile renderer
 static const int g_tiles_t = DH_KNOB("DH_G_TILES_T", 256);              // ... from this many padded targets per sample on
+static const int g_dense_min = DH_KNOB("DH_G_DENSE_MIN", 48);          // ... which a unit takes when its list holds at least this many objects
 static const int g_no_bin = DH_KNOB("DH_G_NOBIN", 0);                  // 1: ignore the workspace of the *_ws entries
 static const int g_lpt = DH_KNOB("DH_G_LPT", 10);                      // heaviest-first hand-out inside the last g_lpt / 2 waves (0 = off)
 static const int g_pdl = DH_KNOB("DH_G_PDL", 1);                       // programmatic dependent launch of the groups kernels
@@ -697,7 +698,8 @@ static const int g_tail_waves_x2 = DH_KNOB("DH_G_TAIL_WAVES_X2", 2);   // tail t
 // is not, so that every resident CTA slot still sees several units.
 // `es` = bytes per heatmap element (4, or 2 for the 16-bit planes: rows per group still follow the fp32 scratch).
 // Returns false when 16-bit planes cannot be cut into 16-byte aligned groups.
-static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4, bool accum = false, bool lean = false) {
+static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4, bool accum = false, bool lean = false,
+                             bool dense = false) {
     // rows per group: as many as a staging buffer holds while DH_G_MINB(_ACCUM) CTAs still fit the SM's shared memory
     const bool one = accum || lean;  // one staging buffer per warp, four CTAs per SM
     const long long smem_budget = (227ll * 1024) / (one ? DH_G_MINB_ACCUM : DH_G_MINB) - 1024 - kGPermSmem;  // 1 KB: the system's
@@ -733,7 +735,13 @@ static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4, bo
         const long long one_wave = (groups_y + upp - 1) / upp;
         if (one_wave <= cap && one_wave > gpu) gpu = one_wave;
     }
-    if (gpu < kGWarps) gpu = kGWarps;  // at least one group per warp, however small the problem
+    if (dense) {  // units of whole 8-row strips (the tile height of the per-unit dense renderer), at least one
+        long long rows = ((gpu * G + kTRows - 1) / kTRows) * kTRows;
+        if (rows < kTRows) rows = kTRows;
+        gpu = (rows + G - 1) / G;
+    } else if (gpu < kGWarps) {
+        gpu = kGWarps;  // at least one group per warp, however small the problem
+    }
     if (gpu > kGMaxGroups) gpu = kGMaxGroups;
     if (gpu > groups_y) gpu = groups_y;
     p.units_per_plane = (int)((groups_y + gpu - 1) / gpu);
@@ -783,20 +791,21 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 
-template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32, bool LEAN = false>
+template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32, bool LEAN = false, bool DENSE = false>
 static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     static std::atomic<bool> attr_set_dev[64];  // function attributes are per device: one process may drive several GPUs
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DH_ERR_NO_DEVICE;
     if (!attr_set_dev[dev].load(std::memory_order_acquire)) {
         const int cap = (int)groups_smem_bytes(kGStageCap, ACCUM, LEAN);  // widest map: fewer CTAs per SM then
-        cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST, OUT, LEAN>,
+        cudaError_t e = cudaFuncSetAttribute(groups_kernel<ACCUM, SRC, DIGEST, OUT, LEAN, DENSE>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
         if (e != cudaSuccess) return (int)e;
         attr_set_dev[dev].store(true, std::memory_order_release);
     }
     const long long max_ctas = (long long)sms * ((ACCUM || LEAN) ? DH_G_MINB_ACCUM : DH_G_MINB);
-    if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2, ACCUM, LEAN)) return DH_ERR_UNSUPPORTED_SHAPE;
+    if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2, ACCUM, LEAN, DENSE)) return DH_ERR_UNSUPPORTED_SHAPE;
+    p.dense_min = g_dense_min;
     if (p.total_units == 0) return DH_OK;
     // Flat grid, one CTA per unit: the block scheduler hands units out dynamically and in address order, which
     // balances SMs that see different effective store bandwidth; a static grid-stride loop runs at the pace of the
@@ -824,32 +833,8 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
             p.perm_base = B - p.perm_n;
         }
     }
-    const cudaError_t e = launch_pdl(groups_kernel<ACCUM, SRC, DIGEST, OUT, LEAN>, dim3((unsigned)g), dim3(kGThreads),
+    const cudaError_t e = launch_pdl(groups_kernel<ACCUM, SRC, DIGEST, OUT, LEAN, DENSE>, dim3((unsigned)g), dim3(kGThreads),
                                      groups_smem_bytes(p.stage_bytes, ACCUM, LEAN), stream, p);
-    g_launches.fetch_add(1, std::memory_order_relaxed);
-    return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
-}
-
-// Object-heavy renders (dh_tiles_kernel.cuh): one CTA per strip of kTRows rows, register tiles, flat grid + launch control.
-template <bool ACCUM, int SRC, bool DIGEST>
-static int launch_tiles(cudaStream_t stream, RenderParams& p) {
-    const int upp = (p.H + kTRows - 1) / kTRows;
-    p.band_cols = p.band_rows = kTRows;
-    p.bands_y = p.bands_per_plane = upp;
-    p.bands_x = 1;
-    p.units_per_plane = p.units_per_plane2 = upp;
-    p.bands_per_unit = p.bands_per_unit2 = 1;
-    p.tier1_planes = p.num_planes;
-    p.tier1_units = p.total_units = p.num_planes * upp;
-    p.perm_n = 0;
-    p.perm_base = 0;
-    p.stage_bytes = 0;
-    if (p.total_units == 0) return DH_OK;
-    long long g = p.total_units;
-    p.use_clc = !g_no_clc && g <= 0x7fffffffll;  // a clamped grid falls back to the static stride
-    if (g > 0x7fffffffll) g = 0x7fffffffll;
-    const cudaError_t e = launch_pdl(tiles_kernel<ACCUM, SRC, DIGEST>, dim3((unsigned)g), dim3(kGThreads),
-                                     tiles_smem_bytes(ACCUM), stream, p);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
@@ -926,9 +911,9 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode, long lo
             // object-heavy renders (hundreds of objects per plane: instruction-issue bound, not store bound): register
             // tiles. k < 0 stays with the staged renderer (its order-preserving encode covers that sign).
             if (g_tiles && p.T >= g_tiles_t && !(p.k < 0.0f)) {
-                if (accum) return launch_tiles<true, SRC, false>(stream, p);
-                if (p.digest != nullptr) return launch_tiles<false, SRC, true>(stream, p);
-                return launch_tiles<false, SRC, false>(stream, p);
+                if (accum) return launch_groups<true, SRC, false, OUT_F32, false, true>(stream, p, di.sms);
+                if (p.digest != nullptr) return launch_groups<false, SRC, true, OUT_F32, false, true>(stream, p, di.sms);
+                return launch_groups<false, SRC, false, OUT_F32, false, true>(stream, p, di.sms);
             }
         }
         if (accum) return launch_groups<true, SRC, false>(stream, p, di.sms);

@@ -1,54 +1,42 @@
-// dh_tiles_kernel.cuh — the OBJECT-HEAVY renderer: register tiles instead of staged rows.
-// Included by dh_kernels.cu after dh_groups_kernel.cuh (shares ObjI, unit_header, scan_slot, Digest, the CLC / mbarrier /
-// bulk-store wrappers).
+// dh_tiles_kernel.cuh — the OBJECT-HEAVY unit renderer: register tiles instead of staged rows.
+// Included by dh_groups_kernel.cuh right before groups_kernel (uses ObjI, Digest); device functions only.
 //
 // Same result as the reference's per-object max-blend (draw_heatmap_cuda_kernel.cuh:26-49, 76-109), same arithmetic per
-// pixel as groups_kernel (m = (dy^2 + dx^2) * (1/var) with explicit IEEE roundings, cuh:45; max_o k*expf(-m_o) ==
-// k*expf(-min_o m_o) for k >= 0), for planes on which HUNDREDS of objects overlap (BASELINE cfg4: 1024 objects of
-// radius 16-64 on a 512x512 plane, every pixel under ~29 of them). There the launch is bound by instruction issue, not
-// by stores (ncu, profiles/r02/ncu_groups_kernel_cfg4.txt: issue-active 84 %, DRAM 0.07 %), and groups_kernel spends
+// pixel as the staged renderer (m = (dy^2 + dx^2) * (1/var) with explicit IEEE roundings, cuh:45; max_o k*expf(-m_o) ==
+// k*expf(-min_o m_o) for k >= 0), for units on which DOZENS TO HUNDREDS of objects land (BASELINE cfg4: 1024 objects of
+// radius 16-64 on a 512x512 plane, every pixel under ~29 of them). There a launch is bound by instruction issue, not by
+// stores (ncu, profiles/r02/ncu_groups_kernel_cfg4.txt: issue-active 84 %, DRAM 0.07 %), and the staged renderer spends
 // ~30 warp instructions per 32 object-pixels: every object is swept into shared-memory staging rows with a
 // read-modify-write per pixel quad, two rows at a time, and every row of every object pays the row set-up again.
 //
-// Here a unit is a STRIP of kTRows = 8 whole rows of one plane, cut into tiles of 8 x 64 pixels, one tile per warp at a
-// time. A lane owns two columns of the tile (x, x + 32) and keeps the running minimum of m for its 16 pixels in
-// REGISTERS (as raw float bits: m >= 0, so unsigned order == float order; 0xFFFFFFFF = untouched). Per object and tile
-// what depends on the column (dx, dx^2, |dx| <= r) is computed once, what depends on the row (dy^2, |dy| <= r) once per
-// row for both columns: ~10 instructions per row of 64 pixels, ~96 per (object, tile) — about a third of what the
-// staged sweep issues. No shared-memory traffic in the sweep except one broadcast 16-byte load per (object, tile).
-// The strip's object list is built by the whole CTA exactly as in groups_kernel (scan of the sample's slots, K1 fused,
-// ballot + popc compaction), in passes of kTCap slots, so any T is served without an overflow path: the accumulators
-// simply persist over the passes. One expf per touched pixel at the end; FRESH writes every pixel of the tile (value or
-// zero) with coalesced 128-byte stores, ACCUMULATE read-max-writes the touched ones (cuh:30). A strip without any object
-// leaves as bulk stores of the zero tile.
-// Selected by the host for T >= 256 and k >= 0 (dh_kernels.cu launch_render); k < 0 keeps the staged renderer, whose
-// order-preserving encode covers that sign.
+// WHO DECIDES: the device, per unit. The host cannot see how many objects a sample really holds (the sizes live in
+// device memory; T is only the padded slot count — CenterPoint-style callers pad ~50 objects to 500 slots), so it only
+// selects the groups_kernel instantiation that CONTAINS this renderer (DENSE: T >= 256 and k >= 0); every CTA then looks
+// at the list it has just built for its unit and takes this path when the list is long (RenderParams::dense_min <=
+// entries <= kGCap), the staged / register paths of groups_kernel otherwise. (The first version was a kernel of its own
+// chosen by T alone: cfg4 fine, but the 8-GPU slice of cfg5 padded to T = 256 took 0.73 instead of 0.24 ms.)
 //
-// Two sweeps. sweep_tile (the first one written, kept as the exact path for unusual objects) predicates every pixel:
-// ~11 warp instructions per (object, row of 64 pixels). sweep_tile_fast serves "plain" objects — r <= kTExactR, so
-// dy^2 + dx^2 < 2^24 is an exact integer in fp32 however it is formed, and 0 < 1/var <= 1e30, so no in-window m
-// overflows — and replaces predication by arithmetic: a pixel outside the object's columns gets dx^2 = +inf, a row
-// outside its rows dy = +inf, hence m = +inf, which never beats a real value and doubles as "untouched". What is left
-// per (object, row) is FADD2 (dy, dy) + (1, 1), FFMA2 dy * dy + (dx0^2, dx1^2), FMUL2 by (w, w) — the packed fp32
-// instructions of sm_100, each component rounded as the scalar instruction would — and, objects taken two at a time,
-// one three-input FMNMX3 per pixel pair of objects: 4 instead of 11 issue slots. fma(dy, dy, dx^2) equals the
-// reference's (float)(i*i) + (float)(j*j) (cuh:45) bit for bit because every term is an exact integer below 2^24.
-// A pass whose list holds an object that is not plain (block-uniform flag set by the scan) switches the tile to the
-// predicated sweep for the rest of the unit; the accumulators' "untouched" code is converted once (+inf -> all ones).
+// A dense unit is cut into STRIPS of kTRows = 8 rows and tiles of 8 x 64 pixels, one tile per warp at a time. A lane owns
+// two columns of the tile (x, x + 32) and keeps the running minimum of m for its 16 pixels in REGISTERS. The unit list
+// is first rewritten in place into float form (TileEnt), which also tells whether every object is "plain".
+//
+// Two sweeps. sweep_tile (the exact path for unusual objects) predicates every pixel: ~11 warp instructions per (object,
+// row of 64 pixels), accumulators as raw bits of m (m >= 0, so unsigned order == float order; all ones = untouched).
+// sweep_tile_fast serves "plain" objects — r <= kTExactR, so dy^2 + dx^2 < 2^24 is an exact integer in fp32 however it
+// is formed, and 0 < 1/var <= 1e30, so no in-window m overflows — and replaces predication by arithmetic: a pixel
+// outside the object's columns gets dx^2 = +inf, a row outside its rows dy = +inf, hence m = +inf, which never beats a
+// real value and doubles as "untouched". What is left per (object, row) is FADD2 (dy, dy) + (1, 1), FFMA2 dy * dy +
+// (dx0^2, dx1^2), FMUL2 by (w, w) — the packed fp32 instructions of sm_100, each component rounded as the scalar
+// instruction would — and, objects taken two at a time, one three-input FMNMX3 per pixel and pair of objects: 4 instead
+// of 11 issue slots. fma(dy, dy, dx^2) equals the reference's (float)(i*i) + (float)(j*j) (cuh:45) bit for bit because
+// every term is an exact integer below 2^24. One expf per touched pixel at the end; FRESH writes every pixel of the tile
+// (value or zero) with coalesced 128-byte row segments, ACCUMULATE read-max-writes the touched ones (cuh:30).
 #pragma once
 
 namespace dh {
 
-#ifndef DH_T_ROWS
-#define DH_T_ROWS 8
-#endif
-#ifndef DH_T_MINB
-#define DH_T_MINB 4
-#endif
-constexpr int kTRows = DH_T_ROWS;  // rows of a strip / tile
+constexpr int kTRows = 8;     // rows of a strip / tile (12 and 16 measured: no gain, profiles/r02/tiles/geometry_ab.txt)
 constexpr int kTCols = 64;    // columns of a tile (two per lane)
-constexpr int kTCap = 1024;   // slots scanned, and list entries held, per pass
-constexpr int kTMinB = DH_T_MINB;  // resident CTAs per SM the register budget is cut for
 constexpr int kTExactR = 2896;  // 2 * 2896^2 < 2^24: squared distances of in-window pixels are exact fp32 integers
 constexpr unsigned kTNone = 0xffffffffu;      // untouched, predicated sweep (m >= 0: never a real value's bits)
 constexpr unsigned kTNoneFast = 0x7f800000u;  // untouched, arithmetic sweep (+inf)
@@ -74,35 +62,35 @@ __device__ __forceinline__ float fmin3(float a, float b, float c) {
     return d;
 }
 
-// A list entry of the strip: the object in the form both sweeps consume. All four are exact: |x| <= r + W < 2^24 and
-// |y0 - y| <= r + kTRows for every object that passed the cull (r <= DH_MAX_RADIUS = 2^22).
+// A list entry of a dense unit: the object in the form both sweeps consume. All four are exact: |x| <= r + W < 2^24 and
+// |y0 - y| <= r + rows of the unit for every object that passed the cull (r <= DH_MAX_RADIUS = 2^22).
 struct __align__(16) TileEnt {
     float fx;   // centre column
     float fr;   // radius
-    float fdy;  // first row of the strip - centre row
+    float fdy;  // first row of the UNIT - centre row
     float w;    // 1 / var
 };
-static_assert(sizeof(TileEnt) == 16, "one 128-bit shared-memory load per entry");
+static_assert(sizeof(TileEnt) == sizeof(ObjI), "the unit list is rewritten in place");
 
-__host__ __device__ constexpr size_t tiles_queue_bytes() { return (size_t)kGWarps * (kTCap + 2) * sizeof(unsigned short); }
-__host__ __device__ constexpr size_t tiles_smem_bytes(bool accum) {
-    return (size_t)(accum ? 0 : kGZeroBytes) + (size_t)kTCap * sizeof(TileEnt) + tiles_queue_bytes();
+constexpr int kTQueueBytes = (kGCap + 2) * (int)sizeof(unsigned short);  // per-warp hit queue (lives in the warp's staging buffer)
+
+// entry overlaps the strip whose first row is `dys` rows below the unit's first row, and the tile's columns [t0f, t1f)
+__device__ __forceinline__ bool tile_hit(const TileEnt& o, float dys, float t0f, float t1f) {
+    const float fdy = o.fdy + dys;
+    return (o.fx + o.fr >= t0f) && (o.fx - o.fr < t1f) && (fdy + (float)(kTRows - 1) >= -o.fr) && (fdy <= o.fr);
 }
 
-// All objects of `list[0, cnt)` that overlap the tile's columns [tx0, tx0 + 64) into the lane's 8 x 2 accumulators
-// (raw bits of m, kTNone = untouched): every pixel predicated, any object. Every list entry already overlaps the
-// strip's rows (unit cull) and the map's columns. Warp-collective.
-__device__ __forceinline__ void sweep_tile(const TileEnt* __restrict__ list, int cnt, int tx0, int lane,
+// All objects of `list[0, cnt)` that overlap the tile (rows: the strip `dys` rows into the unit; columns [tx0, tx0 + 64))
+// into the lane's 8 x 2 accumulators (raw bits of m, kTNone = untouched): every pixel predicated, any object.
+// Warp-collective.
+__device__ __forceinline__ void sweep_tile(const TileEnt* __restrict__ list, int cnt, int tx0, float dys, int lane,
                                            float (&acc)[kTRows][2]) {
     const float xlf = (float)(tx0 + lane);  // my first column
     const float t0f = (float)tx0, t1f = (float)(tx0 + kTCols);
     for (int base = 0; base < cnt; base += 32) {
         const int e = base + lane;
         bool hit = false;
-        if (e < cnt) {
-            const float2 xr = *reinterpret_cast<const float2*>(&list[e]);
-            hit = (xr.x + xr.y >= t0f) && (xr.x - xr.y < t1f);
-        }
+        if (e < cnt) hit = tile_hit(list[e], dys, t0f, t1f);
         unsigned bal = __ballot_sync(0xffffffffu, hit);
         while (bal) {
             const int src = __ffs(bal) - 1;
@@ -111,7 +99,7 @@ __device__ __forceinline__ void sweep_tile(const TileEnt* __restrict__ list, int
             const float fdx0 = xlf - o.fx, fdx1 = fdx0 + 32.0f;
             const float dx20 = __fmul_rn(fdx0, fdx0), dx21 = __fmul_rn(fdx1, fdx1);
             const bool in0 = fabsf(fdx0) <= o.fr, in1 = fabsf(fdx1) <= o.fr;
-            float fdy = o.fdy;
+            float fdy = o.fdy + dys;
 #pragma unroll
             for (int rr = 0; rr < kTRows; ++rr) {
                 const float fi = __fmul_rn(fdy, fdy);
@@ -133,16 +121,16 @@ struct TileObj {
     bool allrows;  // every row of the tile lies inside the object's rows (warp-uniform)
 };
 
-__device__ __forceinline__ TileObj tile_obj(const TileEnt& o, float xlf) {
+__device__ __forceinline__ TileObj tile_obj(const TileEnt& o, float xlf, float dys) {
     TileObj t;
     const float inf = __uint_as_float(kTNoneFast);
     const float fdx0 = xlf - o.fx, fdx1 = fdx0 + 32.0f;
     t.a0 = fabsf(fdx0) <= o.fr ? __fmul_rn(fdx0, fdx0) : inf;
     t.a1 = fabsf(fdx1) <= o.fr ? __fmul_rn(fdx1, fdx1) : inf;
-    t.fdy = o.fdy;
+    t.fdy = o.fdy + dys;
     t.w = o.w;
     t.fr = o.fr;
-    t.allrows = (o.fdy >= -o.fr) && (o.fdy + (float)(kTRows - 1) <= o.fr);
+    t.allrows = (t.fdy >= -o.fr) && (t.fdy + (float)(kTRows - 1) <= o.fr);
     return t;
 }
 
@@ -175,10 +163,10 @@ __device__ __forceinline__ void sweep_pair(const TileObj& A, const TileObj& B, f
 }
 
 // Same contract as sweep_tile for lists of plain objects only (tile_obj_plain); accumulators hold m as floats, +inf =
-// untouched. First the list entries that overlap the tile's columns are compacted into the warp's queue `q` (ballot +
-// popc prefix, 16-bit entry indices), then the queue is swept two objects at a time — no bit scanning and no carried
-// state between the objects; an odd queue ends with its last object twice (min is idempotent).
-__device__ __forceinline__ void sweep_tile_fast(const TileEnt* __restrict__ list, int cnt, int tx0, int lane,
+// untouched. First the list entries that overlap the tile are compacted into the warp's queue `q` (ballot + popc
+// prefix, 16-bit entry indices), then the queue is swept two objects at a time — no bit scanning and no carried state
+// between the objects; an odd queue ends with its last object twice (min is idempotent).
+__device__ __forceinline__ void sweep_tile_fast(const TileEnt* __restrict__ list, int cnt, int tx0, float dys, int lane,
                                                 unsigned short* __restrict__ q, float (&acc)[kTRows][2]) {
     const float xlf = (float)(tx0 + lane);
     const float t0f = (float)tx0, t1f = (float)(tx0 + kTCols);
@@ -186,10 +174,7 @@ __device__ __forceinline__ void sweep_tile_fast(const TileEnt* __restrict__ list
     for (int base = 0; base < cnt; base += 32) {
         const int e = base + lane;
         bool hit = false;
-        if (e < cnt) {
-            const float2 xr = *reinterpret_cast<const float2*>(&list[e]);
-            hit = (xr.x + xr.y >= t0f) && (xr.x - xr.y < t1f);
-        }
+        if (e < cnt) hit = tile_hit(list[e], dys, t0f, t1f);
         const unsigned bal = __ballot_sync(0xffffffffu, hit);
         if (hit) q[n + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)e;
         n += __popc(bal);
@@ -200,172 +185,132 @@ __device__ __forceinline__ void sweep_tile_fast(const TileEnt* __restrict__ list
     const unsigned* const q2 = reinterpret_cast<const unsigned*>(q);
     for (int i = 0; i < n; i += 2) {
         const unsigned pr = q2[i >> 1];  // broadcast
-        const TileObj A = tile_obj(list[pr & 0xffffu], xlf), B = tile_obj(list[pr >> 16], xlf);
+        const TileObj A = tile_obj(list[pr & 0xffffu], xlf, dys), B = tile_obj(list[pr >> 16], xlf, dys);
         if (A.allrows && B.allrows) sweep_pair<false>(A, B, acc);
         else sweep_pair<true>(A, B, acc);
     }
-    __syncwarp();  // the queue is rewritten by the next pass
+    __syncwarp();  // the queue is rewritten for the next tile
 }
 
-template <bool ACCUM, int SRC, bool DIGEST>
-__global__ void __launch_bounds__(kGThreads, kTMinB) tiles_kernel(const RenderParams p) {
-    static_assert(SRC == SRC_BATCHED || SRC == SRC_BOXES, "tiles_kernel serves the RaggedBatch sources");
-    static_assert(!(ACCUM && DIGEST), "the fused digest exists in FRESH mode only");
-    constexpr int ZB = ACCUM ? 0 : kGZeroBytes;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    float4* const zero_tile = reinterpret_cast<float4*>(smem_raw);
-    TileEnt* const s_list = reinterpret_cast<TileEnt*>(smem_raw + ZB);
-    unsigned short* const s_queue = reinterpret_cast<unsigned short*>(smem_raw + ZB + (size_t)kTCap * sizeof(TileEnt));
-    __shared__ int s_cnt2[2];                          // list size, double-buffered by pass parity (no reset barrier)
-    __shared__ int s_odd2[2];                          // the pass's list holds an object that is not tile_obj_plain
-    __shared__ __align__(16) uint4 s_clc;              // cluster-launch-control response
-    __shared__ __align__(8) unsigned long long s_bar;  // its mbarrier
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int W = p.W;
-    const float k = p.k;
-    const long long plane_elems = (long long)p.H * W;
-    const int tiles_x = (W + kTCols - 1) / kTCols;
-    for (int i = tid; i < ZB / 16; i += kGThreads) zero_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (tid == 0) {
-        mbar_init(&s_bar, 1);
-        s_cnt2[0] = s_cnt2[1] = 0;
-        s_odd2[0] = s_odd2[1] = 0;
+// K4 for one tile: one expf per touched pixel (cuh:45), then the blend. Rows ty0.. (below uy1), columns tx0 + lane (+32).
+template <bool ACCUM, bool DIGEST>
+__device__ __forceinline__ void finish_tile(const float (&acc)[kTRows][2], unsigned none, int tx0, int ty0, int uy1, int W,
+                                            float k, float* __restrict__ plane_f, long long index0, int lane, Digest& dg) {
+    const int xl = tx0 + lane;
+#pragma unroll
+    for (int rr = 0; rr < kTRows; ++rr) {
+        const int y = ty0 + rr;
+        if (y < uy1) {
+            float* const row = plane_f + (long long)y * W;
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const int x = xl + 32 * c;
+                if (x < W) {
+                    const unsigned t = __float_as_uint(acc[rr][c]);
+                    if constexpr (ACCUM) {
+                        if (t != none) {
+                            const float v = __fmul_rn(expf(-__uint_as_float(t)), k);
+                            const float g = row[x];
+                            if (!(g >= v)) row[x] = v;  // cuh:30: keep old iff old >= v
+                        }
+                    } else {
+                        float f = 0.0f;
+                        if (t != none) {
+                            const float v = __fmul_rn(expf(-__uint_as_float(t)), k);
+                            f = (0.0f >= v) ? 0.0f : v;  // max-blend into the fused zero-init
+                            if constexpr (DIGEST) dg.add(f, index0 + (long long)y * W + x);
+                        }
+                        row[x] = f;
+                    }
+                }
+            }
+        }
     }
-    fence_proxy_async();
-    pdl_wait();  // nothing global before this point (see groups_kernel)
-    pdl_launch_dependents();
+}
 
-    long long u = blockIdx.x;
-    unsigned par = 0, clc_phase = 0;
-    Digest dg;
-    for (;;) {
-        UnitSrc us;
-        int uy0, uy1;
-        bool count_skips;
-        const int nscan = unit_header<SRC>(p, u, kTRows, us, uy0, uy1, count_skips, nullptr);
-        float* const plane_f = p.heat + us.plane * plane_elems;
-        const long long index0 = p.digest_base + us.plane * plane_elems;
-        bool asked = false;
-        for (int t0 = 0; t0 < tiles_x; t0 += kGWarps) {  // one tile per warp and round (one round for W <= 512)
-            const int tile = t0 + warp;
-            const int tx0 = tile * kTCols;
+// One dense unit: rows [uy0, uy1) of the plane at `plane_f`, strip by strip, every warp of the CTA (block-collective).
+// `ucnt` objects landed on the unit. If they fit the unit list (ucnt <= kGCap) the list is rewritten in place into the
+// float form (fdy relative to uy0) — the barrier that publishes it also tells whether every object is plain — and every
+// tile sweeps it. If not, the sample's slots are scanned again per strip in passes of kGCap slots against the strip's
+// rows (a pass cannot overflow the list) and the accumulators of a tile persist over the passes; a pass that holds an
+// object that is not plain switches the tile to the predicated sweep for its remaining passes — no real value is +inf
+// up to then, so the "untouched" code is converted once. `q`: this warp's hit queue (kTQueueBytes).
+template <bool ACCUM, int SRC, bool DIGEST>
+__device__ __forceinline__ void render_unit_dense(const RenderParams& p, const UnitSrc& us, int nscan, int ucnt, int uy0,
+                                                  int uy1, int W, float k, float* __restrict__ plane_f, long long index0,
+                                                  ObjI* s_unit, unsigned short* __restrict__ q, int tid, int lane, int warp,
+                                                  Digest& dg) {
+    __shared__ int s_dcnt[2], s_dodd[2];  // pass list size / "not plain" flag, double-buffered by pass parity
+    TileEnt* const s_list = reinterpret_cast<TileEnt*>(s_unit);
+    const int tiles_x = (W + kTCols - 1) / kTCols;
+    const bool prebuilt = ucnt <= kGCap;  // block-uniform
+    bool slow0 = false;
+    if (prebuilt) {
+        bool odd = false;
+        for (int e = tid; e < ucnt; e += kGThreads) {
+            const ObjI o = s_unit[e];
+            odd = odd || !tile_obj_plain(o);
+            s_list[e] = TileEnt{(float)o.x, (float)o.r, (float)(uy0 - o.y), o.w};
+        }
+        slow0 = __syncthreads_or(odd) != 0;
+    } else if (tid == 0) {
+        s_dcnt[0] = s_dcnt[1] = s_dodd[0] = s_dodd[1] = 0;  // published by the first pass's first barrier
+    }
+    const int npass = prebuilt ? 1 : (nscan + kGCap - 1) / kGCap;
+    unsigned par = 0;
+    for (int ty0 = uy0; ty0 < uy1; ty0 += kTRows) {
+        const int ty1 = min(ty0 + kTRows, uy1);
+        const float dys = prebuilt ? (float)(ty0 - uy0) : 0.0f;  // pass lists are built relative to the strip
+        for (int t0 = 0; t0 < tiles_x; t0 += kGWarps) {
+            const int tile = t0 + warp, tx0 = tile * kTCols;
+            bool slow = slow0;  // same value in every thread
             float acc[kTRows][2];  // min m per pixel: floats while every object was plain, raw bits after that
 #pragma unroll
-            for (int rr = 0; rr < kTRows; ++rr) acc[rr][0] = acc[rr][1] = __uint_as_float(kTNoneFast);
-            bool any = false;   // the strip holds at least one object (same value in every thread)
-            bool slow = false;  // a pass held an object that is not plain: predicated sweep from then on (same in every thread)
-            for (int s0 = 0; s0 < nscan || s0 == 0; s0 += kTCap, par ^= 1u) {
-                __syncthreads();  // everybody is done with the previous pass's list
-                if (!asked) {
-                    asked = true;
-                    if (tid == 0 && p.use_clc) {  // ask for the next unit now; the answer lands while this one is rendered
-                        fence_proxy_async();
-                        mbar_expect_tx(&s_bar, 16);
-                        clc_try_cancel(&s_clc, &s_bar);
-                    }
-                }
-                int& s_cnt = s_cnt2[par];
-                const int send = min(nscan, s0 + kTCap);
-                for (int base = s0; base < send; base += kGThreads) {
-                    ObjI o;
-                    const int t = base + tid;
-                    const bool pred = (t < send) && scan_slot<SRC>(p, us, t, nscan, uy0, uy1, W, count_skips && t0 == 0, o);
-                    const unsigned bal = __ballot_sync(0xffffffffu, pred);
-                    if (bal) {
-                        int pos = 0;
-                        if (lane == 0) pos = atomicAdd(&s_cnt, __popc(bal));
-                        pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(bal & ((1u << lane) - 1u));
-                        if (pred) {  // pos < kTCap: a pass scans at most kTCap slots
-                            s_list[pos] = TileEnt{(float)o.x, (float)o.r, (float)(uy0 - o.y), o.w};
-                            if (!tile_obj_plain(o)) s_odd2[par] = 1;
-                        }
-                    }
-                }
-                __syncthreads();
-                const int cnt = s_cnt;
-                const bool odd = s_odd2[par] != 0;
-                if (tid == 0) s_cnt2[par ^ 1u] = s_odd2[par ^ 1u] = 0;  // last read before this pass's first barrier
-                any |= cnt > 0;
-                if (odd && !slow) {  // no real value is +inf so far (plain objects): +inf means untouched
-                    slow = true;
-#pragma unroll
-                    for (int rr = 0; rr < kTRows; ++rr) {
-                        if (__float_as_uint(acc[rr][0]) == kTNoneFast) acc[rr][0] = __uint_as_float(kTNone);
-                        if (__float_as_uint(acc[rr][1]) == kTNoneFast) acc[rr][1] = __uint_as_float(kTNone);
-                    }
-                }
-                if (tile < tiles_x && cnt > 0) {
-                    if (slow) sweep_tile(s_list, cnt, tx0, lane, acc);
-                    else sweep_tile_fast(s_list, cnt, tx0, lane, s_queue + warp * (kTCap + 2), acc);
-                }
-            }
-            if constexpr (!ACCUM) {
-                if (!any) {  // nothing on the strip: it leaves from the zero tile, no per-pixel work (and no further round)
-                    if (tid == 0) {
-                        char* dst = reinterpret_cast<char*>(plane_f + (long long)uy0 * W);
-                        long long bytes = (long long)(uy1 - uy0) * W * 4;
-                        while (bytes > 0) {
-                            const unsigned c = (unsigned)(bytes < kGZeroBytes ? bytes : kGZeroBytes);
-                            bulk_store(dst, zero_tile, c);
-                            dst += c;
-                            bytes -= c;
-                        }
-                        bulk_commit();
-                    }
-                    break;
-                }
-            } else {
-                if (!any) break;
-            }
-            if (tile < tiles_x) {  // K4: one expf per touched pixel (cuh:45), then the blend
-                const int xl = tx0 + lane;
-                const unsigned none = slow ? kTNone : kTNoneFast;
-#pragma unroll
-                for (int rr = 0; rr < kTRows; ++rr) {
-                    const int y = uy0 + rr;
-                    if (y < uy1) {
-                        float* const row = plane_f + (long long)y * W;
-#pragma unroll
-                        for (int c = 0; c < 2; ++c) {
-                            const int x = xl + 32 * c;
-                            if (x < W) {
-                                const unsigned t = __float_as_uint(acc[rr][c]);
-                                if constexpr (ACCUM) {
-                                    if (t != none) {
-                                        const float v = __fmul_rn(expf(-__uint_as_float(t)), k);
-                                        const float g = row[x];
-                                        if (!(g >= v)) row[x] = v;  // cuh:30: keep old iff old >= v
-                                    }
-                                } else {
-                                    float f = 0.0f;
-                                    if (t != none) {
-                                        const float v = __fmul_rn(expf(-__uint_as_float(t)), k);
-                                        f = (0.0f >= v) ? 0.0f : v;  // max-blend into the fused zero-init
-                                        if constexpr (DIGEST) dg.add(f, index0 + (long long)y * W + x);
-                                    }
-                                    row[x] = f;
-                                }
+            for (int rr = 0; rr < kTRows; ++rr) acc[rr][0] = acc[rr][1] = __uint_as_float(slow ? kTNone : kTNoneFast);
+            for (int ps = 0; ps < npass; ++ps) {
+                int cnt = ucnt;
+                if (!prebuilt) {
+                    __syncthreads();  // everybody is done with the previous pass's list
+                    const int s0 = ps * kGCap, send = min(nscan, s0 + kGCap);
+                    for (int base = s0; base < send; base += kGThreads) {
+                        ObjI o;
+                        const int t = base + tid;
+                        const bool pred = (t < send) && scan_slot<SRC>(p, us, t, nscan, ty0, ty1, W, false, o);
+                        const unsigned bal = __ballot_sync(0xffffffffu, pred);
+                        if (bal) {
+                            int pos = 0;
+                            if (lane == 0) pos = atomicAdd(&s_dcnt[par], __popc(bal));
+                            pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(bal & ((1u << lane) - 1u));
+                            if (pred) {  // pos < kGCap: a pass scans at most kGCap slots
+                                s_list[pos] = TileEnt{(float)o.x, (float)o.r, (float)(ty0 - o.y), o.w};
+                                if (!tile_obj_plain(o)) s_dodd[par] = 1;
                             }
                         }
                     }
+                    __syncthreads();
+                    cnt = s_dcnt[par];
+                    const bool odd = s_dodd[par] != 0;
+                    if (tid == 0) s_dcnt[par ^ 1u] = s_dodd[par ^ 1u] = 0;  // last read before this pass's first barrier
+                    par ^= 1u;
+                    if (odd && !slow) {
+                        slow = true;
+#pragma unroll
+                        for (int rr = 0; rr < kTRows; ++rr) {
+                            if (__float_as_uint(acc[rr][0]) == kTNoneFast) acc[rr][0] = __uint_as_float(kTNone);
+                            if (__float_as_uint(acc[rr][1]) == kTNoneFast) acc[rr][1] = __uint_as_float(kTNone);
+                        }
+                    }
+                }
+                if (tile < tiles_x && cnt > 0) {
+                    if (slow) sweep_tile(s_list, cnt, tx0, dys, lane, acc);
+                    else sweep_tile_fast(s_list, cnt, tx0, dys, lane, q, acc);
                 }
             }
-        }
-        // next unit: the one the block scheduler hands over (cluster launch control), else the static stride
-        if (p.use_clc) {
-            mbar_wait(&s_bar, clc_phase);
-            clc_phase ^= 1u;
-            unsigned nx;
-            if (!clc_response(&s_clc, nx)) break;
-            u = nx;
-        } else {
-            u += gridDim.x;
-            if (u >= p.total_units) break;
+            if (tile < tiles_x)
+                finish_tile<ACCUM, DIGEST>(acc, slow ? kTNone : kTNoneFast, tx0, ty0, uy1, W, k, plane_f, index0, lane, dg);
         }
     }
-    if constexpr (!ACCUM) bulk_wait_read<0>();  // the zero tile must outlive every bulk read issued by this thread
-    if constexpr (DIGEST) digest_flush(dg, p.digest, tid, lane, warp);
+    if (!prebuilt) __syncthreads();  // the list storage goes back to the kernel
 }
 
 }  // namespace dh

@@ -1,5 +1,6 @@
-"""GPU: the object-heavy renderer (csrc/dh_tiles_kernel.cuh, selected for T >= 256 padded slots and k >= 0) against the
-oracle and against the staged renderer on THE SAME objects: padding the slot arrays from T = 255 to T >= 256 changes
+"""GPU: the object-heavy renderer (csrc/dh_tiles_kernel.cuh: register tiles; compiled into the groups_kernel instantiation
+the host selects for T >= 256 padded slots and k >= 0, taken PER UNIT when at least 48 objects land on the unit) against
+the oracle and against the staged renderer on THE SAME objects: padding the slot arrays from T = 255 to T >= 256 changes
 the kernel, never the result. Shapes chosen to hit every edge of the tile geometry: H not a multiple of the 8-row
 strip, W not a multiple of the 64-column tile, W > 512 (more tiles than warps: two rounds), T > 1024 (several list
 passes), empty strips / samples (bulk zero path), objects centred off the map, negative and oversize radii, both
@@ -41,6 +42,8 @@ CASES = [
     (2, 255, 2, 64, 128, 12, 255, 2500, torch.int64),  # small objects, hugely padded T: three list passes
     (5, 120, 3, 33, 64, 70, 120, 512, torch.int64),    # objects larger than the map; one tile per strip
     (4, 250, 2, 8, 512, 5, 250, 256, torch.int32),     # a single strip per plane
+    (3, 20, 2, 64, 128, 10, 20, 300, torch.int64),     # few objects in widely padded slots: every unit stays staged
+    (4, 140, 1, 96, 256, 30, 140, 400, torch.int32),   # dense and sparse units side by side (sample sizes 0..140)
 ]
 
 
@@ -145,20 +148,22 @@ def _bits(t):
     return t.contiguous().view(torch.int32)
 
 
+@pytest.mark.parametrize("T", [1500, 300])  # per unit: more objects than the shared list holds (slot passes) / fewer
 @pytest.mark.parametrize("factor,odd_slots", [
     (6.0, ()),                  # every object plain: arithmetic sweep only (odd and even hit counts per tile)
     (6.0, (3, 77)),             # r > 2896 in the first list pass: predicated sweep from the start
-    (6.0, (1100, 1490)),        # ... only in the SECOND pass: the tile switches sweeps with accumulators in flight
+    (6.0, (1100, 1490)),        # ... only in a LATER pass: the tile switches sweeps with accumulators in flight
     (1e21, ()),                 # var underflows to 0, 1/var = inf: m = inf off centre, NaN at the centre (cuh:45)
     (1e-21, ()),                # var = inf, 1/var = 0: m = 0 over the whole window
     (3e16, ()),                 # 1/var ~ 1e31 > 1e30 but finite: m overflows for distant pixels only
 ])
-def test_tile_renderer_unusual_objects_bit_equal_staged(cabi, cuda_dev, oracle, factor, odd_slots):
+def test_tile_renderer_unusual_objects_bit_equal_staged(cabi, cuda_dev, oracle, factor, odd_slots, T):
     """The tile renderer's two sweeps (packed-fp32 arithmetic masking for plain objects, per-pixel predication for the
     rest) against the staged renderer on the same T (the *_ws entry never selects the tile renderer): same bits, NaNs
     included, FRESH and ACCUMULATE into a prefilled map; against the oracle where the values are ordinary."""
     dev = cuda_dev
-    B, C, H, W, T = 2, 2, 44, 200, 1500
+    B, C, H, W = 2, 2, 44, 200
+    odd_slots = tuple(t * T // 1500 for t in odd_slots)
     rng = np.random.default_rng(77)
     centers = np.stack([rng.integers(-20, W + 20, (B, T)), rng.integers(-20, H + 20, (B, T))], 2).astype(np.int32)
     radii = rng.integers(0, 31, (B, T)).astype(np.int32)
@@ -167,7 +172,7 @@ def test_tile_renderer_unusual_objects_bit_equal_staged(cabi, cuda_dev, oracle, 
         radii[:, t] = (2897, 5000)[i % 2]
         centers[:, t] = (W // 2 + 2900 * (i % 2), H // 2)  # 2897 covers the map; 5000 from 2900 px to the right too
         labels[:, t] = i % C
-    sizes = np.array([T, 1499 if odd_slots else 1201], np.int64)
+    sizes = np.array([T, T - 1 if odd_slots else T * 4 // 5], np.int64)
     d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     ci, ri, lab, sz = d(centers), d(radii), d(labels), d(sizes)
     prefill = torch.from_numpy(rng.uniform(-0.5, 0.9, (B, C, H, W)).astype(np.float32)).to(dev)
