@@ -42,17 +42,20 @@ def cuda_sources():
     return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
 
 
-def _includes(src):
-    """Quoted includes of a source file (csrc headers + the public header): its rebuild dependencies."""
+def _includes(src, seen=None):
+    """Quoted includes of a source file, transitively (csrc headers + the public header): its rebuild dependencies."""
     import re
 
-    out = [src]
+    seen = [] if seen is None else seen
+    if src in seen:
+        return seen
+    seen.append(src)
     for name in re.findall(r'^\s*#\s*include\s+"([^"]+)"', open(src).read(), flags=re.M):
         for d in (CSRC, INCLUDE):
             q = os.path.join(d, name)
             if os.path.exists(q):
-                out.append(q)
-    return out
+                _includes(q, seen)
+    return seen
 
 
 def build_cuda_lib(force=False, verbose_ptxas=False):

@@ -84,7 +84,9 @@ struct RenderParams {
     // of their object count (0 = hand-out in index order)
     int perm_n;
     long long perm_base;
-    int dense_min;  // groups_kernel<..., DENSE>: units with at least this many list entries are rendered as register tiles
+    // groups_kernel<..., DENSE>: a unit is rendered as register tiles when at least dense_min objects land on it and the
+    // sum of d (d + 64) over them (d = window side) reaches dense_cost16 / 16 x the unit's pixel count
+    int dense_min, dense_cost16;
     const void* bin_list;  // int4 (x, y, r, bits(1/var)) per object, a plane's objects contiguous
     const void* bin_rec;   // int2 (first entry, count) per plane
 };
@@ -685,7 +687,9 @@ static const int g_lean = DH_KNOB("DH_G_LEAN", 1);                     // object
 static const int g_lean_t = DH_KNOB("DH_G_LEAN_T", 256);                // ... from this many padded targets per sample on
 static const int g_tiles = DH_KNOB("DH_G_TILES", 1);                   // T >= g_tiles_t, k >= 0: the instantiation with the per-unit register-tile renderer
 static const int g_tiles_t = DH_KNOB("DH_G_TILES_T", 256);              // ... from this many padded targets per sample on
-static const int g_dense_min = DH_KNOB("DH_G_DENSE_MIN", 48);          // ... which a unit takes when its list holds at least this many objects
+static const int g_dense_min = DH_KNOB("DH_G_DENSE_MIN", 8);           // ... which a unit takes when its list holds at least this many objects
+static const int g_dense_cost16 = DH_KNOB("DH_G_DENSE_COST16", 48);    // ... whose staged-path cost estimate reaches this / 16 x the unit's pixels (FRESH)
+static const int g_dense_cost16_accum = DH_KNOB("DH_G_DENSE_COST16_ACCUM", 112);  // ... the same for ACCUMULATE (measured breakevens: ~3 and ~7)
 static const int g_no_bin = DH_KNOB("DH_G_NOBIN", 0);                  // 1: ignore the workspace of the *_ws entries
 static const int g_lpt = DH_KNOB("DH_G_LPT", 10);                      // heaviest-first hand-out inside the last g_lpt / 2 waves (0 = off)
 static const int g_pdl = DH_KNOB("DH_G_PDL", 1);                       // programmatic dependent launch of the groups kernels
@@ -722,13 +726,17 @@ static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4, bo
     const long long total_groups = p.num_planes * groups_y;
     // units per resident CTA slot: 4, or 8 when samples can hold many objects (units are then compute-heavy and of
     // similar cost, so the last, partly filled wave is expensive: cfg4 ran 4.1 waves of 1024-object units)
-    const long long per_slot = (p.T >= 256) ? g_heavy_per_slot : 4;
+    // (DENSE instantiations render an object-heavy unit with register tiles, whose cost is the same for every strip, and
+    // pay one scan of the sample's slots per unit: they take the ordinary plan — cfg4: one wave of 40-row units 0.079 ms,
+    // 16-row units in 2.3 waves 0.081, 8-row units in 4.6 waves 0.086.)
+    const bool heavy = p.T >= 256 && !dense;
+    const long long per_slot = heavy ? g_heavy_per_slot : 4;
     long long gpu = total_groups / (per_slot * max_ctas);
     const long long cap = (g_unit_bytes + group_bytes - 1) / group_bytes;
     if (gpu > cap) gpu = cap;
     // Small problems (fewer planes than resident CTA slots, not object-heavy): ONE wave. Every unit pays ~3 us of pure
     // latency, so a second, partly filled wave of small units costs more than fewer, larger units in a single wave.
-    if (g_single_wave && p.T < 256 && p.num_planes <= max_ctas) {
+    if (g_single_wave && !heavy && p.num_planes <= max_ctas) {
         long long upp = max_ctas / p.num_planes;
         if (upp > groups_y / kGWarps) upp = groups_y / kGWarps;
         if (upp < 1) upp = 1;
@@ -806,6 +814,7 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     const long long max_ctas = (long long)sms * ((ACCUM || LEAN) ? DH_G_MINB_ACCUM : DH_G_MINB);
     if (!make_groups_plan(p, max_ctas, OUT == OUT_F32 ? 4 : 2, ACCUM, LEAN, DENSE)) return DH_ERR_UNSUPPORTED_SHAPE;
     p.dense_min = g_dense_min;
+    p.dense_cost16 = ACCUM ? g_dense_cost16_accum : g_dense_cost16;
     if (p.total_units == 0) return DH_OK;
     // Flat grid, one CTA per unit: the block scheduler hands units out dynamically and in address order, which
     // balances SMs that see different effective store bandwidth; a static grid-stride loop runs at the pace of the

@@ -163,18 +163,44 @@ __device__ __forceinline__ void sweep_pair(const TileObj& A, const TileObj& B, f
 }
 
 // Same contract as sweep_tile for lists of plain objects only (tile_obj_plain); accumulators hold m as floats, +inf =
-// untouched. First the list entries that overlap the tile are compacted into the warp's queue `q` (ballot + popc
-// prefix, 16-bit entry indices), then the queue is swept two objects at a time — no bit scanning and no carried state
-// between the objects; an odd queue ends with its last object twice (min is idempotent).
-__device__ __forceinline__ void sweep_tile_fast(const TileEnt* __restrict__ list, int cnt, int tx0, float dys, int lane,
-                                                unsigned short* __restrict__ q, float (&acc)[kTRows][2]) {
+// untouched. The tile is rows [strip, strip + nrows) x columns [tx0, min(tx0 + 64, W)).
+// 1. Dominance bound (one list entry per lane): among the objects whose window covers the WHOLE tile, the smallest
+//    m at the tile point farthest from the centre, M = min_B RN(D2far_B * w_B). Every pixel of the tile ends at m <= M.
+// 2. Queue: the entries that overlap the tile AND can still win somewhere on it, RN(D2near_A * w_A) <= M, compacted into
+//    the warp's queue `q` (ballot + popc prefix, 16-bit entry indices). An object dropped here has m > M >= the final m
+//    on every pixel of the tile, so dropping it changes no bit: D2near / D2far are exact integers (r <= kTExactR), a
+//    pixel's m is RN(D2 * w) with D2near <= D2 <= D2far, and rounding is monotone. On cfg4 (every pixel under ~29
+//    objects) 45 % of the (object, tile) pairs go this way.
+// 3. The queue is swept two objects at a time — no bit scanning and no carried state between the objects; an odd queue
+//    ends with its last object twice (min is idempotent).
+__device__ __forceinline__ void sweep_tile_fast(const TileEnt* __restrict__ list, int cnt, int tx0, float dys, int nrows,
+                                                int W, int lane, unsigned short* __restrict__ q, float (&acc)[kTRows][2]) {
     const float xlf = (float)(tx0 + lane);
-    const float t0f = (float)tx0, t1f = (float)(tx0 + kTCols);
+    const float x0t = (float)tx0, x1t = (float)min(tx0 + kTCols - 1, W - 1), nr1 = (float)(nrows - 1);
+    unsigned M = kTNoneFast;  // bits of +inf; m >= 0, so unsigned order == float order
+    for (int base = 0; base < cnt; base += 32) {
+        const int e = base + lane;
+        unsigned mb = kTNoneFast;
+        if (e < cnt) {
+            const TileEnt o = list[e];
+            const float fdy = o.fdy + dys;  // first row of the tile - centre row
+            const float dxf = fmaxf(fabsf(x0t - o.fx), fabsf(x1t - o.fx)), dyf = fmaxf(fabsf(fdy), fabsf(fdy + nr1));
+            if (dxf <= o.fr && dyf <= o.fr)  // the window covers the tile
+                mb = __float_as_uint(__fmul_rn(__fmaf_rn(dxf, dxf, __fmul_rn(dyf, dyf)), o.w));
+        }
+        M = min(M, __reduce_min_sync(0xffffffffu, mb));
+    }
     int n = 0;  // warp-uniform
     for (int base = 0; base < cnt; base += 32) {
         const int e = base + lane;
         bool hit = false;
-        if (e < cnt) hit = tile_hit(list[e], dys, t0f, t1f);
+        if (e < cnt) {
+            const TileEnt o = list[e];
+            const float fdy = o.fdy + dys;
+            const float dxn = fmaxf(0.0f, fmaxf(x0t - o.fx, o.fx - x1t)), dyn = fmaxf(0.0f, fmaxf(fdy, -(fdy + nr1)));
+            hit = dxn <= o.fr && dyn <= o.fr &&  // the window overlaps the tile ...
+                  __float_as_uint(__fmul_rn(__fmaf_rn(dxn, dxn, __fmul_rn(dyn, dyn)), o.w)) <= M;  // ... and can still win
+        }
         const unsigned bal = __ballot_sync(0xffffffffu, hit);
         if (hit) q[n + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)e;
         n += __popc(bal);
@@ -303,7 +329,7 @@ __device__ __forceinline__ void render_unit_dense(const RenderParams& p, const U
                 }
                 if (tile < tiles_x && cnt > 0) {
                     if (slow) sweep_tile(s_list, cnt, tx0, dys, lane, acc);
-                    else sweep_tile_fast(s_list, cnt, tx0, dys, lane, q, acc);
+                    else sweep_tile_fast(s_list, cnt, tx0, dys, ty1 - ty0, W, lane, q, acc);
                 }
             }
             if (tile < tiles_x)
