@@ -456,8 +456,9 @@ def side_configs_leg(ctx, peak):
             r.update({"bound": "instruction issue (not HBM)", "pixel_object_pairs": pairs,
                       "pairs_per_s": pairs / (ms * 1e-3), "issue_peak_warp_inst_per_s": issue_peak,
                       "pairs_per_issue_slot": pairs / (ms * 1e-3) / issue_peak,
-                      "note": "one warp instruction handles <= 32 pixels (128 in the 4-pixel-per-lane sweep); "
-                              "profiles/r02 holds the ncu instruction count"})
+                      "note": "register-tile renderer chosen per unit on the device: a packed-fp32 instruction handles 64 "
+                              "(pixel, object) pairs, ~4 issue slots per object-row of 64 pixels, and pairs of dominated "
+                              "objects are never evaluated; profiles/r02/tiles holds the ncu instruction count"})
         out[name] = r
         del heats
     return out
