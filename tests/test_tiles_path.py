@@ -191,3 +191,32 @@ def test_tile_renderer_unusual_objects_bit_equal_staged(cabi, cuda_dev, oracle, 
         want_t = torch.from_numpy(want).to(dev)
         assert torch.equal(out[False][0] > 0, want_t > 0)
         assert float((out[False][0] - want_t).abs().max()) <= 1e-6
+
+
+@pytest.mark.parametrize("H,W", [(37, 200), (8, 64), (50, 1000)])
+def test_tile_renderer_writes_nothing_outside_the_planes(cabi, cuda_dev, H, W):
+    """Guard bands around a densely hit output (partial last strip, partial last tile): the sentinels before and after
+    the planes stay intact in both modes and the planes equal the staged renderer's (no compute-sanitizer on this
+    pool: bounds are checked this way)."""
+    dev = cuda_dev
+    B, C, T, n = 2, 2, 320, 300
+    rng = np.random.default_rng(H * W)
+    centers = np.stack([rng.integers(-30, W + 30, (B, T)), rng.integers(-30, H + 30, (B, T))], 2).astype(np.int32)
+    radii = rng.integers(1, 40, (B, T)).astype(np.int32)
+    labels = rng.integers(0, C, (B, T)).astype(np.int32)
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    ci, ri, lab, sz = d(centers), d(radii), d(labels), d(np.array([n, n - 7], np.int64))
+    N, pad = B * C * H * W, 4096
+    for mode in (_cabi.DH_MODE_FRESH, _cabi.DH_MODE_ACCUMULATE):
+        out = {}
+        for ws in (False, True):
+            buf = torch.full((N + 2 * pad,), -7.5, device=dev)
+            heat = buf[pad:pad + N].view(B, C, H, W)
+            if mode == _cabi.DH_MODE_ACCUMULATE:
+                heat.zero_()
+            _cabi.draw_batched(cabi, heat, ci, ri, sz, lab, 6.0, 1.0, mode=mode, ws=ws)
+            torch.cuda.synchronize()
+            assert bool((buf[:pad] == -7.5).all()) and bool((buf[pad + N:] == -7.5).all()), f"mode {mode}, ws {ws}"
+            out[ws] = heat.clone()
+        assert torch.equal(_bits(out[False]), _bits(out[True])), f"mode {mode}"
+        assert float(out[False].min()) >= 0.0 and float(out[False].max()) == 1.0
