@@ -921,11 +921,10 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
         }
         bool dense_done = false;
         if constexpr (DENSE) {
-            // Many objects on this unit (block-uniform test): register tiles. The list is rewritten in place into the
-            // float form the sweeps consume; the barrier that publishes it also tells whether every object is plain.
-            // ... when the staged paths would spend more on its objects than the tile renderer spends on every pixel of
-            // the unit: sum of d (d + 64) over the objects against a multiple of the unit's area (profiles/r02/
-            // experiments.md section 13), and never for a handful of objects
+            // Register tiles for this unit (block-uniform test) when the staged paths would spend more on its objects than
+            // the tile renderer spends on every pixel of the unit: sum of d (d + 64) over the objects against a multiple
+            // of the unit's area (measured breakevens, profiles/r02/experiments.md section 13), and never for a handful
+            // of objects.
             const unsigned long long ucost = s_cost2[par];
             if (ucnt >= p.dense_min && ucost * 16ull >= (unsigned long long)p.dense_cost16 * (unsigned)((uy1 - uy0) * W) &&
                 stage >= kTQueueBytes) {

@@ -917,8 +917,11 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode, long lo
     }
     if (vec && p.W <= kGMaxW) {  // main path: row groups striped over warps, per-warp staging + bulk stores
         if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
-            // object-heavy renders (hundreds of objects per plane: instruction-issue bound, not store bound): register
-            // tiles. k < 0 stays with the staged renderer (its order-preserving encode covers that sign).
+            // Slot arrays wide enough to hold an object-heavy sample (hundreds of objects per plane: instruction-issue
+            // bound, not store bound): the instantiation that also contains the register-tile renderer. T is only the
+            // padded slot count — which renderer a unit gets is decided on the device, per unit, from the objects that
+            // land on it (dh_tiles_kernel.cuh). k < 0 stays with the staged renderer (its order-preserving encode covers
+            // that sign).
             if (g_tiles && p.T >= g_tiles_t && !(p.k < 0.0f)) {
                 if (accum) return launch_groups<true, SRC, false, OUT_F32, false, true>(stream, p, di.sms);
                 if (p.digest != nullptr) return launch_groups<false, SRC, true, OUT_F32, false, true>(stream, p, di.sms);
