@@ -523,7 +523,7 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
     }
 }
 
-// Unit -> plane, rows, source range. Returns the number of slots to scan (`nscan`, independent of any load).
+// Unit -> plane, rows, source range. Returns the number of slots to scan (`nscan`; independent of any load up to 256 slots).
 // Heaviest-first hand-out. Units are handed out in index order by the block scheduler, and a unit with many objects
 // takes 3-5 x an empty one, so a launch used to end with a long tail of half-idle SMs while the last heavy units
 // finished (unit timelines, profiles/r02/call4: the last ~8 us of 37 on cfg3, ~11 us of 211 on the 8-GPU slice of cfg5
@@ -649,7 +649,13 @@ __device__ __forceinline__ int unit_header(const RenderParams& p, long long u, i
         us.n = (int)ns;
         us.src_base = sample * p.T;
         count_skips = (ug == 0 && us.cls == 0);
-        return p.T;  // scan bound that does not depend on a load
+        // Scan bound. Up to one step of the block (T <= kGThreads) it is T itself, which does not depend on a load: every
+        // slot load is issued at once. Wider slot arrays are mostly padding in practice (500 slots for ~50 objects):
+        // there the bound follows the sample's size, rounded up to whole steps — slots from us.n on are never drawn and
+        // never counted (cuh:84) — at the price of waiting for the size before the first slot load.
+        if (p.T <= kGThreads) return p.T;
+        const int steps = (us.n + kGThreads - 1) / kGThreads;
+        return min(p.T, steps * kGThreads);
     } else if constexpr (SRC == SRC_CSR) {
         const int o0 = p.csr_off[us.plane], o1 = p.csr_off[us.plane + 1];
         us.src_base = o0;
