@@ -938,7 +938,13 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
                     if (lane == 0) bulk_wait_read<0>();
                     __syncwarp();
                 }
-                stage_clean = false;  // the queue lives in the staging buffer: all-zero again before the next staged group
+                // The queue lives in the staging buffer: all-zero again before the next staged group, which also makes the
+                // staging state start over — so it is dead across the tile sweep, whose 16 accumulators need the registers
+                // (kept alive, the allocator spilled it inside the per-group path of the sparse units).
+                stage_clean = false;
+                ws.cur = 0;
+                ws.c0x0 = ws.c1x0 = 1;
+                ws.c0x1 = ws.c1x1 = 0;
                 render_unit_dense<ACCUM, SRC, DIGEST>(p, us, nscan, ucnt, uy0, uy1, W, p.k, reinterpret_cast<float*>(plane_b),
                                                       p.digest_base + us.plane * plane_elems, s_unit,
                                                       reinterpret_cast<unsigned short*>(ws.buf0), tid, lane, warp, dg);
