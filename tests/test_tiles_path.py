@@ -220,3 +220,36 @@ def test_tile_renderer_writes_nothing_outside_the_planes(cabi, cuda_dev, H, W):
             out[ws] = heat.clone()
         assert torch.equal(_bits(out[False]), _bits(out[True])), f"mode {mode}"
         assert float(out[False].min()) >= 0.0 and float(out[False].max()) == 1.0
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_tile_renderer_random_shapes_bit_equal_staged(cabi, cuda_dev, seed):
+    """Differential run over random shapes, slot counts, object counts and radius ranges (dense units, sparse units,
+    lists beyond the shared capacity, radii beyond the exact-integer bound): the per-unit renderer choice never changes
+    a bit against the staged renderer of the *_ws entry, FRESH and ACCUMULATE into a prefilled map."""
+    dev = cuda_dev
+    rng = np.random.default_rng(9000 + seed)
+    for _ in range(5):
+        B, C = int(rng.integers(1, 5)), int(rng.integers(1, 4))
+        H, W = int(rng.integers(1, 140)), 4 * int(rng.integers(1, 257))
+        T = int(rng.integers(256, 1400))
+        r_hi = int(rng.choice([3, 12, 40, 120, 3500]))
+        sizes = rng.integers(0, T + 1, B).astype(np.int64)
+        sizes[rng.integers(0, B)] = T if rng.random() < 0.5 else int(rng.integers(0, 40))
+        centers = np.stack([rng.integers(-r_hi, W + r_hi, (B, T)), rng.integers(-r_hi, H + r_hi, (B, T))], 2).astype(np.int32)
+        radii = rng.integers(-1, r_hi + 1, (B, T)).astype(np.int32)
+        labels = rng.integers(0, C, (B, T)).astype(np.int32)
+        factor = float(rng.choice([6.0, 2.5, 11.0]))
+        d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        ci, ri, lab, sz = d(centers), d(radii), d(labels), d(sizes)
+        prefill = torch.from_numpy(rng.uniform(-0.5, 0.9, (B, C, H, W)).astype(np.float32)).to(dev)
+        res = []
+        for ws in (False, True):
+            fresh = _cabi.draw_batched(cabi, torch.full((B, C, H, W), 3.0, device=dev), ci, ri, sz, lab, factor, 0.9,
+                                       mode=_cabi.DH_MODE_FRESH, ws=ws)
+            accp = _cabi.draw_batched(cabi, prefill.clone(), ci, ri, sz, lab, factor, 0.9, ws=ws)
+            torch.cuda.synchronize()
+            res.append((fresh, accp))
+        what = f"B={B} C={C} H={H} W={W} T={T} r_hi={r_hi} sizes={sizes.tolist()} factor={factor}"
+        assert torch.equal(_bits(res[0][0]), _bits(res[1][0])), "fresh: " + what
+        assert torch.equal(_bits(res[0][1]), _bits(res[1][1])), "accumulate: " + what
