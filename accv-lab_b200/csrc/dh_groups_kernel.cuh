@@ -821,7 +821,7 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
     // this unit is rendered, so no barrier is needed between "cleared" and "scan" (round 1 had one: three per unit)
     __shared__ int s_cnt2[2];
     __shared__ unsigned long long s_mask2[2];
-    __shared__ unsigned long long s_cost2[2];  // DENSE: what the staged paths would roughly spend on the unit's objects
+    __shared__ unsigned s_cost2[2];  // DENSE: what the staged paths would roughly spend on the unit's objects (in units of 64)
     __shared__ __align__(16) uint4 s_clc;              // cluster-launch-control response
     __shared__ __align__(8) unsigned long long s_bar;  // its mbarrier
     __shared__ unsigned short s_perm[kGPermCap];       // heaviest-first hand-out order (see build_perm)
@@ -838,7 +838,7 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
             mbar_init(&s_bar, 1);
             s_cnt2[0] = s_cnt2[1] = 0;
             s_mask2[0] = s_mask2[1] = 0ull;
-            s_cost2[0] = s_cost2[1] = 0ull;
+            s_cost2[0] = s_cost2[1] = 0u;
         }
         fence_proxy_async();  // zero tile and mbarrier -> visible to the async proxy
     }
@@ -904,14 +904,15 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
                 const unsigned bhi = __reduce_or_sync(0xffffffffu, (unsigned)(bits >> 32));
                 int pos = 0;
                 unsigned cost = 0u;
-                if constexpr (DENSE) {  // d * (d + 64), d = window side (clamped): rows x (fixed + per-chunk) work of a staged object
+                if constexpr (DENSE) {  // d (d + 64) / 64, d = window side (clamped): rows x (fixed + per-chunk) work of a
+                    // staged object. 32-bit on purpose: a 64-bit shared-memory add is a compare-and-swap loop.
                     const unsigned d = pred ? (unsigned)min(2 * o.r + 1, 1024) : 0u;
-                    cost = __reduce_add_sync(0xffffffffu, d * (d + 64u));
+                    cost = __reduce_add_sync(0xffffffffu, (d * (d + 64u)) >> 6);
                 }
                 if (lane == 0) {
                     atomicOr(&s_mask, ((unsigned long long)bhi << 32) | blo);
                     pos = atomicAdd(&s_cnt, __popc(bal));
-                    if constexpr (DENSE) atomicAdd(&s_cost2[par], (unsigned long long)cost);
+                    if constexpr (DENSE) atomicAdd(&s_cost2[par], cost);
                 }
                 pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(bal & ((1u << lane) - 1u));
                 if (pred && pos < kGCap) s_unit[pos] = o;
@@ -923,7 +924,7 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
         if (tid == 0) {  // the other slot was last read before this unit's first barrier: clear it for the next unit
             s_cnt2[par ^ 1u] = 0;
             s_mask2[par ^ 1u] = 0ull;
-            s_cost2[par ^ 1u] = 0ull;
+            s_cost2[par ^ 1u] = 0u;
         }
         bool dense_done = false;
         if constexpr (DENSE) {
@@ -932,7 +933,7 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
             // of the unit's area (measured breakevens, profiles/r02/experiments.md section 13), and never for a handful
             // of objects.
             const unsigned long long ucost = s_cost2[par];
-            if (ucnt >= p.dense_min && ucost * 16ull >= (unsigned long long)p.dense_cost16 * (unsigned)((uy1 - uy0) * W) &&
+            if (ucnt >= p.dense_min && ucost * 1024ull >= (unsigned long long)p.dense_cost16 * (unsigned)((uy1 - uy0) * W) &&
                 stage >= kTQueueBytes) {
                 if constexpr (!ACCUM) {  // the copy engine may still be reading my staging buffer (an earlier unit's group)
                     if (lane == 0) bulk_wait_read<0>();
