@@ -432,7 +432,10 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
         unsigned bal = __ballot_sync(0xffffffffu, hit);
         const int nh = __popc(bal);
         if (nh <= kSparseMax) {  // register path: every hit object is evaluated per pixel, nothing goes through staging
-            if (nh > 0) {
+            if (nh == 1) {  // the common case: four shuffles, not eight
+                const ObjI O1[1] = {shfl_obj(mine, __ffs(bal) - 1)};
+                sparse_rows<ACCUM, DIGEST, OUT, 1>(obuf, gdst, gindex, y0, nrows, W, O1, kneg, k, lane, ux0, ux1, dg);
+            } else if (nh > 0) {
                 ObjI O[kSparseMax];
                 unsigned rest = bal;
 #pragma unroll
@@ -441,10 +444,7 @@ __device__ __forceinline__ void render_group(const RenderParams& p, WarpStage& w
                     rest &= rest - 1u;
                     O[j] = shfl_obj(mine, src);
                 }
-                if (nh == 1) {
-                    const ObjI O1[1] = {O[0]};
-                    sparse_rows<ACCUM, DIGEST, OUT, 1>(obuf, gdst, gindex, y0, nrows, W, O1, kneg, k, lane, ux0, ux1, dg);
-                } else if (nh == 2) {
+                if (nh == 2) {
                     const ObjI O2[2] = {O[0], O[1]};
                     sparse_rows<ACCUM, DIGEST, OUT, 2>(obuf, gdst, gindex, y0, nrows, W, O2, kneg, k, lane, ux0, ux1, dg);
                 } else {
