@@ -263,9 +263,9 @@ __device__ __forceinline__ void sparse_rows(unsigned* __restrict__ buf, float* _
 #pragma unroll
                     for (int j = 0; j < N; ++j) th[h] = th[h] || ((h ? in1[j] : in0[j]) && tx[j]);
                 }
-#pragma unroll
-                for (int h = 0; h < 2; ++h)
-                    if (th[h]) g[h] = gdst[(long long)(rr + h) * W + x];
+                float* const gp = gdst + (rr * W + x);  // one address per chunk (a group is at most 4 KB: 32-bit offsets)
+                if (th[0]) g[0] = gp[0];
+                if (th[1]) g[1] = gp[W];
                 float v[2];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
@@ -280,9 +280,8 @@ __device__ __forceinline__ void sparse_rows(unsigned* __restrict__ buf, float* _
                     }
                     v[h] = __fmul_rn(expf(kneg ? acc : -acc), k);  // = expf(-m) * k
                 }
-#pragma unroll
-                for (int h = 0; h < 2; ++h)
-                    if (th[h] && !(g[h] >= v[h])) gdst[(long long)(rr + h) * W + x] = v[h];  // cuh:30
+                if (th[0] && !(g[0] >= v[0])) gp[0] = v[0];  // cuh:30
+                if (th[1] && !(g[1] >= v[1])) gp[W] = v[1];
             } else {
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {  // row rr, row rr + 1
