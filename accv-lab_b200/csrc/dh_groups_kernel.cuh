@@ -207,18 +207,12 @@ __device__ __forceinline__ void sparse_rows(unsigned* __restrict__ buf, float* _
         ow[j] = kneg ? -O[j].w : O[j].w;
         fr[j] = (float)O[j].r;
     }
-    // one finished pixel of row `rr` (v = expf(-m) * k already formed)
-    auto emit = [&](int rr, int x, float v) {
-        if constexpr (ACCUM) {
-            float* const gp = gdst + (long long)rr * W + x;
-            const float g = *gp;
-            if (!(g >= v)) *gp = v;  // cuh:30
-        } else {
-            const float f = (0.0f >= v) ? 0.0f : v;
-            if constexpr (OUT == OUT_F32) buf[rr * W + x] = __float_as_uint(f);
-            else reinterpret_cast<unsigned short*>(buf)[rr * W + x] = cvt16<OUT>(f);  // `buf` = the 16-bit buffer
-            if constexpr (DIGEST) dg.add(f, gindex + (long long)rr * W + x);
-        }
+    // one finished FRESH pixel at offset `off` = row * W + x of the group (v = expf(-m) * k already formed)
+    auto emit = [&](int off, float v) {
+        const float f = (0.0f >= v) ? 0.0f : v;
+        if constexpr (OUT == OUT_F32) buf[off] = __float_as_uint(f);
+        else reinterpret_cast<unsigned short*>(buf)[off] = cvt16<OUT>(f);  // `buf` = the 16-bit buffer
+        if constexpr (DIGEST) dg.add(f, gindex + off);
     };
     for (int rr = 0; rr < nrows; rr += 2) {
         const bool has1 = rr + 1 < nrows;
@@ -283,6 +277,7 @@ __device__ __forceinline__ void sparse_rows(unsigned* __restrict__ buf, float* _
                 if (th[0] && !(g[0] >= v[0])) gp[0] = v[0];  // cuh:30
                 if (th[1] && !(g[1] >= v[1])) gp[W] = v[1];
             } else {
+                const int off = rr * W + x;  // one offset per chunk (a group is at most 4 KB)
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {  // row rr, row rr + 1
                     float acc = 0.0f;
@@ -294,7 +289,7 @@ __device__ __forceinline__ void sparse_rows(unsigned* __restrict__ buf, float* _
                         acc = t ? (touched ? fminf(acc, m) : m) : acc;
                         touched = touched || t;
                     }
-                    if (touched) emit(rr + h, x, __fmul_rn(expf(kneg ? acc : -acc), k));  // = expf(-m) * k
+                    if (touched) emit(h ? off + W : off, __fmul_rn(expf(kneg ? acc : -acc), k));  // = expf(-m) * k
                 }
             }
         }
