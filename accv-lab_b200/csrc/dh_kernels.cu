@@ -916,6 +916,14 @@ static int launch_render(cudaStream_t stream, RenderParams& p, int mode, long lo
         }
     }
     if (vec && p.W <= kGMaxW) {  // main path: row groups striped over warps, per-warp staging + bulk stores
+        if constexpr (SRC == SRC_CSR) {
+            // Flat entry: the host knows the average number of objects per plane. From 16 on, the instantiation that also
+            // contains the register-tile renderer (each unit still decides for itself, dh_tiles_kernel.cuh).
+            if (g_tiles && !(p.k < 0.0f) && p.num_objects >= 16 * p.num_planes) {
+                if (accum) return launch_groups<true, SRC, false, OUT_F32, false, true>(stream, p, di.sms);
+                return launch_groups<false, SRC, false, OUT_F32, false, true>(stream, p, di.sms);
+            }
+        }
         if constexpr (SRC == SRC_BATCHED || SRC == SRC_BOXES) {
             // Slot arrays wide enough to hold an object-heavy sample (hundreds of objects per plane: instruction-issue
             // bound, not store bound): the instantiation that also contains the register-tile renderer. T is only the

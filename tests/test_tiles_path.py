@@ -253,3 +253,34 @@ def test_tile_renderer_random_shapes_bit_equal_staged(cabi, cuda_dev, seed):
         what = f"B={B} C={C} H={H} W={W} T={T} r_hi={r_hi} sizes={sizes.tolist()} factor={factor}"
         assert torch.equal(_bits(res[0][0]), _bits(res[1][0])), "fresh: " + what
         assert torch.equal(_bits(res[0][1]), _bits(res[1][1])), "accumulate: " + what
+
+
+def test_flat_entry_dense_planes_bit_equal_staged_batched(cabi, cuda_dev, oracle):
+    """The flat entry (reference draw_heatmap: concatenated objects + a plane index each) with hundreds of objects per
+    plane also reaches the per-unit tile renderer (selected from 16 objects per plane on average): same bits as the
+    staged renderer of the batched *_ws entry on the same objects, both modes, and the oracle's values."""
+    dev = cuda_dev
+    w = workloads.make("cfg4", B=3)
+    c = w.cfg
+    oci, ori = oracle.radius_center(w.centers_f, w.bboxes_f, c.osf)
+    n = [int(s) for s in w.sizes]
+    cen = np.concatenate([oci[b, :n[b]] for b in range(w.B)]).astype(np.int32)
+    rad = np.concatenate([ori[b, :n[b]] for b in range(w.B)]).astype(np.int32)
+    idx = np.concatenate([np.full(n[b], b, np.int32) for b in range(w.B)])
+    perm = np.random.default_rng(4).permutation(len(idx))  # the flat entry takes the objects in any order
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    sizes = d(w.sizes)
+    prefill = torch.from_numpy(np.random.default_rng(6).uniform(-0.5, 0.9, (w.B, c.H, c.W)).astype(np.float32)).to(dev)
+    for mode in (_cabi.DH_MODE_FRESH, _cabi.DH_MODE_ACCUMULATE):
+        start = (lambda: torch.full((w.B, c.H, c.W), 2.0, device=dev)) if mode == _cabi.DH_MODE_FRESH else prefill.clone
+        flat = _cabi.draw_flat(cabi, start(), d(cen[perm]), d(rad[perm]), d(idx[perm]), 6.0, 1.0, mode=mode)
+        staged = _cabi.draw_batched(cabi, start(), d(oci), d(ori), sizes, None, 6.0, 1.0, mode=mode, ws=True)
+        torch.cuda.synchronize()
+        assert torch.equal(_bits(flat), _bits(staged)), f"mode {mode}"
+    want = np.zeros((w.B, c.H, c.W), np.float32)
+    oracle.draw_batched(want, oci, ori, w.sizes, 6.0, 1.0, None)
+    fresh = _cabi.draw_flat(cabi, torch.empty((w.B, c.H, c.W), device=dev), d(cen), d(rad), d(idx), 6.0, 1.0,
+                            mode=_cabi.DH_MODE_FRESH)
+    torch.cuda.synchronize()
+    want_t = torch.from_numpy(want).to(dev)
+    assert torch.equal(fresh > 0, want_t > 0) and float((fresh - want_t).abs().max()) <= 1e-6
