@@ -796,15 +796,15 @@ __device__ long long g_trace_units = 0;
 #include "dh_tiles_kernel.cuh"  // render_unit_dense: what a DENSE instantiation does with a unit that many objects land on
 namespace dh {
 
-// DENSE (selected by the host for T >= 256 padded slots — flat entry: from 16 objects per plane on average — and k >= 0,
-// fp32 planes): the instantiation
+// DENSE (selected by the host for T >= 256 padded slots — flat entry: from 16 objects per plane on average — and k >= 0):
+// the instantiation
 // also contains the register-tile renderer of dh_tiles_kernel.cuh, and each CTA decides PER UNIT, from the list it has
 // just built, which renderer the unit gets (see that file's header). Everything else is the plain kernel.
 template <bool ACCUM, int SRC, bool DIGEST, int OUT = OUT_F32, bool LEAN = false, bool DENSE = false>
 __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM : DH_G_MINB) groups_kernel(const RenderParams p) {
     static_assert(!LEAN || (!ACCUM && OUT == OUT_F32), "the lean layout is a FRESH fp32 variant");
-    static_assert(!DENSE || (OUT == OUT_F32 && !LEAN && (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_CSR)),
-                  "the per-unit dense renderer serves fp32 planes from the RaggedBatch sources and the flat entry's per-plane lists");
+    static_assert(!DENSE || (!LEAN && (SRC == SRC_BATCHED || SRC == SRC_BOXES || SRC == SRC_CSR)),
+                  "the per-unit dense renderer serves the RaggedBatch sources and the flat entry's per-plane lists");
     constexpr int ZB = ACCUM ? 0 : kGZeroBytes;    // bytes of the zero tile
     constexpr int NB = (ACCUM || LEAN) ? 1 : 2;    // staging buffers per warp
     constexpr int ES = (OUT == OUT_F32) ? 4 : 2;  // bytes per heatmap element
@@ -941,8 +941,8 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
                 ws.cur = 0;
                 ws.c0x0 = ws.c1x0 = 1;
                 ws.c0x1 = ws.c1x1 = 0;
-                render_unit_dense<ACCUM, SRC, DIGEST>(p, us, nscan, ucnt, uy0, uy1, W, p.k, reinterpret_cast<float*>(plane_b),
-                                                      p.digest_base + us.plane * plane_elems, s_unit,
+                render_unit_dense<ACCUM, SRC, DIGEST, OUT>(p, us, nscan, ucnt, uy0, uy1, W, p.k, plane_b,
+                                                           p.digest_base + us.plane * plane_elems, s_unit,
                                                       reinterpret_cast<unsigned short*>(ws.buf0), tid, lane, warp, dg);
                 dense_done = true;
             }

@@ -988,6 +988,10 @@ static int launch_render16(cudaStream_t stream, RenderParams& p, int out_dtype, 
         if (out_dtype == DH_OUT_F16) return launch_groups2<false, false, OUT_F16>(stream, p, di.sms, B, workspace);
         return launch_groups2<false, false, OUT_BF16>(stream, p, di.sms, B, workspace);
     }
+    if (g_tiles && p.T >= g_tiles_t && !(p.k < 0.0f)) {  // as for fp32 planes: the instantiation with the per-unit tile renderer
+        if (out_dtype == DH_OUT_F16) return launch_groups<false, SRC, false, OUT_F16, false, true>(stream, p, di.sms);
+        return launch_groups<false, SRC, false, OUT_BF16, false, true>(stream, p, di.sms);
+    }
     if (out_dtype == DH_OUT_F16) return launch_groups<false, SRC, false, OUT_F16>(stream, p, di.sms);
     return launch_groups<false, SRC, false, OUT_BF16>(stream, p, di.sms);
 }

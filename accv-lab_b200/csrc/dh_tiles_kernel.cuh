@@ -219,15 +219,17 @@ __device__ __forceinline__ void sweep_tile_fast(const TileEnt* __restrict__ list
 }
 
 // K4 for one tile: one expf per touched pixel (cuh:45), then the blend. Rows ty0.. (below uy1), columns tx0 + lane (+32).
-template <bool ACCUM, bool DIGEST>
+// 16-bit planes (OUT != OUT_F32, FRESH only): the fp32 value rounded once at the store, as everywhere else.
+template <bool ACCUM, bool DIGEST, int OUT>
 __device__ __forceinline__ void finish_tile(const float (&acc)[kTRows][2], unsigned none, int tx0, int ty0, int uy1, int W,
-                                            float k, float* __restrict__ plane_f, long long index0, int lane, Digest& dg) {
+                                            float k, char* __restrict__ plane_b, long long index0, int lane, Digest& dg) {
     const int xl = tx0 + lane;
 #pragma unroll
     for (int rr = 0; rr < kTRows; ++rr) {
         const int y = ty0 + rr;
         if (y < uy1) {
-            float* const row = plane_f + (long long)y * W;
+            float* const row = reinterpret_cast<float*>(plane_b) + (long long)y * W;                    // OUT_F32
+            unsigned short* const hrow = reinterpret_cast<unsigned short*>(plane_b) + (long long)y * W;  // 16-bit planes
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 const int x = xl + 32 * c;
@@ -246,7 +248,8 @@ __device__ __forceinline__ void finish_tile(const float (&acc)[kTRows][2], unsig
                             f = (0.0f >= v) ? 0.0f : v;  // max-blend into the fused zero-init
                             if constexpr (DIGEST) dg.add(f, index0 + (long long)y * W + x);
                         }
-                        row[x] = f;
+                        if constexpr (OUT == OUT_F32) row[x] = f;
+                        else hrow[x] = cvt16<OUT>(f);
                     }
                 }
             }
@@ -254,16 +257,16 @@ __device__ __forceinline__ void finish_tile(const float (&acc)[kTRows][2], unsig
     }
 }
 
-// One dense unit: rows [uy0, uy1) of the plane at `plane_f`, strip by strip, every warp of the CTA (block-collective).
+// One dense unit: rows [uy0, uy1) of the plane at `plane_b`, strip by strip, every warp of the CTA (block-collective).
 // `ucnt` objects landed on the unit. If they fit the unit list (ucnt <= kGCap) the list is rewritten in place into the
 // float form (fdy relative to uy0) — the barrier that publishes it also tells whether every object is plain — and every
 // tile sweeps it. If not, the sample's slots are scanned again per strip in passes of kGCap slots against the strip's
 // rows (a pass cannot overflow the list) and the accumulators of a tile persist over the passes; a pass that holds an
 // object that is not plain switches the tile to the predicated sweep for its remaining passes — no real value is +inf
 // up to then, so the "untouched" code is converted once. `q`: this warp's hit queue (kTQueueBytes).
-template <bool ACCUM, int SRC, bool DIGEST>
+template <bool ACCUM, int SRC, bool DIGEST, int OUT>
 __device__ __forceinline__ void render_unit_dense(const RenderParams& p, const UnitSrc& us, int nscan, int ucnt, int uy0,
-                                                  int uy1, int W, float k, float* __restrict__ plane_f, long long index0,
+                                                  int uy1, int W, float k, char* __restrict__ plane_b, long long index0,
                                                   ObjI* s_unit, unsigned short* __restrict__ q, int tid, int lane, int warp,
                                                   Digest& dg) {
     __shared__ int s_dcnt[2], s_dodd[2];  // pass list size / "not plain" flag, double-buffered by pass parity
@@ -333,7 +336,7 @@ __device__ __forceinline__ void render_unit_dense(const RenderParams& p, const U
                 }
             }
             if (tile < tiles_x)
-                finish_tile<ACCUM, DIGEST>(acc, slow ? kTNone : kTNoneFast, tx0, ty0, uy1, W, k, plane_f, index0, lane, dg);
+                finish_tile<ACCUM, DIGEST, OUT>(acc, slow ? kTNone : kTNoneFast, tx0, ty0, uy1, W, k, plane_b, index0, lane, dg);
         }
     }
     if (!prebuilt) __syncthreads();  // the list storage goes back to the kernel
