@@ -883,7 +883,7 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
             g_trace[u * 4 + 2] = sm;
         }
 #endif
-        if (tid == 0 && p.use_clc) {  // ask for the next unit now; the answer lands while this one is rendered
+        if (tid == 0 && p.use_clc == 2) {  // A/B only: ask for the next unit at the START of this one (round 1 / early round 2)
             fence_proxy_async();
             mbar_expect_tx(&s_bar, 16);
             clc_try_cancel(&s_clc, &s_bar);
@@ -1012,6 +1012,18 @@ __global__ void __launch_bounds__(kGThreads, (ACCUM || LEAN) ? DH_G_MINB_ACCUM :
 #endif
         // next unit: the one the block scheduler hands over (cluster launch control), else the static stride
         if (p.use_clc) {
+            // The next unit is claimed only NOW, when this one is done. Claimed at the start of a unit (so that the answer
+            // arrives while it is rendered — how this kernel began) the claim of a CTA that then spends 15-20 us on a heavy
+            // unit sits on its next unit all that time while other CTAs run dry: unit timelines showed the last 3 us of
+            // cfg3 with 2-25 of 444 slots busy, every late unit one that a long-running CTA had reserved. Claiming late
+            // makes the hand-out truly dynamic (list scheduling in heaviest-first order); the round trip to the block
+            // scheduler hides behind the bulk stores still draining. cfg3 37.1 -> 34.7 us, b384 207.0 -> 205.5 us, cfg5
+            // 1.566 -> 1.562 ms (profiles/r02/clc_mode_ab.txt).
+            if (tid == 0 && p.use_clc != 2) {
+                fence_proxy_async();
+                mbar_expect_tx(&s_bar, 16);
+                clc_try_cancel(&s_clc, &s_bar);
+            }
             mbar_wait(&s_bar, clc_phase);
             clc_phase ^= 1u;
             unsigned nx;

@@ -692,8 +692,10 @@ static const int g_dense_cost16 = DH_KNOB("DH_G_DENSE_COST16", 48);    // ... wh
 static const int g_dense_cost16_accum = DH_KNOB("DH_G_DENSE_COST16_ACCUM", 112);  // ... the same for ACCUMULATE (measured breakevens: ~3 and ~7)
 static const int g_no_bin = DH_KNOB("DH_G_NOBIN", 0);                  // 1: ignore the workspace of the *_ws entries
 static const int g_lpt = DH_KNOB("DH_G_LPT", 10);                      // heaviest-first hand-out inside the last g_lpt / 2 waves (0 = off)
+static const int g_clc_mode = DH_KNOB("DH_G_CLC_MODE", 1);             // when a CTA claims its next unit: 1 when the current one is done, 2 at its start (A/B)
 static const int g_pdl = DH_KNOB("DH_G_PDL", 1);                       // programmatic dependent launch of the groups kernels
-static const int g_tail_div = DH_KNOB("DH_G_TAIL_DIV", 2);             // tail-tier units are 1/this of a full unit (1 = off)
+static const int g_tail_div = DH_KNOB("DH_G_TAIL_DIV", 4);             // tail-tier units are 1/this of a full unit (1 = off); 2 until units were claimed late, then re-measured
+static const int g_tail_cap_div = DH_KNOB("DH_G_TAIL_CAP_DIV", 2);     // ... but at most 1/this of all planes
 static const int g_tail_waves_x2 = DH_KNOB("DH_G_TAIL_WAVES_X2", 2);   // tail tier = this/2 waves of full-size units
 
 // Plan of the groups kernels: row group = G whole rows (<= kGStageCap bytes), unit = up to 64 groups of one plane,
@@ -760,14 +762,18 @@ static bool make_groups_plan(RenderParams& p, long long max_ctas, int es = 4, bo
     // The planes that are handed out last (about one wave of full-size units) are cut into half-size units. Measured
     // gain is small (cfg3 43.7 -> 42.3 us, 8-GPU slice of cfg5 221.0 -> 220.1 us): an EMPTY unit already takes 3-4 us
     // of pure latency (sizes -> slots -> barriers -> next-unit handshake), so finer units buy little; quarter or
-    // eighth units and longer tiers were slower (profiles/r01/experiments.md).
+    // eighth units and longer tiers were slower (profiles/r01/experiments.md). Since the next unit is claimed when the
+    // current one is done (dh_groups_kernel.cuh), quarter-size units are the better tier where they still hold a group
+    // per warp (96 / 192 / 384 samples of cfg5: 58.9 / 107.1 / 205.4 us against 59.1 / 107.7 / 205.3 with halves), and
+    // cfg3, whose units are too small to be cut in four, is best without a tier (34.3 against 34.7 us):
+    // profiles/r02/retune_tail_tier.txt.
     p.tier1_planes = p.num_planes;
     p.bands_per_unit2 = p.bands_per_unit;
     p.units_per_plane2 = p.units_per_plane;
     const int small = g_tail_div > 1 ? p.bands_per_unit / g_tail_div : 0;
     if (small >= kGWarps && p.num_planes * p.units_per_plane > max_ctas) {
         long long planes2 = (g_tail_waves_x2 * max_ctas / 2 + p.units_per_plane - 1) / p.units_per_plane;
-        if (planes2 > p.num_planes / 2) planes2 = p.num_planes / 2;
+        if (planes2 > p.num_planes / g_tail_cap_div) planes2 = p.num_planes / g_tail_cap_div;
         if (planes2 > 0) {
             p.tier1_planes = p.num_planes - planes2;
             p.units_per_plane2 = (groups_y + small - 1) / small;
@@ -822,6 +828,7 @@ static int launch_groups(cudaStream_t stream, RenderParams& p, int sms) {
     // over the not-yet-launched ones through cluster launch control, so only ~sms*DH_G_MINB CTAs ever start.
     long long g = p.total_units;
     p.use_clc = !g_persistent && !g_no_clc && g <= 0x7fffffffll;  // a clamped grid falls back to the static stride
+    if (p.use_clc) p.use_clc = g_clc_mode;
     if (g_persistent && g > max_ctas) g = max_ctas;
     if (g > 0x7fffffffll) g = 0x7fffffffll;
     // heaviest-first hand-out (dh_groups_kernel.cuh build_perm): only when the launch has more than one wave — a single

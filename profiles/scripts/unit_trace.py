@@ -58,3 +58,5 @@ print("5 longest units: (start, dur, objects, touched groups)", [(round(float(st
 for lo_, hi_ in ((0, 1), (1, 4), (4, 16), (16, 1 << 20)):
     m = (ucnt >= lo_) & (ucnt < hi_)
     if m.any(): print(f"units with {lo_}..{hi_-1} objects: {int(m.sum())}, mean duration {dur[m].mean():.2f} us")
+if os.environ.get("DH_TRACE_SAVE"):  # raw (start ns, end ns, SM, objects | touched groups << 32) per unit, for offline analysis
+    np.save(os.environ["DH_TRACE_SAVE"], t)
