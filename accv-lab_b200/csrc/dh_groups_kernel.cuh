@@ -300,6 +300,7 @@ __device__ __forceinline__ void sparse_rows(unsigned* __restrict__ buf, float* _
 // this grid that has not been launched yet, cancels that launch and does its work itself. The grid still has one CTA
 // per unit and units are still handed out dynamically and in address order, but shared-memory set-up is paid once per
 // resident CTA and — the point — a CTA starts the next unit's list build while its bulk stores are still draining.
+// The request goes out when the current unit is DONE, not at its start (see the end of the unit loop in groups_kernel).
 __device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
